@@ -1,0 +1,284 @@
+/* TEST INFRASTRUCTURE ONLY.
+ *
+ * C entry points around the UNMODIFIED reference sources (compiled where they lie under
+ * /root/reference by oracle/Makefile into oracle/_ref/libshenqi_ref.so).  This file contains no
+ * reference code: it only fills the reference's own structs (PartManager, DomainDecomp, PetaPM,
+ * gravshort_tree_params) and calls the reference's own functions
+ *   PEANO / peano_hilbert_key      libgadget/utils/peano.h:15, peano.cpp:144
+ *   slots_gc_sorted                libgadget/slotsmanager.cpp:419
+ *   force_tree_full                libgadget/forcetree.cpp:110
+ *   grav_short_tree                libgadget/gravshort-tree2.cpp:141
+ *   GravLocalTreeWalk::visit       libgadget/gravshort2.hpp:227   (interaction counts)
+ *   grav_short_pair                libgadget/gravshort-pair.c:22
+ * the way libgadget/tests/test_forcetree.cpp:294-331 and test_gravity.cpp:197-247 do
+ * (single rank, trivial domain).  Only tests/, smoke() and bench.py's CPU-baseline leg load it.
+ */
+#include <mpi.h>
+#include <string.h>
+#include <math.h>
+#include <omp.h>
+#include <string>
+
+#include <libgadget/utils/mymalloc.h>
+#include <libgadget/utils/endrun.h>
+#include <libgadget/utils/peano.h>
+#include <libgadget/partmanager.h>
+#include <libgadget/slotsmanager.h>
+#include <libgadget/walltime.h>
+#include <libgadget/domain.h>
+#include <libgadget/forcetree.h>
+#include <libgadget/gravity.h>
+#include <libgadget/gravity_old.h>
+#include <libgadget/petapm.h>
+#include <libgadget/timestep.h>
+#include <libgadget/gravshort2.hpp>
+
+/* ---- symbols the path references but which live in reference files we do not build ---- */
+/* libgadget/timestep.cpp:78 : forward to the particle manager, no list */
+ActiveParticles init_empty_active_particles(struct part_manager_type * pman)
+{
+    ActiveParticles act;
+    memset(&act, 0, sizeof(act));
+    act.ActiveParticle = NULL;
+    act.NumActiveParticle = pman->NumPart;
+    act.Particles = pman->Base;
+    return act;
+}
+/* libgadget/timebinmgr.cpp: only consulted for gas/BH hmax; DM-only path never reaches it */
+int is_timebin_active(int bin, inttime_t current_ti) { (void) bin; (void) current_ti; return 1; }
+
+static struct ClockTable RefClocks;
+static DomainDecomp RefDomain;
+static ForceTree RefTree;
+static int ref_initialised = 0;
+
+static void ref_trivial_domain(DomainDecomp * ddecomp)
+{
+    memset(ddecomp, 0, sizeof(*ddecomp));
+    ddecomp->domain_allocated_flag = 1;
+    ddecomp->NTopNodes = 1;
+    ddecomp->NTopLeaves = 1;
+    ddecomp->TopNodes = (struct topnode_data *) calloc(1, sizeof(struct topnode_data));
+    ddecomp->TopNodes[0].Daughter = -1;
+    ddecomp->TopNodes[0].Leaf = 0;
+    ddecomp->TopNodes[0].StartKey = 0;
+    ddecomp->TopNodes[0].Shift = BITS_PER_DIMENSION * 3;
+    ddecomp->TopLeaves = (struct topleaf_data *) calloc(1, sizeof(struct topleaf_data));
+    ddecomp->TopLeaves[0].Task = 0;
+    ddecomp->Tasks = (struct task_data *) calloc(1, sizeof(struct task_data));
+    ddecomp->Tasks[0].StartLeaf = 0;
+    ddecomp->Tasks[0].EndLeaf = 1;
+}
+
+extern "C" {
+
+int ref_init(void)
+{
+    if(ref_initialised)
+        return 0;
+    int thr;
+    MPI_Init_thread(NULL, NULL, MPI_THREAD_FUNNELED, &thr);
+    init_endrun(0);
+    allocator_malloc_init(A_MAIN, "MAIN", 0);
+    allocator_malloc_init(A_TEMP, "TEMP", 0);
+    walltime_init(&RefClocks);
+    memset(PartManager, 0, sizeof(PartManager[0]));
+    memset(SlotsManager, 0, sizeof(SlotsManager[0]));
+    memset(&RefTree, 0, sizeof(RefTree));
+    ref_trivial_domain(&RefDomain);
+    ref_initialised = 1;
+    return 0;
+}
+
+int ref_sizeof_particle(void) { return (int) sizeof(struct particle_data); }
+int ref_sizeof_node(void) { return (int) sizeof(struct NODE); }
+
+uint64_t ref_peano_hilbert_key(int x, int y, int z, int bits) { return peano_hilbert_key(x, y, z, bits); }
+
+void ref_peano_keys(const double * pos, int64_t n, double box, uint64_t * keys)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < n; i++)
+        keys[i] = PEANO(pos + 3 * i, box);
+}
+
+/* Load n particles (type 1 unless types given) into the reference's particle manager. */
+void ref_set_particles(const double * pos, const float * mass, const uint64_t * ids, const unsigned char * types, int64_t n, double box)
+{
+    ref_init();
+    if(force_tree_allocated(&RefTree))
+        force_tree_free(&RefTree);
+    if(PartManager->Base)
+        myfree(PartManager->Base);
+    memset(PartManager, 0, sizeof(PartManager[0]));
+    particle_alloc_memory(PartManager, box, n);
+    memset(PartManager->Base, 0, sizeof(struct particle_data) * n);
+    #pragma omp parallel for
+    for(int64_t i = 0; i < n; i++) {
+        struct particle_data * p = &PartManager->Base[i];
+        for(int j = 0; j < 3; j++)
+            p->Pos[j] = pos[3 * i + j];
+        p->Mass = mass[i];
+        p->ID = ids ? ids[i] : (uint64_t) (i + 1);
+        p->Type = types ? types[i] : 1;
+    }
+    PartManager->NumPart = n;
+    PartManager->BoxSize = box;
+}
+
+int64_t ref_num_particles(void) { return PartManager->NumPart; }
+
+void ref_set_accels(const double * fulltree, const double * gravpm)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        for(int j = 0; j < 3; j++) {
+            if(fulltree) PartManager->Base[i].FullTreeGravAccel[j] = fulltree[3 * i + j];
+            if(gravpm) PartManager->Base[i].GravPM[j] = gravpm[3 * i + j];
+        }
+}
+
+void ref_get_particles(double * pos, float * mass, uint64_t * ids, double * fulltree, double * potential)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++) {
+        const struct particle_data * p = &PartManager->Base[i];
+        for(int j = 0; j < 3; j++) {
+            if(pos) pos[3 * i + j] = p->Pos[j];
+            if(fulltree) fulltree[3 * i + j] = p->FullTreeGravAccel[j];
+        }
+        if(mass) mass[i] = p->Mass;
+        if(ids) ids[i] = p->ID;
+        if(potential) potential[i] = p->Potential;
+    }
+}
+
+/* raw access to the reference's AoS, for boundary-layout tests */
+void * ref_particle_base(void) { return PartManager->Base; }
+
+/* slots_gc_sorted: PH key + sort by (type,key) + permute */
+double ref_sort_particles(void)
+{
+    double t0 = MPI_Wtime();
+    slots_gc_sorted(PartManager, SlotsManager);
+    return MPI_Wtime() - t0;
+}
+
+/* force_tree_full with the trivial single-rank domain. Returns numnodes; seconds in *secs. */
+int64_t ref_tree_build(double treeallocfactor, double * secs)
+{
+    init_forcetree_params(treeallocfactor);
+    double t0 = MPI_Wtime();
+    force_tree_full(&RefTree, &RefDomain, 0, "");
+    if(secs) *secs = MPI_Wtime() - t0;
+    return RefTree.numnodes;
+}
+
+void ref_tree_free(void)
+{
+    if(force_tree_allocated(&RefTree))
+        force_tree_free(&RefTree);
+}
+
+int64_t ref_tree_firstnode(void) { return RefTree.firstnode; }
+int64_t ref_tree_numnodes(void) { return RefTree.numnodes; }
+int64_t ref_tree_numparticles(void) { return RefTree.NumParticles; }
+/* copy the NODE image [firstnode, firstnode+numnodes) out as raw bytes */
+void ref_tree_copy_nodes(void * out)
+{
+    memcpy(out, RefTree.Nodes_base, sizeof(struct NODE) * RefTree.numnodes);
+}
+
+static PetaPM ref_make_pm(int Nmesh, double Asmth, double G)
+{
+    PetaPM pm;
+    memset(&pm, 0, sizeof(pm));
+    pm.Nmesh = Nmesh;
+    pm.Asmth = Asmth;
+    pm.G = G;
+    pm.BoxSize = PartManager->BoxSize;
+    pm.CellSize = PartManager->BoxSize / Nmesh;
+    return pm;
+}
+
+static struct gravshort_tree_params ref_make_treepar(double ErrTolForceAcc, double BHOpeningAngle, double MaxBHOpeningAngle,
+        int TreeUseBH, double Rcut, double FracSoft, int windowtype)
+{
+    struct gravshort_tree_params tp;
+    memset(&tp, 0, sizeof(tp));
+    tp.ErrTolForceAcc = ErrTolForceAcc;
+    tp.BHOpeningAngle = BHOpeningAngle;
+    tp.MaxBHOpeningAngle = MaxBHOpeningAngle;
+    tp.TreeUseBH = TreeUseBH;
+    tp.Rcut = Rcut;
+    tp.FractionalGravitySoftening = FracSoft;
+    tp.MaxExportBufferBytes = 1024 * 1024 * 1024L;
+    tp.ShortRangeForceWindowType = (enum ShortRangeForceWindowType) windowtype;
+    return tp;
+}
+
+/* grav_short_tree on all particles (tree must be built). accel: N x 3 (already x G). Returns seconds. */
+double ref_grav_short_tree(int Nmesh, double Asmth, double G, double ErrTolForceAcc, double BHOpeningAngle,
+        double MaxBHOpeningAngle, int TreeUseBH, double Rcut, double FracSoft, double MeanSeparation,
+        int windowtype, double rho0, double * accel)
+{
+    PetaPM pm = ref_make_pm(Nmesh, Asmth, G);
+    set_gravshort_treepar(ref_make_treepar(ErrTolForceAcc, BHOpeningAngle, MaxBHOpeningAngle, TreeUseBH, Rcut, FracSoft, windowtype));
+    gravshort_set_softenings(MeanSeparation);
+    ActiveParticles act = init_empty_active_particles(PartManager);
+    double t0 = MPI_Wtime();
+    grav_short_tree(&act, &pm, &RefTree, (MyFloat (*)[3]) accel, rho0, 0, false);
+    return MPI_Wtime() - t0;
+}
+
+/* Per-particle interaction counts of the reference's own local walk (gravshort2.hpp:227-322),
+ * with the same parameters; does not modify any particle. Returns the total. */
+int64_t ref_grav_count_interactions(int Nmesh, double Asmth, double G, double ErrTolForceAcc, double BHOpeningAngle,
+        double MaxBHOpeningAngle, int TreeUseBH, double Rcut, double FracSoft, double MeanSeparation,
+        int windowtype, int64_t * counts)
+{
+    PetaPM pm = ref_make_pm(Nmesh, Asmth, G);
+    struct gravshort_tree_params tp = ref_make_treepar(ErrTolForceAcc, BHOpeningAngle, MaxBHOpeningAngle, TreeUseBH, Rcut, FracSoft, windowtype);
+    set_gravshort_treepar(tp);
+    gravshort_set_softenings(MeanSeparation);
+    GravShortTable gravtab(tp.ShortRangeForceWindowType, Asmth);
+    GravTreeParams priv(tp, 0, 1.0, &pm, RefTree.BoxSize, gravtab);
+    int64_t total = 0;
+    #pragma omp parallel for schedule(dynamic, 64) reduction(+: total)
+    for(int64_t i = 0; i < PartManager->NumPart; i++) {
+        GravTreeQuery input(PartManager->Base[i], NULL, RefTree.firstnode, priv);
+        GravTreeResult output(input);
+        GravLocalTreeWalk lv(RefTree.Nodes, input);
+        const int64_t n = lv.visit<TREEWALK_PRIMARY>(input, &output, priv, PartManager->Base);
+        if(counts) counts[i] = n;
+        total += n;
+    }
+    return total;
+}
+
+/* grav_short_pair: direct sum over r <= Rcut; result lands in FullTreeGravAccel/Potential (tree is full). */
+double ref_grav_short_pair(int Nmesh, double Asmth, double G, double Rcut, double FracSoft, double MeanSeparation,
+        int windowtype, double rho0, double * accel)
+{
+    PetaPM pm = ref_make_pm(Nmesh, Asmth, G);
+    struct gravshort_tree_params tp = ref_make_treepar(0.002, 0.175, 0.9, 0, Rcut, FracSoft, windowtype);
+    set_gravshort_treepar(tp);
+    set_gravshort_treepar_old(tp);
+    gravshort_set_softenings(MeanSeparation);
+    ActiveParticles act = init_empty_active_particles(PartManager);
+    double t0 = MPI_Wtime();
+    grav_short_pair(&act, &pm, &RefTree, Rcut, rho0);
+    double dt = MPI_Wtime() - t0;
+    if(accel) {
+        #pragma omp parallel for
+        for(int64_t i = 0; i < PartManager->NumPart; i++)
+            for(int j = 0; j < 3; j++)
+                accel[3 * i + j] = PartManager->Base[i].FullTreeGravAccel[j];
+    }
+    return dt;
+}
+
+double ref_force_softening(void) { return FORCE_SOFTENING(); }
+int ref_omp_threads(void) { return omp_get_max_threads(); }
+
+} /* extern "C" */

@@ -1,0 +1,151 @@
+/* TEST INFRASTRUCTURE ONLY - single-rank stand-in for <mpi.h>.
+ *
+ * The reference (MP-Gadget/shenqi) needs MPI to compile; MPI is not installed in
+ * this image.  This header lets the reference's own, unmodified sources for the
+ * short-range gravity path compile into oracle/_ref/ as a one-rank program.
+ * Every collective degenerates to a local copy; point-to-point calls are never
+ * reached with one rank (there is nobody to export to) and abort if they are.
+ *
+ * Nothing in the product (shenqi_b200/) includes this file.
+ */
+#ifndef SHENQI_ORACLE_MPI_SHIM_H
+#define SHENQI_ORACLE_MPI_SHIM_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int MPI_Comm;
+typedef long MPI_Datatype;   /* encodes the byte size of one element */
+typedef int MPI_Op;
+typedef int MPI_Request;
+typedef long MPI_Aint;
+typedef struct { int MPI_SOURCE, MPI_TAG, MPI_ERROR; } MPI_Status;
+
+#define MPI_COMM_WORLD 1
+#define MPI_COMM_NULL 0
+#define MPI_SUCCESS 0
+#define MPI_UNDEFINED (-32766)
+#define MPI_ANY_SOURCE (-1)
+#define MPI_ANY_TAG (-1)
+#define MPI_REQUEST_NULL (-1)
+#define MPI_STATUS_IGNORE ((MPI_Status *) 0)
+#define MPI_STATUSES_IGNORE ((MPI_Status *) 0)
+#define MPI_IN_PLACE ((void *) 1)
+#define MPI_THREAD_FUNNELED 1
+#define MPI_MAX_PROCESSOR_NAME 64
+
+#define MPI_DATATYPE_NULL ((MPI_Datatype) 0)
+#define MPI_BYTE ((MPI_Datatype) 1)
+#define MPI_CHAR ((MPI_Datatype) 1)
+#define MPI_INT ((MPI_Datatype) 4)
+#define MPI_UNSIGNED ((MPI_Datatype) 4)
+#define MPI_FLOAT ((MPI_Datatype) 4)
+#define MPI_LONG ((MPI_Datatype) 8)
+#define MPI_INT64 ((MPI_Datatype) 8)
+#define MPI_INT64_T ((MPI_Datatype) 8)
+#define MPI_UINT64 ((MPI_Datatype) 8)
+#define MPI_UINT64_T ((MPI_Datatype) 8)
+#define MPI_LONG_LONG ((MPI_Datatype) 8)
+#define MPI_UNSIGNED_LONG ((MPI_Datatype) 8)
+#define MPI_DOUBLE ((MPI_Datatype) 8)
+#define MPI_AINT ((MPI_Datatype) 8)
+
+#define MPI_SUM 1
+#define MPI_MAX 2
+#define MPI_MIN 3
+#define MPI_LOR 4
+#define MPI_LAND 5
+#define MPI_BOR 6
+
+static inline void shim_mpi_unreachable(const char * what)
+{
+    fprintf(stderr, "oracle mpi shim: %s reached with a single rank\n", what);
+    abort();
+}
+
+static inline int shim_mpi_copy(const void * sendbuf, void * recvbuf, long count, MPI_Datatype type)
+{
+    if(sendbuf != MPI_IN_PLACE && sendbuf != recvbuf && count > 0)
+        memmove(recvbuf, sendbuf, (size_t) count * (size_t) type);
+    return MPI_SUCCESS;
+}
+
+static inline int MPI_Init(int * argc, char *** argv) { (void) argc; (void) argv; return MPI_SUCCESS; }
+static inline int MPI_Init_thread(int * argc, char *** argv, int required, int * provided)
+{ (void) argc; (void) argv; if(provided) *provided = required; return MPI_SUCCESS; }
+static inline int MPI_Finalize(void) { return MPI_SUCCESS; }
+static inline int MPI_Initialized(int * flag) { *flag = 1; return MPI_SUCCESS; }
+static inline int MPI_Abort(MPI_Comm comm, int code) { (void) comm; fprintf(stderr, "MPI_Abort(%d)\n", code); abort(); return 0; }
+static inline int MPI_Comm_rank(MPI_Comm comm, int * rank) { (void) comm; *rank = 0; return MPI_SUCCESS; }
+static inline int MPI_Comm_size(MPI_Comm comm, int * size) { (void) comm; *size = 1; return MPI_SUCCESS; }
+static inline int MPI_Barrier(MPI_Comm comm) { (void) comm; return MPI_SUCCESS; }
+static inline double MPI_Wtime(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double) ts.tv_sec + 1e-9 * (double) ts.tv_nsec;
+}
+static inline int MPI_Get_processor_name(char * name, int * len) { strcpy(name, "oracle"); *len = 6; return MPI_SUCCESS; }
+
+static inline int MPI_Type_contiguous(int count, MPI_Datatype oldtype, MPI_Datatype * newtype)
+{ *newtype = (MPI_Datatype) count * oldtype; return MPI_SUCCESS; }
+static inline int MPI_Type_commit(MPI_Datatype * type) { (void) type; return MPI_SUCCESS; }
+static inline int MPI_Type_free(MPI_Datatype * type) { *type = MPI_DATATYPE_NULL; return MPI_SUCCESS; }
+static inline int MPI_Type_get_extent(MPI_Datatype type, MPI_Aint * lb, MPI_Aint * extent)
+{ *lb = 0; *extent = (MPI_Aint) type; return MPI_SUCCESS; }
+static inline int MPI_Type_size(MPI_Datatype type, int * size) { *size = (int) type; return MPI_SUCCESS; }
+
+static inline int MPI_Bcast(void * buf, int count, MPI_Datatype type, int root, MPI_Comm comm)
+{ (void) buf; (void) count; (void) type; (void) root; (void) comm; return MPI_SUCCESS; }
+static inline int MPI_Reduce(const void * sendbuf, void * recvbuf, int count, MPI_Datatype type, MPI_Op op, int root, MPI_Comm comm)
+{ (void) op; (void) root; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, count, type); }
+static inline int MPI_Allreduce(const void * sendbuf, void * recvbuf, int count, MPI_Datatype type, MPI_Op op, MPI_Comm comm)
+{ (void) op; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, count, type); }
+static inline int MPI_Alltoall(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, int recvcount, MPI_Datatype recvtype, MPI_Comm comm)
+{ (void) recvcount; (void) recvtype; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, sendcount, sendtype); }
+static inline int MPI_Alltoallv(const void * sendbuf, const int * sendcounts, const int * sdispls, MPI_Datatype sendtype,
+        void * recvbuf, const int * recvcounts, const int * rdispls, MPI_Datatype recvtype, MPI_Comm comm)
+{
+    (void) recvcounts; (void) recvtype; (void) comm;
+    if(sendbuf == MPI_IN_PLACE) return MPI_SUCCESS;
+    memmove((char *) recvbuf + (size_t) rdispls[0] * recvtype, (const char *) sendbuf + (size_t) sdispls[0] * sendtype, (size_t) sendcounts[0] * sendtype);
+    return MPI_SUCCESS;
+}
+static inline int MPI_Allgather(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, int recvcount, MPI_Datatype recvtype, MPI_Comm comm)
+{ (void) recvcount; (void) recvtype; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, sendcount, sendtype); }
+static inline int MPI_Allgatherv(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, const int * recvcounts, const int * displs, MPI_Datatype recvtype, MPI_Comm comm)
+{
+    (void) recvcounts; (void) comm;
+    if(sendbuf == MPI_IN_PLACE) return MPI_SUCCESS;
+    memmove((char *) recvbuf + (size_t) displs[0] * recvtype, sendbuf, (size_t) sendcount * sendtype);
+    return MPI_SUCCESS;
+}
+static inline int MPI_Gather(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, int recvcount, MPI_Datatype recvtype, int root, MPI_Comm comm)
+{ (void) recvcount; (void) recvtype; (void) root; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, sendcount, sendtype); }
+
+static inline int MPI_Isend(const void * buf, int count, MPI_Datatype type, int dest, int tag, MPI_Comm comm, MPI_Request * req)
+{ (void) buf; (void) count; (void) type; (void) dest; (void) tag; (void) comm; (void) req; shim_mpi_unreachable("MPI_Isend"); return 0; }
+static inline int MPI_Irecv(void * buf, int count, MPI_Datatype type, int src, int tag, MPI_Comm comm, MPI_Request * req)
+{ (void) buf; (void) count; (void) type; (void) src; (void) tag; (void) comm; (void) req; shim_mpi_unreachable("MPI_Irecv"); return 0; }
+static inline int MPI_Send(const void * buf, int count, MPI_Datatype type, int dest, int tag, MPI_Comm comm)
+{ (void) buf; (void) count; (void) type; (void) dest; (void) tag; (void) comm; shim_mpi_unreachable("MPI_Send"); return 0; }
+static inline int MPI_Recv(void * buf, int count, MPI_Datatype type, int src, int tag, MPI_Comm comm, MPI_Status * st)
+{ (void) buf; (void) count; (void) type; (void) src; (void) tag; (void) comm; (void) st; shim_mpi_unreachable("MPI_Recv"); return 0; }
+static inline int MPI_Waitall(int count, MPI_Request * reqs, MPI_Status * sts)
+{ (void) count; (void) reqs; (void) sts; return MPI_SUCCESS; }
+static inline int MPI_Waitsome(int incount, MPI_Request * reqs, int * outcount, int * indices, MPI_Status * sts)
+{ (void) incount; (void) reqs; (void) indices; (void) sts; *outcount = MPI_UNDEFINED; return MPI_SUCCESS; }
+static inline int MPI_Wait(MPI_Request * req, MPI_Status * st) { (void) req; (void) st; return MPI_SUCCESS; }
+
+#ifdef __cplusplus
+}
+#endif
+#endif
