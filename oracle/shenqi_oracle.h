@@ -1,0 +1,95 @@
+/* TEST INFRASTRUCTURE ONLY - CPU restatement ("port") of the reference's short-range TreePM path.
+ *
+ * Plain C, double precision, one function per reference function, each citing the file:line it
+ * follows (paths relative to /root/reference).  Pinned (tests/test_oracle_*.py) against
+ *   - the 64 golden Peano-Hilbert keys of libgadget/tests/test_peano.cpp:102 (+ Hilbert-curve adjacency),
+ *   - the reference's own code compiled into oracle/_ref/libshenqi_ref.so (keys, sort order, tree
+ *     topology + moments, grav_short_tree accelerations, interaction counts, grav_short_pair),
+ *   - the tree invariants of libgadget/tests/test_forcetree.cpp:21-169.
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may load this library.
+ * The product (shenqi_b200/) never links or calls it.
+ */
+#ifndef SHENQI_ORACLE_H
+#define SHENQI_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Same byte layout as the reference's struct NODE (libgadget/forcetree.h:29-66), 120 bytes. */
+typedef struct sqo_node {
+    int sibling;
+    int father;
+    double len;
+    double center[3];
+    double cofm[3];
+    double mass;
+    double hmax;
+    int suns[8];
+    int noccupied;
+    unsigned int flags; /* bit0 InternalTopLevel, bit1 TopLevel, bit2 DependsOnLocalMass, bits3-4 ChildType */
+} sqo_node;
+
+#define SQO_PARTICLE_NODE 0
+#define SQO_NODE_NODE 1
+#define SQO_PSEUDO_NODE 2
+#define SQO_CHILDTYPE(n) (((n)->flags >> 3) & 3u)
+#define SQO_TOPLEVEL(n) (((n)->flags >> 1) & 1u)
+
+/* Parameters of one grav_short_tree call: GravTreeParams, libgadget/gravshort2.hpp:21-55 */
+typedef struct sqo_grav_params {
+    double BoxSize;
+    int Nmesh;
+    double Asmth;
+    double G;
+    double ErrTolForceAcc;
+    double BHOpeningAngle;
+    double MaxBHOpeningAngle;
+    int TreeUseBH;
+    double TreeRcut;           /* in units of Asmth * cellsize */
+    double GravitySoftening;   /* comoving Plummer-equivalent epsilon; ForceSoftening = 2.8 * epsilon */
+    int WindowType;            /* 1 exact table, 2 erfc */
+    double rho0;
+    int update_potential;      /* tree->full_particle_tree_flag */
+} sqo_grav_params;
+
+/* libgadget/utils/peano.cpp:144-183 */
+uint64_t sqo_peano_hilbert_key(int x, int y, int z, int bits);
+/* libgadget/utils/peano.h:15-21 */
+void sqo_peano_keys(const double * pos, int64_t n, double box, uint64_t * keys);
+/* libgadget/slotsmanager.cpp:395-437: order by (TypeKey, Key); ties broken by input index */
+void sqo_sort_order(const uint64_t * keys, const unsigned char * types, int64_t n, int64_t * perm);
+
+/* libgadget/forcetree.cpp:653-686, 726-859, 480-519, 369-476, 1016-1142 with the single-rank
+ * trivial domain of libgadget/tests/test_forcetree.cpp:294-314.  nodes[0] is the root
+ * (node number firstnode).  Returns the number of nodes used, or -1 if maxnodes is too small. */
+int64_t sqo_tree_build(const double * pos, const float * mass, int64_t n, double box,
+                       sqo_node * nodes, int64_t maxnodes, int64_t firstnode);
+
+/* libgadget/gravshort2.hpp:227-358 (visit<PRIMARY>, apply_accn), :88-107 (postprocess), :111-121.
+ * oldacc[i] = |FullTreeGravAccel+GravPM|/G.  accel (N x 3) is multiplied by G; potential may be NULL.
+ * counts[i] = number of apply_accn calls (may be NULL).  Returns total interactions. */
+int64_t sqo_grav_short_tree(const sqo_node * nodes, int64_t firstnode, const double * pos, const float * mass,
+                            const double * oldacc, const int * active, int64_t nactive,
+                            const sqo_grav_params * par, double * accel, double * potential, int64_t * counts);
+
+/* libgadget/gravshort-pair.c:22-127: direct sum over r <= Rcut*Asmth*cellsize, O(N^2). accel x G. */
+void sqo_grav_short_pair(const double * pos, const float * mass, int64_t n, const sqo_grav_params * par,
+                         double * accel, double * potential);
+
+/* libgadget/petapm.cpp:1132-1183 + 1304-1310 on one periodic slab: mesh[Nmesh^3], z fastest. */
+void sqo_cic_paint(const double * pos, const float * mass, int64_t n, double box, int nmesh, double * mesh);
+/* libgadget/petapm.cpp:1132-1183 + gravpm.cpp:489-500: out[i] += sum_w mesh */
+void sqo_cic_readout(const double * mesh, const double * pos, int64_t n, double box, int nmesh, double * out);
+/* libgadget/gravpm.cpp:378-444 (potential_transfer, no neutrinos) and :448-487 (force_transfer), on a
+ * numpy rfftn layout: rho_k[x][y][kz], kz = 0..Nmesh/2, complex interleaved.  out arrays same shape. */
+void sqo_pm_transfer(const double * rho_k, int nmesh, double box, double asmth, double G,
+                     double * pot_k, double * fx_k, double * fy_k, double * fz_k);
+
+/* Window table as GravShortTable builds it (libgadget/gravshort-tree2.cpp:29-69): floats. */
+void sqo_window_table(int windowtype, double asmth, float * force_tab, float * pot_tab, double * dx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

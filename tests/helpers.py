@@ -1,0 +1,250 @@
+"""Test-side helpers: ctypes loaders for the checkers (oracle restatement, reference build) and the
+canonical tree form used to compare topologies.  TEST INFRASTRUCTURE ONLY."""
+import ctypes, os, subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "libshenqi_oracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libshenqi_ref.so")
+
+c_i64, c_dbl, c_int = ctypes.c_int64, ctypes.c_double, ctypes.c_int
+
+# byte layout of the reference's struct NODE (libgadget/forcetree.h:38-66), 120 B
+NODE_DTYPE = np.dtype([("sibling", "<i4"), ("father", "<i4"), ("len", "<f8"), ("center", "<f8", 3),
+                       ("cofm", "<f8", 3), ("mass", "<f8"), ("hmax", "<f8"), ("suns", "<i4", 8),
+                       ("noccupied", "<i4"), ("flags", "<u4")])
+assert NODE_DTYPE.itemsize == 120
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class GravParams(ctypes.Structure):
+    """sqo_grav_params (oracle/shenqi_oracle.h)"""
+    _fields_ = [("BoxSize", c_dbl), ("Nmesh", c_int), ("Asmth", c_dbl), ("G", c_dbl), ("ErrTolForceAcc", c_dbl),
+                ("BHOpeningAngle", c_dbl), ("MaxBHOpeningAngle", c_dbl), ("TreeUseBH", c_int), ("TreeRcut", c_dbl),
+                ("GravitySoftening", c_dbl), ("WindowType", c_int), ("rho0", c_dbl), ("update_potential", c_int)]
+
+
+def default_params(box, nmesh, npart, **kw):
+    p = dict(BoxSize=box, Nmesh=nmesh, Asmth=1.5, G=43.0071, ErrTolForceAcc=0.002, BHOpeningAngle=0.175,
+             MaxBHOpeningAngle=0.9, TreeUseBH=0, TreeRcut=6.0, GravitySoftening=(box / round(npart ** (1 / 3.))) / 30.,
+             WindowType=1, rho0=1.0, update_potential=0)
+    p.update(kw)
+    return p
+
+
+def build_oracle():
+    if not os.path.exists(ORACLE_SO):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "libshenqi_oracle.so"])
+
+
+_oracle = None
+def oracle():
+    global _oracle
+    if _oracle is None:
+        build_oracle()
+        L = ctypes.CDLL(ORACLE_SO)
+        L.sqo_peano_hilbert_key.restype = ctypes.c_uint64
+        L.sqo_tree_build.restype = c_i64
+        L.sqo_grav_short_tree.restype = c_i64
+        _oracle = L
+    return _oracle
+
+
+_ref = None
+def ref():
+    """The reference's own code (oracle/_ref); None when it was not built (no /root/reference at build time)."""
+    global _ref
+    if _ref is None:
+        if not os.path.exists(REF_SO):
+            return None
+        L = ctypes.CDLL(REF_SO)
+        L.ref_init()
+        L.ref_peano_hilbert_key.restype = ctypes.c_uint64
+        for f in ("ref_sort_particles", "ref_grav_short_tree", "ref_grav_short_pair", "ref_force_softening"):
+            getattr(L, f).restype = c_dbl
+        for f in ("ref_tree_build", "ref_tree_firstnode", "ref_tree_numnodes", "ref_grav_count_interactions", "ref_num_particles"):
+            getattr(L, f).restype = c_i64
+        _ref = L
+    return _ref
+
+
+# ----------------------------------------------------------------------------- oracle wrappers
+def o_keys(pos, box):
+    keys = np.zeros(len(pos), np.uint64)
+    oracle().sqo_peano_keys(ptr(pos), c_i64(len(pos)), c_dbl(box), ptr(keys))
+    return keys
+
+
+def o_sort(keys, types=None):
+    perm = np.zeros(len(keys), np.int64)
+    oracle().sqo_sort_order(ptr(keys), ptr(types), c_i64(len(keys)), ptr(perm))
+    return perm
+
+
+def o_tree(pos, mass, box, firstnode=None, factor=1.5):
+    n = len(pos)
+    firstnode = n if firstnode is None else firstnode
+    maxnodes = int(factor * n) + 64
+    nodes = np.zeros(maxnodes, NODE_DTYPE)
+    nn = oracle().sqo_tree_build(ptr(pos), ptr(mass), c_i64(n), c_dbl(box), ptr(nodes), c_i64(maxnodes), c_i64(firstnode))
+    assert nn > 0, "oracle tree build ran out of nodes"
+    return nodes[:nn].copy(), firstnode
+
+
+def o_walk(nodes, firstnode, pos, mass, oldacc, par, active=None, want_pot=False):
+    n = len(pos)
+    P = GravParams(**par)
+    acc = np.zeros((n, 3)); pot = np.zeros(n) if want_pot else None; cnt = np.zeros(n, np.int64)
+    act = None if active is None else np.ascontiguousarray(active, np.int32)
+    tot = oracle().sqo_grav_short_tree(ptr(nodes), c_i64(firstnode), ptr(pos), ptr(mass), ptr(oldacc), ptr(act),
+                                       c_i64(n if act is None else len(act)), ctypes.byref(P), ptr(acc), ptr(pot), ptr(cnt))
+    return acc, pot, cnt, tot
+
+
+def o_pair(pos, mass, par, want_pot=False):
+    n = len(pos)
+    P = GravParams(**par)
+    acc = np.zeros((n, 3)); pot = np.zeros(n) if want_pot else None
+    oracle().sqo_grav_short_pair(ptr(pos), ptr(mass), c_i64(n), ctypes.byref(P), ptr(acc), ptr(pot))
+    return acc, pot
+
+
+def o_cic_paint(pos, mass, box, nmesh):
+    mesh = np.zeros((nmesh, nmesh, nmesh))
+    oracle().sqo_cic_paint(ptr(pos), ptr(mass), c_i64(len(pos)), c_dbl(box), c_int(nmesh), ptr(mesh))
+    return mesh
+
+
+def o_cic_readout(mesh, pos, box, nmesh):
+    out = np.zeros(len(pos))
+    mesh = np.ascontiguousarray(mesh)
+    oracle().sqo_cic_readout(ptr(mesh), ptr(pos), c_i64(len(pos)), c_dbl(box), c_int(nmesh), ptr(out))
+    return out
+
+
+def o_pm_force(pos, mass, box, nmesh, asmth, G):
+    """Whole PM step restated: paint -> rfftn -> transfer -> irfftn (unnormalised, heFFTe scale::none,
+    libgadget/petapm.cpp:54,66) -> readout.  Returns (potential, accel[N,3])."""
+    mesh = o_cic_paint(pos, mass, box, nmesh)
+    rho_k = np.ascontiguousarray(np.fft.rfftn(mesh))
+    outs = [np.zeros_like(rho_k) for _ in range(4)]
+    oracle().sqo_pm_transfer(ptr(rho_k), c_int(nmesh), c_dbl(box), c_dbl(asmth), c_dbl(G), *[ptr(o) for o in outs])
+    res = []
+    for o in outs:
+        real = np.fft.irfftn(o, s=(nmesh,) * 3) * float(nmesh) ** 3
+        res.append(o_cic_readout(real, pos, box, nmesh))
+    return res[0], np.stack(res[1:], 1)
+
+
+# ----------------------------------------------------------------------------- reference wrappers
+def r_load(pos, mass, box, ids=None):
+    R = ref()
+    ids = None if ids is None else np.ascontiguousarray(ids, np.uint64)
+    R.ref_set_particles(ptr(pos), ptr(mass), ptr(ids), None, c_i64(len(pos)), c_dbl(box))
+
+
+def r_sorted_particles():
+    R = ref(); n = R.ref_num_particles()
+    pos = np.zeros((n, 3)); mass = np.zeros(n, np.float32); ids = np.zeros(n, np.uint64)
+    R.ref_get_particles(ptr(pos), ptr(mass), ptr(ids), None, None)
+    return pos, mass, ids
+
+
+def r_tree(factor=0.9):
+    R = ref()
+    secs = c_dbl()
+    nn = R.ref_tree_build(c_dbl(factor), ctypes.byref(secs))
+    nodes = np.zeros(nn, NODE_DTYPE)
+    R.ref_tree_copy_nodes(ptr(nodes))
+    return nodes, R.ref_tree_firstnode(), secs.value
+
+
+def _r_args(par, meansep):
+    return [c_int(par["Nmesh"]), c_dbl(par["Asmth"]), c_dbl(par["G"]), c_dbl(par["ErrTolForceAcc"]), c_dbl(par["BHOpeningAngle"]),
+            c_dbl(par["MaxBHOpeningAngle"]), c_int(par["TreeUseBH"]), c_dbl(par["TreeRcut"]), c_dbl(par["GravitySoftening"] / meansep),
+            c_dbl(meansep), c_int(par["WindowType"])]
+
+
+def r_walk(par, meansep, fulltree=None, gravpm=None):
+    R = ref(); n = R.ref_num_particles()
+    if fulltree is not None or gravpm is not None:
+        R.ref_set_accels(ptr(fulltree), ptr(gravpm))
+    acc = np.zeros((n, 3))
+    secs = R.ref_grav_short_tree(*_r_args(par, meansep), c_dbl(par["rho0"]), ptr(acc))
+    return acc, secs
+
+
+def r_counts(par, meansep):
+    R = ref(); n = R.ref_num_particles()
+    cnt = np.zeros(n, np.int64)
+    tot = R.ref_grav_count_interactions(*_r_args(par, meansep), ptr(cnt))
+    return cnt, tot
+
+
+def r_pair(par, meansep):
+    R = ref(); n = R.ref_num_particles()
+    acc = np.zeros((n, 3))
+    secs = R.ref_grav_short_pair(c_int(par["Nmesh"]), c_dbl(par["Asmth"]), c_dbl(par["G"]), c_dbl(par["TreeRcut"]),
+                                 c_dbl(par["GravitySoftening"] / meansep), c_dbl(meansep), c_int(par["WindowType"]),
+                                 c_dbl(par["rho0"]), ptr(acc))
+    return acc, secs
+
+
+# ----------------------------------------------------------------------------- canonical tree form
+def canonical_tree(nodes, firstnode, ids, box):
+    """Node numbering and leaf-slot order are not canonical in the reference (thread caches, merge order),
+    so compare the set of cells instead: for every node reachable from the root
+       (level, ix, iy, iz, ChildType, TopLevel, InternalTopLevel, nparticles)   sorted,
+    and for every leaf particle (level, ix, iy, iz, ID) sorted; plus per-cell (mass, cofm) in cell order."""
+    N = nodes
+    rootlen = N["len"][0]; corner = N["center"][0] - rootlen / 2
+    frontier = np.array([0], np.int64)
+    cells, parts, moms = [], [], []
+    while len(frontier):
+        nd = N[frontier]
+        level = np.rint(np.log2(rootlen / nd["len"])).astype(np.int64)
+        ijk = np.floor((nd["center"] - corner) / nd["len"][:, None]).astype(np.int64)
+        ctype = (nd["flags"] >> 3) & 3
+        top = (nd["flags"] >> 1) & 1; itop = nd["flags"] & 1
+        isleaf = ctype == 0
+        nocc = np.where(isleaf, nd["noccupied"], 0)
+        cells.append(np.stack([level, ijk[:, 0], ijk[:, 1], ijk[:, 2], ctype, top, itop, nocc], 1))
+        moms.append(np.concatenate([nd["mass"][:, None], nd["cofm"]], 1))
+        lf = np.nonzero(isleaf)[0]
+        for j in range(8):
+            sel = lf[nd["noccupied"][lf] > j]
+            if len(sel):
+                pid = ids[nd["suns"][sel, j]].astype(np.int64)
+                parts.append(np.stack([level[sel], ijk[sel, 0], ijk[sel, 1], ijk[sel, 2], pid], 1))
+        inner = nd[ctype == 1]
+        ch = inner["suns"].reshape(-1)
+        frontier = ch[ch >= 0].astype(np.int64) - firstnode
+    cells = np.concatenate(cells); moms = np.concatenate(moms)
+    order = np.lexsort(cells[:, 3::-1].T)
+    parts = np.concatenate(parts) if parts else np.zeros((0, 5), np.int64)
+    porder = np.lexsort(parts[:, ::-1].T)
+    return cells[order], parts[porder], moms[order]
+
+
+# ----------------------------------------------------------------------------- synthetic particle sets
+def random_clustered(n, box, seed=0):
+    """3-component set of libgadget/tests/test_forcetree.cpp:404-430 (uniform + two clumps)."""
+    rng = np.random.default_rng(seed)
+    pos = np.zeros((n, 3))
+    a, b = n // 4, 3 * n // 4
+    pos[:a] = box * rng.random((a, 3))
+    pos[a:b] = box / 2 + box / 8 * np.exp((rng.random((b - a, 3)) - 0.5) ** 2)
+    pos[b:] = box * 0.1 + box / 32 * np.exp((rng.random((n - b, 3)) - 0.5) ** 2)
+    return pos
+
+
+def lattice(ncbrt, box):
+    i = np.arange(ncbrt ** 3)
+    return np.stack([(box / ncbrt) * (i // ncbrt // ncbrt), (box / ncbrt) * ((i // ncbrt) % ncbrt), (box / ncbrt) * (i % ncbrt)], 1).astype(np.float64)
+
+
+def rel_err(a, b):
+    return np.linalg.norm(a - b, axis=1) / np.maximum(np.linalg.norm(b, axis=1), 1e-300)
