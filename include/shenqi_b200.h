@@ -1,0 +1,153 @@
+/* shenqi_b200 - B200-native (sm_100a) short-range TreePM gravity for MP-Gadget/shenqi.
+ *
+ * Thin C ABI underneath the reference's C++ entry points.  Plain pointers and
+ * sizes only; no exceptions cross this boundary; every call returns SQ_OK or a negative error code
+ * and sq_last_error() holds the message.  One context per process / GPU.  All calls are made from
+ * one host thread; the library is multi-stream inside.  The caller keeps ownership of every host
+ * array; the library owns its device pools.  There is NO CPU fallback: without a CUDA device
+ * sq_ctx_create fails with SQ_ERR_NO_DEVICE.
+ *
+ * Reference interfaces each entry point stands behind (paths under MP-Gadget/shenqi):
+ *   sq_set_params            set_gravshort_treepar / gravshort_set_softenings / gravpm_init_periodic
+ *                            (libgadget/gravity.h:64-80, libgadget/gravshort-tree2.cpp:78-122)
+ *   sq_upload_particles_aos  reads struct particle_data in place (libgadget/partmanager.h:9-71)
+ *   sq_ph_sort               PEANO() + slots_gc_sorted (libgadget/utils/peano.h:15, slotsmanager.cpp:419)
+ *   sq_tree_build            force_tree_full / force_tree_active_moments (libgadget/forcetree.h:127-140)
+ *   sq_tree_export_nodes     the struct NODE image other modules walk (libgadget/forcetree.h:38-66)
+ *   sq_tree_walk             grav_short_tree (libgadget/gravity.h:89, gravshort-tree2.cpp:141)
+ *   sq_pm_force              gravpm_force -> petapm_force (libgadget/gravity.h:86, petapm.cpp:472)
+ */
+#ifndef SHENQI_B200_H
+#define SHENQI_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SQ_OK 0
+#define SQ_ERR_NO_DEVICE (-1)     /* no CUDA device / wrong architecture: there is no CPU path */
+#define SQ_ERR_CUDA (-2)          /* a CUDA runtime or cuFFT call failed */
+#define SQ_ERR_ARG (-3)           /* bad argument or call order */
+#define SQ_ERR_NODE_POOL (-4)     /* tree needs more nodes than the pool holds even after growth (TreeAllocFactor > 3, forcetree.cpp:215-231) */
+#define SQ_ERR_TREE_DEPTH (-5)    /* more than 8 particles share one 2^-21 cell */
+#define SQ_ERR_MASS (-6)          /* a particle with Mass <= 0 (forcetree.cpp:808) */
+
+typedef struct sq_ctx sq_ctx;
+
+/* Knobs of the path: parameter-file names in comments (gadget/params.cpp:29-33, 84-104, 161-165). */
+typedef struct sq_params {
+    double BoxSize;            /* BoxSize */
+    int Nmesh;                 /* Nmesh */
+    double Asmth;              /* Asmth (1.5) */
+    double G;                  /* Newton's constant, internal units */
+    double ErrTolForceAcc;     /* ErrTolForceAcc (0.002) */
+    double BHOpeningAngle;     /* BHOpeningAngle (0.175) */
+    double MaxBHOpeningAngle;  /* MaxBHOpeningAngle (0.9) */
+    int TreeUseBH;             /* TreeUseBH: 0 relative criterion, >0 Barnes-Hut; >1 = BH for the first call only */
+    double TreeRcut;           /* TreeRcut (6), in units of Asmth*cellsize */
+    double GravitySoftening;   /* comoving Plummer-equivalent softening length epsilon (FORCE_SOFTENING() = 2.8 epsilon) */
+    int WindowType;            /* ShortRangeForceWindowType: 1 exact (table), 2 erfc */
+    double rho0;               /* Omega0 * rho_crit, for the potential self term */
+    double TreeAllocFactor;    /* node pool = factor * N (+ growth x1.15 up to 3.0); 0 -> 0.9 (run.cpp:257) */
+} sq_params;
+
+/* Byte offsets into the caller's array-of-structs particle record (defaults = struct particle_data). */
+typedef struct sq_aos_layout {
+    size_t stride;             /* 160 */
+    size_t off_pos;            /* 0   double[3] */
+    size_t off_mass;           /* 28  float */
+    size_t off_flags;          /* 36  bit0 IsGarbage, bit1 Swallowed; byte +3 = Type */
+    size_t off_fulltreegravaccel; /* 64 double[3] */
+    size_t off_gravpm;         /* 88  double[3] */
+    size_t off_id;             /* 136 uint64 */
+    size_t off_potential;      /* 152 double */
+} sq_aos_layout;
+
+typedef struct sq_walk_stats {
+    int64_t ntargets;          /* active particles walked */
+    int64_t ngroups;           /* warps' worth of targets */
+    int64_t interactions;      /* (target, source) pairs evaluated = the reference's ninteractions */
+    int64_t list_entries;      /* shared interaction-list entries evaluated (x group width = lane slots issued) */
+    int64_t nodes_tested;      /* (node, group) opening evaluations */
+    double  kernel_ms;         /* device time of the walk kernel (CUDA events) */
+} sq_walk_stats;
+
+typedef struct sq_tree_info {
+    int64_t numnodes;          /* nodes created */
+    int64_t numparticles;      /* particles in the tree */
+    int64_t maxnodes;          /* pool size used */
+    int     maxlevel;          /* deepest level (root = 0) */
+    int     geo_mismatch;      /* 1 if some particle's geometric octants differ from its key digits (handled) */
+} sq_tree_info;
+
+const char * sq_last_error(void);
+const char * sq_version(void);
+
+int sq_ctx_create(sq_ctx ** ctx, int device);
+void sq_ctx_destroy(sq_ctx * ctx);
+int sq_set_params(sq_ctx * ctx, const sq_params * par);
+int sq_sync(sq_ctx * ctx);
+
+/* ---- particles ------------------------------------------------------------------------------- */
+void sq_default_aos_layout(sq_aos_layout * lay);
+/* Copy the fields the path needs out of the caller's AoS (host memory). */
+int sq_upload_particles_aos(sq_ctx * ctx, const void * base, int64_t n, const sq_aos_layout * lay);
+/* Same from separate host arrays; ids/types/oldacc may be NULL (ids = i+1, type 1, oldacc 0). */
+int sq_upload_particles_soa(sq_ctx * ctx, const double * pos, const float * mass, const uint64_t * ids,
+                            const unsigned char * types, int64_t n);
+/* |FullTreeGravAccel + GravPM| / G per particle, in upload order (gravshort2.hpp:111-121); host arrays N x 3. */
+int sq_set_old_accel(sq_ctx * ctx, const double * fulltreegravaccel, const double * gravpm);
+/* Directly: oldacc[i] in upload order. */
+int sq_set_oldacc(sq_ctx * ctx, const double * oldacc);
+
+/* ---- Peano-Hilbert keys + sort (slots_gc_sorted) --------------------------------------------- */
+/* Keys, stable radix sort by (TypeKey, Key), gather into PH order on the device. */
+int sq_ph_sort(sq_ctx * ctx);
+/* keys in upload order (before sort) */
+int sq_get_keys(sq_ctx * ctx, uint64_t * keys);
+/* sorted keys, and perm[i] = upload index of the particle at sorted position i */
+int sq_get_sorted(sq_ctx * ctx, uint64_t * sorted_keys, int32_t * perm);
+
+/* ---- force tree ------------------------------------------------------------------------------ */
+/* Build the oct-tree (leaf capacity 8, root 1.001*Box) and monopole moments from the sorted
+ * particles.  active: upload-order indices of the particles to put in the tree, or NULL for all
+ * (force_tree_active_moments vs force_tree_full). */
+int sq_tree_build(sq_ctx * ctx, const int32_t * active, int64_t nactive, sq_tree_info * info);
+/* Write the tree as the reference's NODE[numnodes] image (120 B each), node numbers starting at
+ * firstnode, particle numbers = sorted positions (or upload indices if upload_order != 0). */
+int sq_tree_export_nodes(sq_ctx * ctx, void * nodes, int64_t firstnode, int upload_order);
+
+/* ---- short-range walk -------------------------------------------------------------------------- */
+/* accel: N x 3 host doubles in upload order (already x G), written for active particles only.
+ * potential: N host doubles or NULL; written only when the tree holds all particles
+ * (full_particle_tree_flag), including the self terms of gravshort2.hpp:95-106.
+ * TreeUseBH > 1 is reset to 0 after the call (gravshort-tree2.cpp:170-171). */
+int sq_tree_walk(sq_ctx * ctx, const int32_t * active, int64_t nactive, double * accel, double * potential,
+                 sq_walk_stats * stats);
+/* Same, results left on the device (benchmark / chained use); fetch with sq_download_accel. */
+int sq_tree_walk_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
+int sq_download_accel(sq_ctx * ctx, double * accel, double * potential);
+
+/* ---- particle mesh --------------------------------------------------------------------------- */
+/* CIC paint -> r2c FFT -> potential + 3 force transfer functions -> 4 c2r FFTs -> fused CIC readout.
+ * gravpm: N x 3 host doubles (upload order); potential: N doubles or NULL (PM part only, added to nothing). */
+int sq_pm_force(sq_ctx * ctx, double * gravpm, double * potential);
+int sq_pm_force_device(sq_ctx * ctx);
+/* stages, for tests: density mesh Nmesh^3 (z fastest) after paint */
+int sq_pm_paint(sq_ctx * ctx);
+int sq_pm_get_mesh(sq_ctx * ctx, double * mesh);
+
+/* ---- timing of the last device stages (CUDA events on the launching stream), milliseconds ------ */
+typedef struct sq_timings {
+    double keys_ms, sort_ms, gather_ms, tree_build_ms, tree_moments_ms, walk_ms;
+    double pm_paint_ms, pm_fft_ms, pm_transfer_ms, pm_readout_ms;
+    int64_t kernel_launches;   /* kernels of this library launched since sq_reset_timings */
+} sq_timings;
+int sq_get_timings(sq_ctx * ctx, sq_timings * t);
+int sq_reset_timings(sq_ctx * ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

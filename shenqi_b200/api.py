@@ -1,0 +1,227 @@
+"""ctypes binding of include/shenqi_b200.h, shaped after the reference's entry points
+(slots_gc_sorted, force_tree_full / force_tree_active_moments, grav_short_tree, gravpm_force)."""
+import ctypes
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+c_i64, c_dbl, c_int = ctypes.c_int64, ctypes.c_double, ctypes.c_int
+
+# struct NODE, libgadget/forcetree.h:38-66 (120 B)
+NODE_DTYPE = np.dtype([("sibling", "<i4"), ("father", "<i4"), ("len", "<f8"), ("center", "<f8", 3),
+                       ("cofm", "<f8", 3), ("mass", "<f8"), ("hmax", "<f8"), ("suns", "<i4", 8),
+                       ("noccupied", "<i4"), ("flags", "<u4")])
+# struct particle_data, libgadget/partmanager.h:9-71 (160 B, LOW_PRECISION=double, non-DEBUG)
+PARTICLE_DTYPE = np.dtype({"names": ["Pos", "TopLeaf", "Mass", "PI", "flags", "TimeBinHydro", "TimeBinGravity", "Type",
+                                     "Vel", "FullTreeGravAccel", "GravPM", "Ti_drift", "Hsml", "DtHsml", "ID", "GrNr", "Potential"],
+                           "formats": [("<f8", 3), "<i4", "<f4", "<i4", "u1", "u1", "u1", "u1",
+                                       ("<f8", 3), ("<f8", 3), ("<f8", 3), "<i8", "<f8", "<f8", "<u8", "<i8", "<f8"],
+                           "offsets": [0, 24, 28, 32, 36, 37, 38, 39, 40, 64, 88, 112, 120, 128, 136, 144, 152],
+                           "itemsize": 160})
+
+
+class ShenqiError(RuntimeError):
+    pass
+
+
+class Params(ctypes.Structure):
+    """sq_params: the parameter-file knobs that reach the path (gadget/params.cpp:29-33, 84-104, 161-165)."""
+    _fields_ = [("BoxSize", c_dbl), ("Nmesh", c_int), ("Asmth", c_dbl), ("G", c_dbl), ("ErrTolForceAcc", c_dbl),
+                ("BHOpeningAngle", c_dbl), ("MaxBHOpeningAngle", c_dbl), ("TreeUseBH", c_int), ("TreeRcut", c_dbl),
+                ("GravitySoftening", c_dbl), ("WindowType", c_int), ("rho0", c_dbl), ("TreeAllocFactor", c_dbl)]
+
+    @classmethod
+    def defaults(cls, BoxSize, Nmesh, GravitySoftening, **kw):
+        p = cls(BoxSize=BoxSize, Nmesh=Nmesh, Asmth=1.5, G=43.0071, ErrTolForceAcc=0.002, BHOpeningAngle=0.175,
+                MaxBHOpeningAngle=0.9, TreeUseBH=2, TreeRcut=6.0, GravitySoftening=GravitySoftening, WindowType=1,
+                rho0=1.0, TreeAllocFactor=0.9)
+        for k, v in kw.items():
+            if not hasattr(p, k):
+                raise KeyError(k)
+            setattr(p, k, v)
+        return p
+
+
+class AosLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_size_t) for n in ("stride", "off_pos", "off_mass", "off_flags", "off_fulltreegravaccel",
+                                               "off_gravpm", "off_id", "off_potential")]
+
+
+class WalkStats(ctypes.Structure):
+    _fields_ = [("ntargets", c_i64), ("ngroups", c_i64), ("interactions", c_i64), ("list_entries", c_i64),
+                ("nodes_tested", c_i64), ("kernel_ms", c_dbl)]
+
+
+class TreeInfo(ctypes.Structure):
+    _fields_ = [("numnodes", c_i64), ("numparticles", c_i64), ("maxnodes", c_i64), ("maxlevel", c_int), ("geo_mismatch", c_int)]
+
+
+class Timings(ctypes.Structure):
+    _fields_ = [(n, c_dbl) for n in ("keys_ms", "sort_ms", "gather_ms", "tree_build_ms", "tree_moments_ms", "walk_ms",
+                                     "pm_paint_ms", "pm_fft_ms", "pm_transfer_ms", "pm_readout_ms")] + [("kernel_launches", c_i64)]
+
+
+EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_sync", "sq_default_aos_layout",
+           "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
+           "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
+           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings"]
+
+
+def library_path():
+    return os.path.join(_HERE, "libshenqi_b200.so")
+
+
+_lib = None
+def load_library():
+    """Load libshenqi_b200.so.  Raises (loudly) if it has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise ShenqiError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(or make -C shenqi_b200/csrc). shenqi_b200 has no CPU fallback." % path)
+        L = ctypes.CDLL(path)
+        L.sq_last_error.restype = ctypes.c_char_p
+        L.sq_version.restype = ctypes.c_char_p
+        L.sq_ctx_destroy.restype = None
+        L.sq_default_aos_layout.restype = None
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Context:
+    """One GPU context (sq_ctx).  Method names follow the reference functions they stand behind."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        self._ctx = ctypes.c_void_p()
+        self._check(self.L.sq_ctx_create(ctypes.byref(self._ctx), c_int(device)))
+        self.n = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            raise ShenqiError("shenqi_b200 error %d: %s" % (rc, self.L.sq_last_error().decode()))
+
+    def close(self):
+        if self._ctx:
+            self.L.sq_ctx_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters: set_gravshort_treepar / gravshort_set_softenings / gravpm_init_periodic
+    def set_params(self, params):
+        self.params = params
+        self._check(self.L.sq_set_params(self._ctx, ctypes.byref(params)))
+
+    # ---- particles
+    def upload_particles(self, pos, mass, types=None):
+        pos = np.ascontiguousarray(pos, np.float64); mass = np.ascontiguousarray(mass, np.float32)
+        assert pos.shape == (len(mass), 3)
+        types = None if types is None else np.ascontiguousarray(types, np.uint8)
+        self.n = len(mass)
+        self._check(self.L.sq_upload_particles_soa(self._ctx, _p(pos), _p(mass), None, _p(types), c_i64(self.n)))
+
+    def upload_particle_data(self, parts):
+        """parts: numpy array with PARTICLE_DTYPE (the reference's struct particle_data, read in place)."""
+        assert parts.dtype.itemsize == 160 and parts.flags.c_contiguous
+        self.n = len(parts)
+        self._check(self.L.sq_upload_particles_aos(self._ctx, _p(parts), c_i64(self.n), None))
+
+    def set_old_accel(self, fulltreegravaccel=None, gravpm=None):
+        a = None if fulltreegravaccel is None else np.ascontiguousarray(fulltreegravaccel, np.float64)
+        b = None if gravpm is None else np.ascontiguousarray(gravpm, np.float64)
+        self._check(self.L.sq_set_old_accel(self._ctx, _p(a), _p(b)))
+
+    def set_oldacc(self, oldacc):
+        a = np.ascontiguousarray(oldacc, np.float64)
+        assert len(a) == self.n
+        self._check(self.L.sq_set_oldacc(self._ctx, _p(a)))
+
+    # ---- PEANO + slots_gc_sorted
+    def ph_sort(self):
+        self._check(self.L.sq_ph_sort(self._ctx))
+
+    def keys(self):
+        k = np.zeros(self.n, np.uint64)
+        self._check(self.L.sq_get_keys(self._ctx, _p(k)))
+        return k
+
+    def sorted_keys_perm(self):
+        k = np.zeros(self.n, np.uint64); perm = np.zeros(self.n, np.int32)
+        self._check(self.L.sq_get_sorted(self._ctx, _p(k), _p(perm)))
+        return k, perm
+
+    # ---- force_tree_full (active=None) / force_tree_active_moments
+    def tree_build(self, active=None):
+        info = TreeInfo()
+        act = None if active is None else np.ascontiguousarray(active, np.int32)
+        self._check(self.L.sq_tree_build(self._ctx, _p(act), c_i64(0 if act is None else len(act)), ctypes.byref(info)))
+        self.tree_info = info
+        return info
+
+    def tree_nodes(self, firstnode=None, upload_order=False):
+        """The tree as the reference's NODE[] image."""
+        firstnode = self.n if firstnode is None else firstnode
+        nodes = np.zeros(self.tree_info.numnodes, NODE_DTYPE)
+        self._check(self.L.sq_tree_export_nodes(self._ctx, _p(nodes), c_i64(firstnode), c_int(1 if upload_order else 0)))
+        return nodes, firstnode
+
+    # ---- grav_short_tree
+    def grav_short_tree(self, active=None, accel=None, potential=None):
+        """Returns (accel[N,3] x G, potential[N] or None, WalkStats). accel/potential in upload order;
+        entries of inactive particles are left as passed in."""
+        st = WalkStats()
+        act = None if active is None else np.ascontiguousarray(active, np.int32)
+        accel = np.zeros((self.n, 3)) if accel is None else accel
+        potential = np.zeros(self.n) if potential is None else potential
+        self._check(self.L.sq_tree_walk(self._ctx, _p(act), c_i64(0 if act is None else len(act)), _p(accel), _p(potential), ctypes.byref(st)))
+        return accel, potential, st
+
+    def grav_short_tree_device(self, active=None):
+        st = WalkStats()
+        act = None if active is None else np.ascontiguousarray(active, np.int32)
+        self._check(self.L.sq_tree_walk_device(self._ctx, _p(act), c_i64(0 if act is None else len(act)), ctypes.byref(st)))
+        return st
+
+    def download_accel(self):
+        accel = np.zeros((self.n, 3)); pot = np.zeros(self.n)
+        self._check(self.L.sq_download_accel(self._ctx, _p(accel), _p(pot)))
+        return accel, pot
+
+    # ---- gravpm_force
+    def gravpm_force(self):
+        gravpm = np.zeros((self.n, 3)); pot = np.zeros(self.n)
+        self._check(self.L.sq_pm_force(self._ctx, _p(gravpm), _p(pot)))
+        return gravpm, pot
+
+    def gravpm_force_device(self):
+        self._check(self.L.sq_pm_force_device(self._ctx))
+
+    def pm_paint(self):
+        self._check(self.L.sq_pm_paint(self._ctx))
+        n = self.params.Nmesh
+        mesh = np.zeros((n, n, n))
+        self._check(self.L.sq_pm_get_mesh(self._ctx, _p(mesh)))
+        return mesh
+
+    def timings(self):
+        t = Timings()
+        self._check(self.L.sq_get_timings(self._ctx, ctypes.byref(t)))
+        return t
+
+    def reset_timings(self):
+        self._check(self.L.sq_reset_timings(self._ctx))
+
+    def set_group_width(self, g):
+        """Targets per warp in the walk (32, 16 or 8): tuning knob."""
+        assert g in (8, 16, 32)
+        ctypes.c_int.in_dll(self.L, "sq_walk_group_width").value = g

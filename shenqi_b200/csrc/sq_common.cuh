@@ -1,0 +1,158 @@
+// shenqi_b200 internal header: context, device buffers, error plumbing, warp helpers.
+// sm_100a only.  No Thrust/CUB, no CPU fallback.
+#pragma once
+#include <cuda_runtime.h>
+#include <cufft.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/shenqi_b200.h"
+
+#define SQ_WARP 32
+#define SQ_FULL 0xffffffffu
+#define SQ_NMAXCHILD 8            /* libgadget/forcetree.h:13 */
+#define SQ_NODEFULL (1 << 16)     /* libgadget/forcetree.h:14 */
+#define SQ_MAXLEVEL 21            /* BITS_PER_DIMENSION, libgadget/utils/peano.h:9 */
+#define SQ_NTAB 512               /* NGRAVTAB, libgadget/gravity.h:35 */
+
+void sq_set_error(const char * fmt, ...);
+
+#define SQ_CUDA(call)                                                                         \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if(e_ != cudaSuccess) {                                                               \
+            sq_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return SQ_ERR_CUDA;                                                               \
+        }                                                                                     \
+    } while(0)
+
+#define SQ_CUFFT(call)                                                                        \
+    do {                                                                                      \
+        cufftResult r_ = (call);                                                              \
+        if(r_ != CUFFT_SUCCESS) {                                                             \
+            sq_set_error("%s:%d: %s -> cufft error %d", __FILE__, __LINE__, #call, (int) r_); \
+            return SQ_ERR_CUDA;                                                               \
+        }                                                                                     \
+    } while(0)
+
+#define SQ_TRY(call) do { int rc_ = (call); if(rc_ != SQ_OK) return rc_; } while(0)
+
+// Growable device buffer owned by the context (the library owns its device pools).
+struct sq_buf {
+    void * p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if(bytes <= cap) return SQ_OK;
+        if(p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 16 + 256;
+        SQ_CUDA(cudaMalloc(&p, want));
+        cap = want;
+        return SQ_OK;
+    }
+    void release() { if(p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T * as() const { return (T *) p; }
+};
+
+// Packed device node, three 128-bit-aligned streams (DESIGN.md "data layout"):
+//   cm[i]  = {cofm.x, cofm.y, cofm.z, mass}      32 B   (two 128-bit loads)
+//   cl[i]  = {center.x, center.y, center.z, len}  32 B
+//   lk[i]  = {first, count, sibling, info}        16 B   (one 128-bit load)
+//     internal node: first = index of first child, count = number of children (contiguous, Morton order)
+//     leaf:          first = first particle (tree order), count = particles (<= 8)
+//     info = level | type << 8 | toplevel << 12 | internaltop << 13 | dependslocal << 14 | octant << 16
+struct sq_tree_dev {
+    double4 * cm = nullptr;
+    double4 * cl = nullptr;
+    int4 * lk = nullptr;
+    int * parent = nullptr;
+    unsigned char * rot = nullptr;   // Peano-Hilbert orientation of the node's cell
+};
+#define SQ_INFO_LEVEL(i) ((i) & 0xff)
+#define SQ_INFO_TYPE(i) (((i) >> 8) & 3)      /* 0 particle node, 1 node node, 2 pseudo */
+#define SQ_INFO_TOP(i) (((i) >> 12) & 1)
+#define SQ_INFO_ITOP(i) (((i) >> 13) & 1)
+#define SQ_INFO_LOCAL(i) (((i) >> 14) & 1)
+#define SQ_INFO_OCT(i) (((i) >> 16) & 7)
+
+struct sq_ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[16] = {};
+    sq_params par = {};
+    bool have_params = false;
+    int64_t kernel_launches = 0;
+    sq_timings tm = {};
+
+    // ---- particles, upload order
+    int64_t n = 0;
+    sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in;
+    bool have_types = false;
+    // ---- particles, PH-sorted order
+    sq_buf pos, mass, oldacc, keys, perm, rank;   // perm[sorted] = upload idx; rank[upload] = sorted pos
+    sq_buf sort_tmp_keys, sort_tmp_vals, sort_hist, scan_tmp, flag_tmp;
+    bool sorted = false;
+    int geo_mismatch = 0;
+
+    // ---- tree
+    sq_buf t_cm, t_cl, t_lk, t_parent, t_rot, t_lvl, t_counters;
+    sq_buf tree_keys, tree_order, tree_pos, tree_mass;   // only when the tree order differs from particle order
+    sq_buf active_sorted;            // sorted positions of the active set the tree was built from
+    int64_t tree_np = 0;             // particles in the tree
+    int64_t tree_maxnodes = 0, tree_numnodes = 0;
+    int tree_maxlevel = 0;
+    int lvl_start[SQ_MAXLEVEL + 3] = {};
+    bool tree_built = false, tree_full = false, tree_identity = true;
+
+    // ---- walk
+    sq_buf w_accel, w_pot, w_stats, w_targets, w_table, w_out_accel, w_out_pot, w_counter;
+    bool walk_done = false;
+    int64_t walk_ntargets = 0;
+
+    // ---- PM
+    sq_buf pm_real[4], pm_cplx[4], pm_out;
+    cufftHandle plan_r2c = 0, plan_c2r = 0;
+    int plan_nmesh = 0;
+    bool pm_done = false;
+};
+
+static inline int sq_div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned sq_lane() { return threadIdx.x & 31; }
+__device__ __forceinline__ unsigned sq_lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
+
+__device__ __forceinline__ int sq_warp_excl_scan(int v, int & total)
+{
+    int x = v;
+    #pragma unroll
+    for(int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(SQ_FULL, x, o);
+        if((int) sq_lane() >= o) x += y;
+    }
+    total = __shfl_sync(SQ_FULL, x, 31);
+    return x - v;
+}
+// libgadget/partmanager.h:99, evaluated exactly as the macro does
+__device__ __forceinline__ double sq_nearest(double x, double box, double half)
+{
+    return (x > half) ? (x - box) : ((x < -half) ? (x + box) : x);
+}
+#endif
+
+// stage entry points (implemented in the .cu files)
+int sq_keys_run(sq_ctx * c);
+int sq_geokeys_run(sq_ctx * c, const double * pos, int64_t n, uint64_t * gkeys);
+int sq_sort_pairs(sq_ctx * c, uint64_t * keys, uint32_t * vals, int64_t n, int begin_bit, int end_bit);
+int sq_exclusive_scan_u32(sq_ctx * c, uint32_t * data, int64_t n, uint32_t * total_out_dev);
+int sq_gather_run(sq_ctx * c);
+int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_buf * out, int64_t * count);
+int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_info * info);
+int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order);
+int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
+int sq_pm_run(sq_ctx * c, bool paint_only);
+void sq_pm_destroy(sq_ctx * c);

@@ -1,0 +1,341 @@
+"""GPU parity tests: every stage of the CUDA path, called through the C ABI, against the CPU oracle
+(oracle/libshenqi_oracle.so, pinned to the reference in test_oracle.py) and, when it travelled with the
+snapshot, against the reference's own code (oracle/_ref/libshenqi_ref.so)."""
+import numpy as np
+import pytest
+from helpers import (oracle, ref, o_keys, o_sort, o_tree, o_walk, o_pair, o_cic_paint, o_pm_force, canonical_tree,
+                     random_clustered, lattice, rel_err, default_params, r_load, r_sorted_particles, r_tree, r_walk, ptr,
+                     c_i64, c_dbl)
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN_KEYS = np.load(__import__("os").path.join(__import__("os").path.dirname(__file__), "golden", "peano_keys_4x4x4.npy"))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import shenqi_b200 as sq
+    c = sq.Context(0)
+    yield c
+    c.close()
+
+
+def make_params(box, nmesh, n, **kw):
+    import shenqi_b200 as sq
+    soft = (box / round(n ** (1 / 3.))) / 30.
+    return sq.Params.defaults(box, nmesh, soft, **kw)
+
+
+def to_oracle_par(P, update_potential=0):
+    return dict(BoxSize=P.BoxSize, Nmesh=P.Nmesh, Asmth=P.Asmth, G=P.G, ErrTolForceAcc=P.ErrTolForceAcc, BHOpeningAngle=P.BHOpeningAngle,
+                MaxBHOpeningAngle=P.MaxBHOpeningAngle, TreeUseBH=P.TreeUseBH, TreeRcut=P.TreeRcut, GravitySoftening=P.GravitySoftening,
+                WindowType=P.WindowType, rho0=P.rho0, update_potential=update_potential)
+
+
+def zeldovich_like(ng, box, amp, seed):
+    rng = np.random.default_rng(seed)
+    return np.mod(lattice(ng, box) + 0.5 * box / ng + amp * (box / ng) * rng.standard_normal((ng ** 3, 3)), box)
+
+
+# ------------------------------------------------------------------------------------------ keys
+def test_keys_golden(ctx):
+    """libgadget/tests/test_peano.cpp:102-117: 4^3 lattice in a box of 4."""
+    i = np.arange(64)
+    pos = np.stack([i % 4, (i // 4) % 4, (i // 16) % 4], 1).astype(np.float64)
+    ctx.set_params(make_params(4.0, 8, 64))
+    ctx.upload_particles(pos, np.ones(64, np.float32))
+    ctx.ph_sort()
+    assert np.array_equal(ctx.keys(), GOLDEN_KEYS)
+
+
+@pytest.mark.parametrize("n,box,seed", [(1, 8.0, 0), (33, 8.0, 1), (3072, 8.0, 2), (3073, 100.0, 3), (200000, 256000.0, 4)])
+def test_keys_and_sort_bit_exact(ctx, n, box, seed):
+    pos = random_clustered(n, box, seed) if n > 100 else np.random.default_rng(seed).random((n, 3)) * box
+    ctx.set_params(make_params(box, 64, max(n, 8)))
+    ctx.upload_particles(pos, np.ones(n, np.float32))
+    ctx.ph_sort()
+    k = o_keys(pos, box)
+    assert np.array_equal(ctx.keys(), k)
+    sk, perm = ctx.sorted_keys_perm()
+    operm = o_sort(k)
+    assert np.array_equal(sk, k[operm])
+    assert np.array_equal(perm.astype(np.int64), operm)      # ties broken by upload index
+
+
+def test_sort_ties_and_edges(ctx):
+    """many identical keys (stability), sortedness, permutation is a bijection."""
+    n = 50000
+    rng = np.random.default_rng(7)
+    pos = np.floor(rng.random((n, 3)) * 6) * (8.0 / 6) + 0.01
+    ctx.set_params(make_params(8.0, 32, n))
+    ctx.upload_particles(pos, np.ones(n, np.float32))
+    ctx.ph_sort()
+    sk, perm = ctx.sorted_keys_perm()
+    assert (np.diff(sk.astype(np.int64)) >= 0).all()
+    assert np.array_equal(np.sort(perm), np.arange(n))
+    assert np.array_equal(perm.astype(np.int64), o_sort(o_keys(pos, 8.0)))
+
+
+def test_empty(ctx):
+    ctx.set_params(make_params(8.0, 16, 8))
+    ctx.upload_particles(np.zeros((0, 3)), np.zeros(0, np.float32))
+    ctx.ph_sort()
+    info = ctx.tree_build()
+    assert info.numnodes == 1 and info.numparticles == 0
+
+
+# ------------------------------------------------------------------------------------------ tree
+def check_tree(ctx, pos, mass, box):
+    n = len(pos)
+    ctx.upload_particles(pos, mass)
+    ctx.ph_sort()
+    info = ctx.tree_build()
+    nodes, first = ctx.tree_nodes(firstnode=n, upload_order=True)
+    ids = np.arange(n)
+    perm = o_sort(o_keys(pos, box))
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    on, ofirst = o_tree(spos, smass, box)
+    cg = canonical_tree(nodes, first, ids, box)
+    co = canonical_tree(on, ofirst, perm, box)
+    assert info.numnodes == len(cg[0]), "every device node is reachable (no empty children are created)"
+    assert np.array_equal(cg[0], co[0]), "cells differ"
+    assert np.array_equal(cg[1], co[1]), "leaf membership differs"
+    scale = np.abs(co[2]).max(axis=0)
+    assert (np.abs(cg[2] - co[2]) / scale).max() < 1e-12
+    # NODE image details: centres and lengths are bit-identical for matching cells
+    return info, nodes, first
+
+
+@pytest.mark.parametrize("kind", ["random", "close", "lattice", "zeldovich", "tiny"])
+def test_tree_topology(ctx, kind):
+    """cases of libgadget/tests/test_forcetree.cpp:339-455 (lattice / 1:5000 clustered / random 3-component)."""
+    box = 8.0
+    if kind == "random":
+        pos = random_clustered(32 ** 3, box, 0)
+    elif kind == "close":
+        nc = 24; i = np.arange(nc ** 3)
+        pos = np.stack([4. + (i // nc // nc) / 5000., 4. + ((i // nc) % nc) / 5000., 4. + (i % nc) / 5000.], 1)
+    elif kind == "lattice":
+        pos = lattice(32, box)          # particles exactly on cell faces: geometric octants != key digits
+    elif kind == "zeldovich":
+        pos = zeldovich_like(32, box, 0.2, 3)
+    else:
+        pos = np.random.default_rng(5).random((9, 3)) * box
+    n = len(pos)
+    mass = (1 + np.random.default_rng(11).random(n)).astype(np.float32)
+    ctx.set_params(make_params(box, 64, n))
+    info, nodes, first = check_tree(ctx, pos, mass, box)
+    if kind == "lattice":
+        assert info.geo_mismatch == 1
+    # invariants of libgadget/tests/test_forcetree.cpp:21-169
+    root = nodes[0]
+    assert abs(root["mass"] - mass.astype(np.float64).sum()) < 1e-9 * mass.sum()
+    assert root["len"] == box * 1.001 and root["father"] == -1 and root["sibling"] == -1
+    inner = nodes[((nodes["flags"] >> 3) & 3) == 1]
+    assert (inner["noccupied"] == 1 << 16).all()
+    leaves = nodes[((nodes["flags"] >> 3) & 3) == 0]
+    assert leaves["noccupied"].sum() == n and (leaves["noccupied"] <= 8).all()
+
+
+def test_tree_node_image_links(ctx):
+    """sibling / father / suns links of the exported NODE image walk like the reference's (gravshort2.hpp:227-322)."""
+    box = 8.0; n = 20000
+    pos = random_clustered(n, box, 9); mass = np.ones(n, np.float32)
+    ctx.set_params(make_params(box, 48, n))
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    nodes, first = ctx.tree_nodes(firstnode=n, upload_order=True)
+    # DFS via suns[0]/sibling must visit every node once and every particle once
+    seen = 0; parts = []
+    no = first
+    while no >= 0:
+        nd = nodes[no - first]; seen += 1
+        if ((nd["flags"] >> 3) & 3) == 1:
+            ch = nd["suns"][nd["suns"] >= 0]
+            assert (nodes["father"][ch - first] == no).all()
+            no = nd["suns"][0]
+        else:
+            parts.extend(nd["suns"][:nd["noccupied"]].tolist())
+            no = nd["sibling"]
+    assert seen == len(nodes)
+    assert sorted(parts) == list(range(n))
+    # the oracle's walk over OUR node image gives the oracle's accelerations
+    par = to_oracle_par(make_params(box, 48, n, TreeUseBH=1))
+    a1, _, c1, _ = o_walk(nodes, first, pos, mass, np.zeros(n), par)
+    perm = o_sort(o_keys(pos, box))
+    on, ofirst = o_tree(np.ascontiguousarray(pos[perm]), mass, box)
+    a2, _, c2, _ = o_walk(on, ofirst, np.ascontiguousarray(pos[perm]), mass, np.zeros(n), par)
+    assert np.array_equal(c1[perm], c2)
+    assert rel_err(a1[perm], a2).max() < 1e-12
+
+
+# ------------------------------------------------------------------------------------------ walk
+def oracle_walk_for(pos, mass, box, P, oldacc, want_pot=False):
+    perm = o_sort(o_keys(pos, box))
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    on, ofirst = o_tree(spos, smass, box)
+    acc, pot, cnt, tot = o_walk(on, ofirst, spos, smass, np.ascontiguousarray(oldacc[perm]), to_oracle_par(P, 1 if want_pot else 0), want_pot=want_pot)
+    inv = np.empty_like(perm); inv[perm] = np.arange(len(perm))
+    return acc[inv], (None if pot is None else pot[inv]), cnt[inv], tot
+
+
+def assert_accel_parity(a, a_ref):
+    """BASELINE.json: median relative error <= 1e-5, 99.9th percentile <= 1e-4."""
+    e = rel_err(a, a_ref)
+    med, p999 = np.median(e), np.percentile(e, 99.9)
+    assert med <= 1e-5 and p999 <= 1e-4, "median %.3g p99.9 %.3g max %.3g" % (med, p999, e.max())
+    return med, p999
+
+
+@pytest.mark.parametrize("kind,width", [("random", 32), ("random", 16), ("random", 8), ("zeldovich", 32), ("close", 32)])
+def test_walk_parity(ctx, kind, width):
+    """Two calls like libgadget/tests/test_gravity.cpp:237-240: Barnes-Hut first, then the relative criterion
+    with the first call's accelerations as |a_old|.  Interaction counts must equal the oracle's exactly
+    (every per-particle opening decision is the reference's)."""
+    box = 8.0
+    if kind == "random":
+        pos = random_clustered(16 ** 3 * 4, box, 1)
+    elif kind == "zeldovich":
+        pos = zeldovich_like(24, box, 0.15, 2)
+    else:
+        nc = 16; i = np.arange(nc ** 3)
+        pos = np.stack([4. + (i // nc // nc) / 5000., 4. + ((i // nc) % nc) / 5000., 4. + (i % nc) / 5000.], 1)
+    n = len(pos)
+    mass = np.ones(n, np.float32)
+    P = make_params(box, 48, n, TreeUseBH=2, TreeRcut=7.0)
+    ctx.set_group_width(width)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    a1, p1, st1 = ctx.grav_short_tree()
+    o1, op1, oc1, ot1 = oracle_walk_for(pos, mass, box, P, np.zeros(n), want_pot=True)
+    assert st1.interactions == ot1
+    assert_accel_parity(a1, o1)
+    assert np.median(np.abs(p1 - op1) / np.abs(op1)) < 1e-5
+    # second call: relative criterion
+    P2 = make_params(box, 48, n, TreeUseBH=0, TreeRcut=7.0)
+    ctx.set_params(P2)
+    ctx.set_old_accel(o1, None)
+    a2, p2, st2 = ctx.grav_short_tree()
+    oldacc = np.linalg.norm(o1, axis=1) / P.G
+    o2, _, oc2, ot2 = oracle_walk_for(pos, mass, box, P2, oldacc)
+    assert st2.interactions == ot2
+    assert_accel_parity(a2, o2)
+    ctx.set_group_width(32)
+
+
+def test_walk_vs_pair_same_error_distribution(ctx):
+    """BASELINE.json: ours and the reference must show the same error distribution against the gravshort-pair direct sum."""
+    box = 8.0; n = 16 ** 3
+    pos = random_clustered(n, box, 4); mass = np.ones(n, np.float32)
+    P = make_params(box, 48, n, TreeUseBH=1, TreeRcut=7.0)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    a, _, _ = ctx.grav_short_tree()
+    o, _, _, _ = oracle_walk_for(pos, mass, box, P, np.zeros(n))
+    pa, _ = o_pair(pos, mass, to_oracle_par(P))
+    e_ours, e_ref = rel_err(a, pa), rel_err(o, pa)
+    assert abs(e_ours.mean() - e_ref.mean()) < 0.02 * e_ref.mean() + 1e-7
+    assert abs(e_ours.max() - e_ref.max()) < 0.05 * e_ref.max() + 1e-6
+    # two-sample KS distance between the error distributions
+    grid = np.sort(np.concatenate([e_ours, e_ref]))
+    ks = np.abs(np.searchsorted(np.sort(e_ours), grid, side="right") - np.searchsorted(np.sort(e_ref), grid, side="right")).max() / n
+    assert ks < 0.02
+
+
+def test_walk_active_subset(ctx):
+    """hierarchical stepping: tree of the active particles only, walked by them (timestep.cpp:291-300)."""
+    box = 8.0; n = 30000
+    pos = random_clustered(n, box, 6); mass = np.ones(n, np.float32)
+    rng = np.random.default_rng(3)
+    active = np.sort(rng.choice(n, n // 5, replace=False)).astype(np.int32)
+    P = make_params(box, 48, n, TreeUseBH=1, TreeRcut=7.0)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    info = ctx.tree_build(active)
+    assert info.numparticles == len(active)
+    acc_in = np.full((n, 3), -7.0)
+    a, _, st = ctx.grav_short_tree(active, accel=acc_in)
+    sub = np.ascontiguousarray(pos[active])
+    o, _, _, ot = oracle_walk_for(sub, mass[active], box, P, np.zeros(len(active)))
+    assert st.interactions == ot
+    assert_accel_parity(a[active], o)
+    untouched = np.setdiff1d(np.arange(n), active)
+    assert (a[untouched] == -7.0).all()
+
+
+@pytest.mark.skipif(ref() is None, reason="reference build (oracle/_ref) did not travel")
+def test_walk_against_reference_build(ctx):
+    """the reference's own grav_short_tree (compiled from /root/reference into oracle/_ref) on the same particles."""
+    box = 8.0; n = 20 ** 3
+    pos = random_clustered(n, box, 8); mass = np.ones(n, np.float32)
+    P = make_params(box, 48, n, TreeUseBH=2, TreeRcut=7.0)
+    ids = np.arange(1, n + 1, dtype=np.uint64)
+    r_load(pos, mass, box, ids); ref().ref_sort_particles()
+    _, _, rids = r_sorted_particles()
+    r_tree(0.9)
+    ra, _ = r_walk(to_oracle_par(P), box / 20)
+    ra_upload = np.zeros_like(ra); ra_upload[rids.astype(np.int64) - 1] = ra
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    a, _, _ = ctx.grav_short_tree()
+    assert_accel_parity(a, ra_upload)
+
+
+# ------------------------------------------------------------------------------------------ PM
+def test_cic_paint(ctx):
+    box = 8.0; n = 40000; nmesh = 32
+    pos = random_clustered(n, box, 2); mass = (1 + np.random.default_rng(1).random(n)).astype(np.float32)
+    ctx.set_params(make_params(box, nmesh, n))
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    mesh = ctx.pm_paint()
+    om = o_cic_paint(pos, mass, box, nmesh)
+    assert abs(mesh.sum() - mass.astype(np.float64).sum()) < 1e-9 * mass.sum()          # mass conservation
+    assert np.abs(mesh - om).max() < 1e-11 * om.max()
+
+
+def test_pm_force(ctx):
+    box = 8.0; n = 16 ** 3; nmesh = 48
+    pos = random_clustered(n, box, 3); mass = np.ones(n, np.float32)
+    P = make_params(box, nmesh, n)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    gpm, pot = ctx.gravpm_force()
+    opot, oacc = o_pm_force(pos, mass, box, nmesh, P.Asmth, P.G)
+    s = np.abs(oacc).max()
+    assert np.abs(gpm - oacc).max() < 1e-10 * s
+    assert np.abs(pot - opot).max() < 1e-10 * np.abs(opot).max()
+
+
+def test_tree_plus_pm_vs_direct_sum(ctx):
+    """libgadget/tests/test_gravity.cpp:155-169 acceptance: PM + tree vs periodic direct sum, maxerr < 3 ErrTol, mean < 0.8 ErrTol."""
+    box = 8.0; n = 16 ** 3; nmesh = 48; G = 43.0071
+    pos = random_clustered(n, box, 0); mass = np.ones(n, np.float32)
+    P = make_params(box, nmesh, n, TreeUseBH=2, TreeRcut=7.0)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    gpm, _ = ctx.gravpm_force()
+    ctx.tree_build()
+    a1, _, _ = ctx.grav_short_tree()
+    ctx.set_old_accel(a1, gpm)
+    a2, _, _ = ctx.grav_short_tree()          # TreeUseBH was 2 -> relative criterion now
+    total = a2 + gpm
+    # periodic direct sum over 27 images (test_gravity.cpp:133-153), softened
+    h = 2.8 * P.GravitySoftening
+    direct = np.zeros((n, 3))
+    for sx in (-1, 0, 1):
+        for sy in (-1, 0, 1):
+            for sz in (-1, 0, 1):
+                off = np.array([sx, sy, sz]) * box
+                for i0 in range(0, n, 512):
+                    d = off[None, None, :] + pos[i0:i0 + 512, None, :] - pos[None, :, :]
+                    r2 = (d ** 2).sum(-1); r = np.sqrt(r2)
+                    with np.errstate(divide="ignore", invalid="ignore"):
+                        fac = 1 / (r2 * r)
+                        u = r / h
+                        f1 = (10.666666666667 + u * u * (32.0 * u - 38.4)) / h ** 3
+                        f2 = (21.333333333333 - 48.0 * u + 38.4 * u * u - 10.666666666667 * u ** 3 - 0.066666666667 / u ** 3) / h ** 3
+                    fac = np.where(r < h, np.where(u < 0.5, f1, f2), fac)
+                    fac[r2 == 0] = 0
+                    direct[i0:i0 + 512] += -(d * fac[..., None]).sum(1) * G
+    meanacc = np.abs(direct).mean()
+    err = np.abs(direct - total) / meanacc
+    assert err.max() < 3 * 0.002 and err.mean() < 0.8 * 0.002, (err.max(), err.mean())
