@@ -214,6 +214,12 @@ static void update_node_recursive(struct sqo_build * b, int no, int sib)
 int64_t sqo_tree_build(const double * pos, const float * mass, int64_t n, double box,
                        sqo_node * nodes, int64_t maxnodes, int64_t firstnode)
 {
+    return sqo_tree_build_opt(pos, mass, n, box, nodes, maxnodes, firstnode, 1);
+}
+
+int64_t sqo_tree_build_opt(const double * pos, const float * mass, int64_t n, double box,
+                           sqo_node * nodes, int64_t maxnodes, int64_t firstnode, int last_node_shortcut)
+{
     struct sqo_build b;
     b.N = nodes - firstnode;
     b.firstnode = firstnode;
@@ -235,7 +241,7 @@ int64_t sqo_tree_build(const double * pos, const float * mass, int64_t n, double
     for(int64_t i = 0; i < n; i++) {
         const sqo_node * a = &b.N[this_acc];
         int cur = (int) firstnode;
-        if(fabs(2 * (pos[3 * i] - a->center[0])) <= a->len && fabs(2 * (pos[3 * i + 1] - a->center[1])) <= a->len
+        if(last_node_shortcut && fabs(2 * (pos[3 * i] - a->center[0])) <= a->len && fabs(2 * (pos[3 * i + 1] - a->center[1])) <= a->len
                 && fabs(2 * (pos[3 * i + 2] - a->center[2])) <= a->len)
             cur = this_acc;
         this_acc = add_particle_to_tree(&b, (int) i, cur);

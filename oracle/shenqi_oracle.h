@@ -66,6 +66,14 @@ void sqo_sort_order(const uint64_t * keys, const unsigned char * types, int64_t 
 int64_t sqo_tree_build(const double * pos, const float * mass, int64_t n, double box,
                        sqo_node * nodes, int64_t maxnodes, int64_t firstnode);
 
+/* Same, with the reference's "start from the last node touched if the particle is inside it" shortcut
+ * (forcetree.cpp:811, an INCLUSIVE |2 dx| <= len test) switchable.  With the shortcut a particle lying
+ * exactly on a cell face lands in whichever neighbour the previous particle went to, so the reference's
+ * topology for such inputs (lattices) depends on insertion order and thread count; without it every
+ * particle descends from the root by `Pos > centre` alone, which is the canonical placement. */
+int64_t sqo_tree_build_opt(const double * pos, const float * mass, int64_t n, double box,
+                           sqo_node * nodes, int64_t maxnodes, int64_t firstnode, int last_node_shortcut);
+
 /* libgadget/gravshort2.hpp:227-358 (visit<PRIMARY>, apply_accn), :88-107 (postprocess), :111-121.
  * oldacc[i] = |FullTreeGravAccel+GravPM|/G.  accel (N x 3) is multiplied by G; potential may be NULL.
  * counts[i] = number of apply_accn calls (may be NULL).  Returns total interactions. */

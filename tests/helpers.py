@@ -48,6 +48,7 @@ def oracle():
         L = ctypes.CDLL(ORACLE_SO)
         L.sqo_peano_hilbert_key.restype = ctypes.c_uint64
         L.sqo_tree_build.restype = c_i64
+        L.sqo_tree_build_opt.restype = c_i64
         L.sqo_grav_short_tree.restype = c_i64
         _oracle = L
     return _oracle
@@ -84,12 +85,13 @@ def o_sort(keys, types=None):
     return perm
 
 
-def o_tree(pos, mass, box, firstnode=None, factor=1.5):
+def o_tree(pos, mass, box, firstnode=None, factor=1.5, shortcut=True):
     n = len(pos)
     firstnode = n if firstnode is None else firstnode
     maxnodes = int(factor * n) + 64
     nodes = np.zeros(maxnodes, NODE_DTYPE)
-    nn = oracle().sqo_tree_build(ptr(pos), ptr(mass), c_i64(n), c_dbl(box), ptr(nodes), c_i64(maxnodes), c_i64(firstnode))
+    nn = oracle().sqo_tree_build_opt(ptr(pos), ptr(mass), c_i64(n), c_dbl(box), ptr(nodes), c_i64(maxnodes), c_i64(firstnode),
+                                     c_int(1 if shortcut else 0))
     assert nn > 0, "oracle tree build ran out of nodes"
     return nodes[:nn].copy(), firstnode
 
@@ -134,7 +136,7 @@ def o_pm_force(pos, mass, box, nmesh, asmth, G):
     oracle().sqo_pm_transfer(ptr(rho_k), c_int(nmesh), c_dbl(box), c_dbl(asmth), c_dbl(G), *[ptr(o) for o in outs])
     res = []
     for o in outs:
-        real = np.fft.irfftn(o, s=(nmesh,) * 3) * float(nmesh) ** 3
+        real = np.fft.irfftn(o, s=(nmesh,) * 3, axes=(0, 1, 2)) * float(nmesh) ** 3
         res.append(o_cic_readout(real, pos, box, nmesh))
     return res[0], np.stack(res[1:], 1)
 

@@ -85,7 +85,7 @@ def test_empty(ctx):
 
 
 # ------------------------------------------------------------------------------------------ tree
-def check_tree(ctx, pos, mass, box):
+def check_tree(ctx, pos, mass, box, shortcut=True):
     n = len(pos)
     ctx.upload_particles(pos, mass)
     ctx.ph_sort()
@@ -94,7 +94,7 @@ def check_tree(ctx, pos, mass, box):
     ids = np.arange(n)
     perm = o_sort(o_keys(pos, box))
     spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
-    on, ofirst = o_tree(spos, smass, box)
+    on, ofirst = o_tree(spos, smass, box, shortcut=shortcut)
     cg = canonical_tree(nodes, first, ids, box)
     co = canonical_tree(on, ofirst, perm, box)
     assert info.numnodes == len(cg[0]), "every device node is reachable (no empty children are created)"
@@ -124,7 +124,9 @@ def test_tree_topology(ctx, kind):
     n = len(pos)
     mass = (1 + np.random.default_rng(11).random(n)).astype(np.float32)
     ctx.set_params(make_params(box, 64, n))
-    info, nodes, first = check_tree(ctx, pos, mass, box)
+    # particles exactly on cell faces: the reference's placement depends on insertion history (forcetree.cpp:811);
+    # compare those inputs against the canonical root descent (oracle header, sqo_tree_build_opt)
+    info, nodes, first = check_tree(ctx, pos, mass, box, shortcut=kind not in ("close", "lattice"))
     if kind == "lattice":
         assert info.geo_mismatch == 1
     # invariants of libgadget/tests/test_forcetree.cpp:21-169
@@ -169,10 +171,10 @@ def test_tree_node_image_links(ctx):
 
 
 # ------------------------------------------------------------------------------------------ walk
-def oracle_walk_for(pos, mass, box, P, oldacc, want_pot=False):
+def oracle_walk_for(pos, mass, box, P, oldacc, want_pot=False, shortcut=True):
     perm = o_sort(o_keys(pos, box))
     spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
-    on, ofirst = o_tree(spos, smass, box)
+    on, ofirst = o_tree(spos, smass, box, shortcut=shortcut)
     acc, pot, cnt, tot = o_walk(on, ofirst, spos, smass, np.ascontiguousarray(oldacc[perm]), to_oracle_par(P, 1 if want_pot else 0), want_pot=want_pot)
     inv = np.empty_like(perm); inv[perm] = np.arange(len(perm))
     return acc[inv], (None if pot is None else pot[inv]), cnt[inv], tot
@@ -206,7 +208,8 @@ def test_walk_parity(ctx, kind, width):
     ctx.set_params(P)
     ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
     a1, p1, st1 = ctx.grav_short_tree()
-    o1, op1, oc1, ot1 = oracle_walk_for(pos, mass, box, P, np.zeros(n), want_pot=True)
+    sc = kind != "close"      # on-face particles: canonical placement (see test_tree_topology)
+    o1, op1, oc1, ot1 = oracle_walk_for(pos, mass, box, P, np.zeros(n), want_pot=True, shortcut=sc)
     assert st1.interactions == ot1
     assert_accel_parity(a1, o1)
     assert np.median(np.abs(p1 - op1) / np.abs(op1)) < 1e-5
@@ -216,7 +219,7 @@ def test_walk_parity(ctx, kind, width):
     ctx.set_old_accel(o1, None)
     a2, p2, st2 = ctx.grav_short_tree()
     oldacc = np.linalg.norm(o1, axis=1) / P.G
-    o2, _, oc2, ot2 = oracle_walk_for(pos, mass, box, P2, oldacc)
+    o2, _, oc2, ot2 = oracle_walk_for(pos, mass, box, P2, oldacc, shortcut=sc)
     assert st2.interactions == ot2
     assert_accel_parity(a2, o2)
     ctx.set_group_width(32)
@@ -338,4 +341,14 @@ def test_tree_plus_pm_vs_direct_sum(ctx):
                     direct[i0:i0 + 512] += -(d * fac[..., None]).sum(1) * G
     meanacc = np.abs(direct).mean()
     err = np.abs(direct - total) / meanacc
-    assert err.max() < 3 * 0.002 and err.mean() < 0.8 * 0.002, (err.max(), err.mean())
+    # the same metric for the CPU oracle (reference algorithm) on the same particles
+    opot, ogpm = o_pm_force(pos, mass, box, nmesh, P.Asmth, G)
+    P1 = make_params(box, nmesh, n, TreeUseBH=1, TreeRcut=7.0)
+    o1, _, _, _ = oracle_walk_for(pos, mass, box, P1, np.zeros(n))
+    P2 = make_params(box, nmesh, n, TreeUseBH=0, TreeRcut=7.0)
+    o2, _, _, _ = oracle_walk_for(pos, mass, box, P2, np.linalg.norm(o1 + ogpm, axis=1) / G)
+    oerr = np.abs(direct - (o2 + ogpm)) / meanacc
+    assert abs(err.max() - oerr.max()) < 1e-3 * oerr.max() and abs(err.mean() - oerr.mean()) < 1e-3 * oerr.mean()
+    # for this particle set the reference algorithm itself reaches max 0.023 / mean 0.0025 of the mean acceleration
+    # (the test_gravity.cpp:165-166 bounds 3 ErrTol / 0.8 ErrTol are for its own mt19937 sample); sanity bounds:
+    assert err.max() < 0.05 and err.mean() < 0.005, (err.max(), err.mean())
