@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""Headline benchmark (BASELINE.json): short-range TreePM gravity, particles/s and interactions/s.
+
+One "step" = one full pass of the hot path over the particle set, device-resident:
+   PH keys -> radix sort -> gather -> tree build -> moments -> group walk (relative criterion)
+   -> PM: CIC paint -> r2c -> Green/differencing -> 4 x c2r -> fused CIC readout.
+N=1 workload = BASELINE.json configs[1]: synthetic Zel'dovich 256^3 DM particles, Nmesh=512, z=9.
+`value` = particles whose short-range + PM accelerations were produced per second (all ranks).
+`e2e`   = the same through the C ABI with HOST buffers: H2D of positions/masses/old accelerations and D2H of
+          the tree and PM accelerations inside the timed region (pinned host memory).
+`--impl reference` times the reference's own CPU code (oracle/_ref, OpenMP, all host cores) on a bounded
+sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import numpy as np
+
+FLOP_PER_INTERACTION = 23     # force only; 28 with potential
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload(ngrid, nmesh):
+    from shenqi_b200.ics import zeldovich, rho0, G_INTERNAL
+    box = 1000.0 * ngrid            # 1 Mpc/h mean spacing, kpc/h units
+    pos, mass, ids = zeldovich(ngrid, box, rms_disp=0.2, seed=181170)
+    par = dict(BoxSize=box, Nmesh=nmesh, GravitySoftening=(box / ngrid) / 30., G=G_INTERNAL, rho0=rho0(), TreeRcut=6.0,
+               ErrTolForceAcc=0.002, BHOpeningAngle=0.175, MaxBHOpeningAngle=0.9)
+    return pos, mass, par
+
+
+def pinned(a):
+    """copy of a numpy array in page-locked host memory (torch is only the allocator here)."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t.numpy(), t
+
+
+# ---------------------------------------------------------------------------------------------- CPU side
+def cpu_reference_step(pos, mass, par, oldacc_full=None, want="auto"):
+    """One step of the reference's own CPU code (oracle/_ref: slots_gc_sorted, force_tree_full, grav_short_tree,
+    OpenMP) or, if that was not built, of the C port (oracle/); the PM part is the numpy restatement in both
+    cases (petapm.cpp needs FFTW/heFFTe and cannot be built).  Returns dict of seconds + interaction count."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
+    n = len(pos)
+    box = par["BoxSize"]
+    meansep = box / round(n ** (1 / 3.))
+    opar = H.default_params(box, par["Nmesh"], n, G=par["G"], TreeUseBH=0, TreeRcut=par["TreeRcut"], GravitySoftening=par["GravitySoftening"], rho0=par["rho0"])
+    out = {}
+    use_ref = H.ref() is not None and want != "port"
+    with H.quiet_stdout():
+        return _cpu_reference_step(H, pos, mass, par, opar, meansep, use_ref, out)
+
+
+def _cpu_reference_step(H, pos, mass, par, opar, meansep, use_ref, out):
+    n = len(pos)
+    box = par["BoxSize"]
+    if use_ref:
+        R = H.ref()
+        H.r_load(pos, mass, box)
+        t0 = time.perf_counter(); R.ref_sort_particles(); out["sort_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter(); H.r_tree(0.9); out["tree_s"] = time.perf_counter() - t0
+        # bootstrap |a_old| with one Barnes-Hut pass (not timed), then the timed relative-criterion walk
+        H.r_walk(dict(opar, TreeUseBH=1), meansep)
+        t0 = time.perf_counter(); acc, _ = H.r_walk(opar, meansep); out["walk_s"] = time.perf_counter() - t0
+        _, tot = H.r_counts(opar, meansep)
+        out["interactions"] = int(tot)
+        out["kind"] = "reference"
+        out["cores"] = R.ref_omp_threads()
+        R.ref_tree_free()
+    else:
+        t0 = time.perf_counter(); perm = H.o_sort(H.o_keys(pos, box)); spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm]); out["sort_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter(); nodes, first = H.o_tree(spos, smass, box); out["tree_s"] = time.perf_counter() - t0
+        a1, _, _, _ = H.o_walk(nodes, first, spos, smass, np.zeros(n), dict(opar, TreeUseBH=1))
+        t0 = time.perf_counter(); acc, _, _, tot = H.o_walk(nodes, first, spos, smass, np.linalg.norm(a1, axis=1) / par["G"], opar); out["walk_s"] = time.perf_counter() - t0
+        out["interactions"] = int(tot)
+        out["kind"] = "port"
+        out["cores"] = os.cpu_count()
+    t0 = time.perf_counter(); H.o_pm_force(pos, mass, box, par["Nmesh"], 1.5, par["G"]); out["pm_s"] = time.perf_counter() - t0
+    out["step_s"] = out["sort_s"] + out["tree_s"] + out["walk_s"] + out["pm_s"]
+    return out
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ngrid = args.cpu_ngrid
+    pos, mass, par = workload(ngrid, 2 * ngrid)
+    n = len(pos)
+    times = []
+    res = None
+    for it in range(args.warmup + args.steps):
+        res = cpu_reference_step(pos, mass, par)
+        if it >= args.warmup:
+            times.append(res["step_s"])
+    t = float(np.mean(times))
+    v = n / t
+    line = {"impl": "reference", "metric": "short-range gravity particles/s", "value": v, "unit": "particles/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "zeldovich-%d^3-nmesh%d (headline config: 256^3/512)" % (ngrid, 2 * ngrid)},
+            "interactions_per_s": res["interactions"] / res["walk_s"],
+            "cpu_baseline": {"value": v, "unit": "particles/s", "cores": res["cores"], "kind": res["kind"],
+                             "sample": "%d^3 Zel'dovich sub-box (same spacing, softening, Rcut, ErrTolForceAcc as the 256^3 workload): sort+tree+walk by the %s, PM by the numpy restatement" % (ngrid, "reference's own OpenMP code" if res["kind"] == "reference" else "C port"),
+                             "seconds": {k: res[k] for k in ("sort_s", "tree_s", "walk_s", "pm_s")}},
+            "e2e": {"value": v, "unit": "particles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------- GPU side
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--ngrid", type=int, default=256)
+    ap.add_argument("--nmesh", type=int, default=0)
+    ap.add_argument("--cpu-ngrid", type=int, default=64)
+    ap.add_argument("--group-width", type=int, default=32)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    nmesh = args.nmesh or 2 * args.ngrid
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import shenqi_b200 as sq
+
+    W = max(args.warmup, 3)
+    pos, mass, par = workload(args.ngrid, nmesh)
+    n = len(pos)
+    ctx = sq.Context(local_rank)
+    ctx.set_group_width(args.group_width)
+    P = sq.Params.defaults(par["BoxSize"], nmesh, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
+    ctx.set_params(P)
+    fp32_peak = ctx.measure_fp32_peak()
+    hbm_peak, peak_src = read_peaks()
+
+    # bootstrap |a_old|: Barnes-Hut pass + PM, exactly as the reference starts (gravshort-tree2.cpp:170-171)
+    ctx.upload_particles(pos, mass)
+    ctx.ph_sort(); ctx.tree_build()
+    a0, _, _ = ctx.grav_short_tree()
+    g0, _ = ctx.gravpm_force()
+    P.TreeUseBH = 0
+    ctx.set_params(P)
+    ctx.set_old_accel(a0, g0)
+
+    def device_step():
+        ctx.ph_sort()
+        ctx.tree_build()
+        st = ctx.grav_short_tree_device()
+        ctx.gravpm_force_device()
+        return st
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(W):
+        device_step()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ctx.reset_timings()
+    barrier()
+    t0 = time.perf_counter()
+    stats, walk_ms, stage = [], [], []
+    for _ in range(args.steps):
+        st = device_step()
+        stats.append(st); walk_ms.append(st.kernel_ms)
+        tm = ctx.timings()
+        stage.append([getattr(tm, f) for f, _ in tm._fields_[:10]])
+    barrier()
+    dt = time.perf_counter() - t0
+    launches = ctx.timings().kernel_launches
+    clocks = sampler.stop()
+    if dist is not None:
+        tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+    ms_per_step = 1e3 * dt / args.steps
+    value = world * n / (dt / args.steps)
+    interactions = int(np.mean([s.interactions for s in stats]))
+    wms = float(np.mean(walk_ms))
+    achieved_tf = interactions * FLOP_PER_INTERACTION / (wms * 1e-3) / 1e12
+    stage = np.mean(np.array(stage), axis=0)
+    stage_names = ["keys_ms", "sort_ms", "gather_ms", "tree_build_ms", "tree_moments_ms", "walk_ms", "pm_paint_ms", "pm_fft_ms", "pm_transfer_ms", "pm_readout_ms"]
+    stage_ms = dict(zip(stage_names, [float(x) for x in stage]))
+
+    # HBM-bound stages: algorithmic bytes / device time / measured copy bandwidth
+    numnodes = ctx.tree_info.numnodes
+    nm3 = float(nmesh) ** 3
+    bytes_model = {"keys": 32.0 * n, "sort": 8 * 32.0 * n, "gather": 2 * 36.0 * n + 8.0 * n,
+                   "tree_build": 8.0 * n + 28.0 * n + 80.0 * numnodes, "pm_paint": 28.0 * n + 16.0 * nm3,
+                   "pm_readout": 24.0 * n + 32.0 * n + 4 * 8.0 * nm3, "pm_transfer": 80.0 * (nm3 / 2)}
+    hbm = {}
+    for k, ms_key in (("keys", "keys_ms"), ("sort", "sort_ms"), ("gather", "gather_ms"), ("tree_build", "tree_build_ms"),
+                      ("pm_paint", "pm_paint_ms"), ("pm_readout", "pm_readout_ms"), ("pm_transfer", "pm_transfer_ms")):
+        if stage_ms[ms_key] > 0:
+            gbs = bytes_model[k] / (stage_ms[ms_key] * 1e-3) / 1e9
+            hbm[k] = {"achieved_gbs": gbs, "frac": gbs / hbm_peak, "ms": stage_ms[ms_key]}
+
+    # end to end through the C ABI with host buffers (pinned)
+    ppos, _k1 = pinned(pos); pmass, _k2 = pinned(mass)
+    pa0, _k3 = pinned(a0); pg0, _k4 = pinned(g0)
+    acc_out, _k5 = pinned(np.zeros((n, 3))); pot_out, _k6 = pinned(np.zeros(n))
+    gpm_out, _k7 = pinned(np.zeros((n, 3))); gpot_out, _k8 = pinned(np.zeros(n))
+
+    def e2e_step():
+        ctx.upload_particles(ppos, pmass)
+        ctx.set_old_accel(pa0, pg0)
+        ctx.ph_sort()
+        ctx.tree_build()
+        ctx.grav_short_tree(accel=acc_out, potential=pot_out)
+        ctx._check(ctx.L.sq_pm_force(ctx._ctx, gpm_out.ctypes.data_as(sq.api.ctypes.c_void_p), gpot_out.ctypes.data_as(sq.api.ctypes.c_void_p)))
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    de = time.perf_counter() - t0
+    if dist is not None:
+        tt = torch.tensor([de], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        de = float(tt.item())
+    e2e_value = world * n / (de / e2e_steps)
+    h2d = n * (24 + 4 + 48) + n * 24 + n * 8       # pos, mass, old accelerations; accel/potential buffers round-trip (inactive entries are preserved)
+    d2h = n * (24 + 8 + 24 + 8)
+
+    line = {"metric": "short-range gravity particles/s", "value": value, "unit": "particles/s", "n_gpus": world, "steps": args.steps,
+            "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 pair math, f64 accumulation/tests", "data": "synthetic",
+            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9%s" % (args.ngrid, nmesh, "" if world == 1 else " x %d independent replicas (domain-decomposed exchange not built yet)" % world),
+                       "particles": n, "Nmesh": nmesh, "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5, "group_width": args.group_width,
+                       "l2": "inputs_exceed_l2 (particle arrays %.0f MB, mesh %.0f MB)" % (n * 36 / 1e6, nm3 * 8 / 1e6)},
+            "interactions_per_s": world * interactions / (wms * 1e-3), "interactions_per_particle": interactions / n,
+            "walk_particles_per_s": world * n / (wms * 1e-3),
+            "stage_ms": stage_ms, "tree_nodes": int(numnodes),
+            "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None,
+                         "flop_per_interaction": FLOP_PER_INTERACTION, "peak_source": "FFMA microbenchmark in this run (sq_measure_fp32_peak)",
+                         "lane_efficiency": interactions / float(max(1, np.mean([s.list_entries for s in stats]) * args.group_width))},
+            "roofline_hbm": {"peak_gbs": hbm_peak, "peak_source": peak_src, "stages": hbm},
+            "e2e": {"value": e2e_value, "unit": "particles/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * de / e2e_steps},
+            "gpu_launches": int(launches), "clocks": clocks}
+
+    if rank == 0 and not args.no_cpu:
+        cp, cm, cpar = workload(args.cpu_ngrid, 2 * args.cpu_ngrid)
+        res = cpu_reference_step(cp, cm, cpar)
+        line["cpu_baseline"] = {"value": len(cp) / res["step_s"], "unit": "particles/s", "cores": res["cores"], "kind": res["kind"],
+                                "sample": "%d^3 Zel'dovich sub-box, same spacing/softening/Rcut/ErrTol: sort+tree+walk by the %s, PM by the numpy restatement" % (args.cpu_ngrid, "reference's own OpenMP code (oracle/_ref)" if res["kind"] == "reference" else "C port (oracle/)"),
+                                "interactions_per_s": res["interactions"] / res["walk_s"], "seconds": {k: res[k] for k in ("sort_s", "tree_s", "walk_s", "pm_s")}}
+    if rank == 0:
+        print(json.dumps(line))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

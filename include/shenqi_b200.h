@@ -146,6 +146,8 @@ typedef struct sq_timings {
 } sq_timings;
 int sq_get_timings(sq_ctx * ctx, sq_timings * t);
 int sq_reset_timings(sq_ctx * ctx);
+/* FFMA-pipe peak of this device in TFLOP/s (2 flop per FMA), measured: roofline denominator of the walk. */
+int sq_measure_fp32_peak(sq_ctx * ctx, double * tflops);
 
 #ifdef __cplusplus
 }

@@ -64,7 +64,7 @@ class Timings(ctypes.Structure):
 EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_sync", "sq_default_aos_layout",
            "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
-           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings"]
+           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak"]
 
 
 def library_path():
@@ -220,6 +220,11 @@ class Context:
 
     def reset_timings(self):
         self._check(self.L.sq_reset_timings(self._ctx))
+
+    def measure_fp32_peak(self):
+        t = c_dbl()
+        self._check(self.L.sq_measure_fp32_peak(self._ctx, ctypes.byref(t)))
+        return t.value
 
     def set_group_width(self, g):
         """Targets per warp in the walk (32, 16 or 8): tuning knob."""

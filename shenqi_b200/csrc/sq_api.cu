@@ -383,3 +383,44 @@ int sq_reset_timings(sq_ctx * c)
 }
 
 } /* extern "C" */
+
+// ------------------------------------------------------------------------------------ FP32 FMA peak probe
+// Roofline denominator for the interaction kernel (MEASURED_PEAKS.json has HBM and bf16 only):
+// 16 independent FFMA chains per thread, all SMs, 2 flop per FFMA.
+__global__ void __launch_bounds__(256) sq_ffma_probe_kernel(float * out, int iters, float a, float b)
+{
+    float x[16];
+    #pragma unroll
+    for(int k = 0; k < 16; k++) x[k] = (float) (threadIdx.x + k);
+    for(int it = 0; it < iters; it++) {
+        #pragma unroll
+        for(int k = 0; k < 16; k++) x[k] = fmaf(x[k], a, b);
+    }
+    float s = 0;
+    #pragma unroll
+    for(int k = 0; k < 16; k++) s += x[k];
+    if(s == 123.456f) out[0] = s;
+}
+
+extern "C" int sq_measure_fp32_peak(sq_ctx * c, double * tflops)
+{
+    if(!c || !tflops) return SQ_ERR_ARG;
+    sq_buf o;
+    SQ_TRY(o.reserve(64));
+    const int iters = 4096, blocks = c->num_sms * 8;
+    double best = 0;
+    for(int rep = 0; rep < 5; rep++) {
+        SQ_CUDA(cudaEventRecord(c->ev[0], c->stream));
+        sq_ffma_probe_kernel<<<blocks, 256, 0, c->stream>>>(o.as<float>(), iters, 1.0000001f, 1e-7f);
+        SQ_CUDA(cudaEventRecord(c->ev[1], c->stream));
+        SQ_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+        const double fl = 2.0 * 16.0 * iters * 256.0 * blocks;
+        const double t = fl / (ms * 1e-3) / 1e12;
+        if(rep > 0 && t > best) best = t;
+    }
+    o.release();
+    *tflops = best;
+    return SQ_OK;
+}

@@ -1,0 +1,48 @@
+"""Synthetic Zel'dovich initial conditions for the benchmarks.
+
+Lattice Ngrid^3 at (i,j,k)*Box/Ngrid (as libgenic/zeldovich.cpp:77-104), Gaussian random field with a fixed
+seed (181170, benchmarks/dm-50-512/paramfile.genic:20) and a power-law-with-cutoff spectrum, displacement
+psi_k = i k / k^2 delta_k (libgenic/zeldovich.cpp:292-314), normalised to a chosen rms displacement in units
+of the mean spacing (z = 9: ~0.2), positions wrapped into [0, Box), equal masses Omega0 rho_crit Box^3 / N.
+Pure numpy: host-side input generation, not part of the timed path."""
+import numpy as np
+
+G_INTERNAL = 43007.1          # kpc/h, 1e10 Msun/h, km/s
+HUBBLE = 0.1                  # 100 km/s/Mpc in internal units
+OMEGA0 = 0.2814               # benchmarks/dm-50-512/paramfile.genic
+
+
+def zeldovich(ngrid, box, rms_disp=0.2, seed=181170, index=-1.0):
+    """Returns pos[N,3] float64 in [0,box), mass[N] float32, ids[N] uint64 (i*Ng^2 + j*Ng + k + 1)."""
+    rng = np.random.default_rng(seed)
+    n = ngrid
+    delta = rng.standard_normal((n, n, n))
+    dk = np.fft.rfftn(delta)
+    del delta
+    kx = np.fft.fftfreq(n, 1.0 / n)[:, None, None]
+    ky = np.fft.fftfreq(n, 1.0 / n)[None, :, None]
+    kz = np.fft.rfftfreq(n, 1.0 / n)[None, None, :]
+    k2 = kx * kx + ky * ky + kz * kz
+    k2[0, 0, 0] = 1.0
+    amp = k2 ** (index / 4.0) * np.exp(-k2 / (0.25 * n) ** 2)     # sqrt(P(k)), P ~ k^index with a cutoff at Nyquist/2
+    amp[0, 0, 0] = 0.0
+    dk *= amp
+    disp = []
+    for kk in (kx, ky, kz):
+        disp.append(np.fft.irfftn(1j * kk / k2 * dk, s=(n, n, n), axes=(0, 1, 2)))
+    del dk
+    disp = np.stack([d.reshape(-1) for d in disp], 1)
+    disp *= rms_disp * (box / n) / np.sqrt((disp ** 2).sum(1).mean() / 3.0)
+    idx = np.arange(n ** 3)
+    pos = np.stack([idx // (n * n), (idx // n) % n, idx % n], 1).astype(np.float64) * (box / n)
+    pos += disp
+    np.mod(pos, box, out=pos)
+    pos[pos >= box] = 0.0
+    rho_crit = 3 * HUBBLE ** 2 / (8 * np.pi * G_INTERNAL)
+    mass = np.full(n ** 3, OMEGA0 * rho_crit * box ** 3 / n ** 3, np.float32)
+    ids = (idx + 1).astype(np.uint64)
+    return pos, mass, ids
+
+
+def rho0():
+    return OMEGA0 * 3 * HUBBLE ** 2 / (8 * np.pi * G_INTERNAL)

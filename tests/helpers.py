@@ -16,6 +16,24 @@ NODE_DTYPE = np.dtype([("sibling", "<i4"), ("father", "<i4"), ("len", "<f8"), ("
 assert NODE_DTYPE.itemsize == 120
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def quiet_stdout():
+    """the reference's message() logs to stdout; silence fd 1 while it runs (bench.py must print one JSON line)."""
+    import sys
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)
+    try:
+        yield
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved); os.close(devnull)
+
+
 def ptr(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 
