@@ -1,0 +1,36 @@
+#!/usr/bin/env python
+"""Short driver for ncu: bootstrap |a_old| (Barnes-Hut pass + PM), then `--steps` device-resident steps of the hot
+path on the bench workload (Zel'dovich ngrid^3, Nmesh = 2 ngrid).  Prints the stage timings of the last step."""
+import argparse, json, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench
+import shenqi_b200 as sq
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--ngrid", type=int, default=128)
+ap.add_argument("--steps", type=int, default=1)
+ap.add_argument("--group-width", type=int, default=32)
+ap.add_argument("--no-pm", action="store_true")
+a = ap.parse_args()
+pos, mass, par = bench.workload(a.ngrid, 2 * a.ngrid)
+ctx = sq.Context(0)
+ctx.set_group_width(a.group_width)
+P = sq.Params.defaults(par["BoxSize"], 2 * a.ngrid, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
+ctx.set_params(P)
+ctx.upload_particles(pos, mass)
+ctx.ph_sort(); ctx.tree_build()
+a0, _, _ = ctx.grav_short_tree()
+g0, _ = ctx.gravpm_force()
+P.TreeUseBH = 0
+ctx.set_params(P)
+ctx.set_old_accel(a0, g0)
+for _ in range(a.steps):
+    ctx.ph_sort(); ctx.tree_build()
+    st = ctx.grav_short_tree_device()
+    if not a.no_pm:
+        ctx.gravpm_force_device()
+tm = ctx.timings()
+print(json.dumps({"n": len(pos), "interactions": st.interactions, "list_entries": st.list_entries, "nodes_tested": st.nodes_tested,
+                  "ngroups": st.ngroups, "walk_ms": st.kernel_ms, "stages": {f: getattr(tm, f) for f, _ in tm._fields_}}))
+ctx.close()
