@@ -70,6 +70,8 @@ typedef struct sq_walk_stats {
     int64_t interactions;      /* (target, source) pairs evaluated = the reference's ninteractions */
     int64_t list_entries;      /* shared interaction-list entries evaluated (x group width = lane slots issued) */
     int64_t nodes_tested;      /* (node, group) opening evaluations */
+    int64_t pair_tests;        /* (target, node) pairs decided in FP32 with error intervals (tier 2) */
+    int64_t exact_tests;       /* (target, node) pairs that needed the reference's FP64 expressions (tier 3) */
     double  kernel_ms;         /* device time of the walk kernel (CUDA events) */
 } sq_walk_stats;
 

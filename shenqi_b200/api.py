@@ -49,7 +49,7 @@ class AosLayout(ctypes.Structure):
 
 class WalkStats(ctypes.Structure):
     _fields_ = [("ntargets", c_i64), ("ngroups", c_i64), ("interactions", c_i64), ("list_entries", c_i64),
-                ("nodes_tested", c_i64), ("kernel_ms", c_dbl)]
+                ("nodes_tested", c_i64), ("pair_tests", c_i64), ("exact_tests", c_i64), ("kernel_ms", c_dbl)]
 
 
 class TreeInfo(ctypes.Structure):

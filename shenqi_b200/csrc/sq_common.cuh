@@ -105,6 +105,7 @@ struct sq_ctx {
     int64_t tree_np = 0;             // particles in the tree
     int64_t tree_maxnodes = 0, tree_numnodes = 0;
     int tree_maxlevel = 0;
+    double tree_total_mass = 0;      // root monopole mass (mass unit of the walk's FP32 tiers)
     int lvl_start[SQ_MAXLEVEL + 3] = {};
     bool tree_built = false, tree_full = false, tree_identity = true;
 

@@ -410,7 +410,10 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
     }
     SQ_CUDA(cudaGetLastError());
     SQ_CUDA(cudaEventRecord(c->ev[6], c->stream));
+    double4 h_root = make_double4(0, 0, 0, 0);
+    SQ_CUDA(cudaMemcpyAsync(&h_root, c->t_cm.p, sizeof(h_root), cudaMemcpyDeviceToHost, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));
+    c->tree_total_mass = h_root.w;
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]); c->tm.tree_build_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]); c->tm.tree_moments_ms = ms;

@@ -12,19 +12,25 @@
 //     (node, mask): mask = the targets of the group that reach this node, i.e. opened every ancestor.
 //     Per step the warp pops up to 32 entries, one per lane; node records come in as coalesced 128-bit
 //     loads (children of a node are contiguous).
-//   * Each lane applies the reference's per-particle tests (discard: r2 vs Rcut and the Rcut+len/2
-//     box; open: relative-acceleration criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle,
-//     inside-0.6-len box) to ITS node for every target in the mask, in FP64 with the reference's
-//     expressions, so every (particle, node) decision is the one the reference takes.  That yields an
-//     accept mask (targets that use the node's monopole) and an open mask (targets that descend).
-//     Accepted nodes and the particles of opened leaves go to the interaction list together with their
-//     masks; children are pushed with the open mask.  A group-level bounding-box test discards nodes
-//     no target can reach without running the per-target loop.
-//   * The list stores sources as FP32 offsets from the group centre (formed in FP64, periodic wrap
-//     applied there, once per source rather than once per pair).  Evaluation is FP32: rsqrt, spline
-//     softening, the erfc/"exact" split factor from a shared-memory-resident table (value, slope pairs
-//     -> one 64-bit LDS + one FMA), FMA accumulation.  Partial sums are carried in FP32 for at most one
-//     list flush (<= LIST_CAP entries) and then added to FP64 accumulators.
+//   * Every (target, node) decision is the reference's own (discard: r2 vs Rcut and the Rcut+len/2 box;
+//     open: relative criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle, inside-0.6-len box), but it is
+//     reached in three tiers so that FP64 is the exception:
+//       1. group tier (FP32 interval arithmetic over the group's bounding box and its min/max |a_old|):
+//          if both ends of the interval give the same class, the whole mask is discarded / accepted /
+//          opened at once;
+//       2. target tier (FP32, coordinates relative to the group centre in units of the split-table
+//          spacing, masses in units of the mean particle mass): the class is evaluated at both ends of
+//          the rounding-error interval of (r2, max-axis distance); equal -> decided;
+//       3. exact tier: the reference's FP64 expressions with per-target NEAREST() for the pairs whose
+//          interval straddles a threshold, and for nodes half a box away from the group.
+//     The decision function is monotone in (r2, emax), so equal classes at the interval ends prove the
+//     FP64 class.  The interaction count therefore equals the reference's exactly.
+//   * Accepted nodes and the particles of opened leaves go to the interaction list with their masks;
+//     children are pushed with the open mask.
+//   * Evaluation is FP32: rsqrt, spline softening (rare, FP64), the erfc/"exact" split factor from a
+//     shared-memory-resident table of (value at mid-point offset, slope) pairs -> one 64-bit LDS + one FMA.
+//     Distances are already in table units, so the table coordinate costs nothing.  Partial sums are
+//     carried in FP32 for one list flush (<= LIST_CAP entries) and then added to FP64 accumulators.
 //   * Epilogue = postprocess: x G, potential self terms; results written in sorted order.
 #include "sq_common.cuh"
 #include "shortrange_table.h"
@@ -34,17 +40,23 @@
 #define WALK_THREADS (WALK_WARPS * 32)
 #define STACK_CAP 512
 #define STACK_RESERVE 160   /* 7 siblings x 22 levels: room a depth-first descent can always need */
-#define LIST_CAP 128
+#define LIST_CAP 128        /* multiple of 4 */
+#define SQ_EPS 4e-6f        /* relative slack on every FP32 threshold (>> 2^-24 rounding chains) */
 
 struct sq_walk_par {
-    double box, half, rcut, rcut2, bh2, h;          // h = ForceSoftening = 2.8 eps
-    double G, cbrtrho0, errtol;
-    int relative;                                   // TreeUseBH == 0
-    float f_box, f_invbox, f_h2, f_inv_cell_dx, f_range;   // f_range: distance beyond which the table gives zero
+    // exact tier (reference expressions, FP64)
+    double box, half, rcut, rcut2, bh2, h, errtol;
+    // scaling: lengths x s (table units), masses x minv
+    double s, minv, Ka, Kp;       // accel = Ka * sum, potential = Kp * sum (+ self terms)
+    double G, cbrtrho0;
+    int relative;                 // TreeUseBH == 0
+    int gw;                       // targets per warp: 32, 16 or 8
+    // FP32 tiers (table units)
+    float f_rcut, f_rc2_lo, f_rc2_hi, f_bh2, f_h2, f_hs, f_boxs, f_invboxs, f_halfs, f_range;
 };
 
 struct sq_walk_warp_smem {
-    double tx[32], ty[32], tz[32], ta[32];
+    float4 tgt[32];               // x, y, z relative to the group centre (table units), w = errtol*|a_old| scaled
     int2 stack[STACK_CAP];
     float4 lst[LIST_CAP];
     unsigned lmask[LIST_CAP];
@@ -52,72 +64,129 @@ struct sq_walk_warp_smem {
     unsigned s_mask[32];
 };
 
-// spline-softened force and potential factors, gravshort2.hpp:332-350 (evaluated in FP64: rare branch)
-__device__ __noinline__ void sq_soft_kernel(float r, float m, double h, float * fac, float * facpot)
+// spline-softened force and potential factors, gravshort2.hpp:332-350 (FP64: rare branch).
+// r, h in table units; returns (fac, facpot) per unit mass in the scaled system.
+__device__ __noinline__ float2 sq_soft_kernel(float r, double h)
 {
-    const double h3_inv = 1.0 / h / h / h;
-    const double u = (double) r / h;
+    const double h_inv = 1.0 / h;
+    const double h3_inv = h_inv * h_inv * h_inv;
+    const double u = (double) r * h_inv;
     double f, wp;
     if(u < 0.5) {
-        f = (double) m * h3_inv * (10.666666666667 + u * u * (32.0 * u - 38.4));
+        f = h3_inv * (10.666666666667 + u * u * (32.0 * u - 38.4));
         wp = -2.8 + u * u * (5.333333333333 + u * u * (6.4 * u - 9.6));
     } else {
-        f = (double) m * h3_inv * (21.333333333333 - 48.0 * u + 38.4 * u * u - 10.666666666667 * u * u * u - 0.066666666667 / (u * u * u));
+        f = h3_inv * (21.333333333333 - 48.0 * u + 38.4 * u * u - 10.666666666667 * u * u * u - 0.066666666667 / (u * u * u));
         wp = -3.2 + 0.066666666667 / u + u * u * (10.666666666667 + u * (-16.0 + u * (9.6 - 2.133333333333 * u)));
     }
-    *fac = (float) f;
-    *facpot = (float) ((double) m / h * wp);
+    return make_float2((float) f, (float) (h_inv * wp));
 }
 
-template <int G, bool POT>
+template <bool POT>
 struct sq_walk_acc {
     float ax, ay, az, ap;
     double dax, day, daz, dap;
-    unsigned nint;
 };
 
-// Evaluate list entries [0, n) for this lane's target (slice sl of S takes entries sl, sl+S, ...).
-template <int G, bool POT>
-__device__ __forceinline__ void sq_walk_flush(sq_walk_warp_smem & W, int n, const float2 * __restrict__ ftab, const float2 * __restrict__ ptab,
-                                              const sq_walk_par & P, float txr, float tyr, float tzr, int tl, int sl, bool pairwrap,
-                                              sq_walk_acc<G, POT> & A)
+__device__ __forceinline__ float2 sq_lds_f2(unsigned addr)
 {
-    constexpr int S = 32 / G;
-    for(int e = sl; e < n; e += S) {
-        const float4 s = W.lst[e];
-        const unsigned m = W.lmask[e];
-        if((m >> tl) & 1u) {
-            float dx = s.x - txr, dy = s.y - tyr, dz = s.z - tzr;
-            if(pairwrap) {
-                dx -= P.f_box * rintf(dx * P.f_invbox);
-                dy -= P.f_box * rintf(dy * P.f_invbox);
-                dz -= P.f_box * rintf(dz * P.f_invbox);
+    float2 v;
+    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float4 sq_lds_f4(unsigned addr)
+{
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+// one MUFU.RSQ (the caller keeps the argument away from 0 and denormals)
+__device__ __forceinline__ float sq_rsqrt(float x)
+{
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// Evaluate list entries [0, n) for this lane's target (slice sl of S takes the 4-entry blocks sl, sl+S, ...).
+template <bool POT, bool WRAP>
+__device__ __forceinline__ void sq_walk_flush(sq_walk_warp_smem & W, int n, unsigned tab_biased,
+                                              const sq_walk_par & P, float tx, float ty, float tz, int tl, int sl, int S,
+                                              sq_walk_acc<POT> & A)
+{
+    const int nb = (n + 3) >> 2;
+    {
+        const int pad = (nb << 2) - n;
+        if((int) sq_lane() < pad) W.lmask[n + sq_lane()] = 0u;
+    }
+    __syncwarp();
+    const unsigned lbit = 1u << tl;
+    const uint4 * mk4 = reinterpret_cast<const uint4 *>(W.lmask);
+    const float h2 = P.f_h2;
+    for(int b = sl; b < nb; b += S) {
+        const uint4 mk = mk4[b];
+        unsigned soft = 0;
+        #pragma unroll
+        for(int j = 0; j < 4; j++) {
+            const float4 s = W.lst[4 * b + j];
+            const unsigned m = j == 0 ? mk.x : (j == 1 ? mk.y : (j == 2 ? mk.z : mk.w));
+            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+            if(WRAP) {
+                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
+                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
+                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
             }
-            const float r2 = dx * dx + dy * dy + dz * dz;
-            const float rinv = rsqrtf(r2);
-            float r = r2 * rinv;
-            float fac = s.w * rinv * rinv * rinv;
-            float facpot = -s.w * rinv;
-            if(r2 < P.f_h2) {
-                r = sqrtf(r2);
-                sq_soft_kernel(r, s.w, P.h, &fac, &facpot);
-            }
-            A.nint++;
-            // gravity.h:48-60: i = r/cellsize/dx, zero beyond the table, linear interpolation
-            const float x = r * P.f_inv_cell_dx;
-            if(x < (float) (SQ_NTAB - 1)) {
-                const float t = (x - 0.5f) + 12582912.f;                 // round(x - 0.5) in the mantissa
-                const int idx = __float_as_int(t) - 0x4B400000;
-                const float frac = x - (t - 12582912.f);
-                const float2 fw = ftab[idx];
-                fac *= fmaf(frac, fw.y, fw.x);
+            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            const bool on = (m & lbit) != 0u;
+            const bool far = r2 >= h2;
+            const float mm = (on && far) ? s.w : 0.f;
+            if(on && !far) soft |= 1u << j;
+            // softened pairs (r2 < h2) take the slow path below; clamping keeps rsqrt finite for them
+            const float rinv = sq_rsqrt(fmaxf(r2, h2));
+            // table coordinate: distances are in table units.  xq = r - 1/2; round-to-nearest of xq = floor(r)
+            // (gravity.h:50-60: i = r/cellsize/dx, zero beyond the table, linear interpolation)
+            const float xq = fminf(fmaf(r2, rinv, -0.5f), 511.f);
+            const float t = xq + 12582912.f;
+            const float d = xq - (t - 12582912.f);
+            const unsigned off = (unsigned) __float_as_int(t) << 4;
+            const float rinv2 = rinv * rinv;
+            if(POT) {
+                const float4 w = sq_lds_f4(tab_biased + off);
+                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
                 A.ax = fmaf(dx, fac, A.ax);
                 A.ay = fmaf(dy, fac, A.ay);
                 A.az = fmaf(dz, fac, A.az);
-                if(POT) {
-                    const float2 pw = ptab[idx];
-                    A.ap = fmaf(facpot, fmaf(frac, pw.y, pw.x), A.ap);
-                }
+                A.ap = fmaf(-mm * rinv, fmaf(d, w.w, w.z), A.ap);
+            } else {
+                const float2 w = sq_lds_f2(tab_biased + off);
+                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
+                A.ax = fmaf(dx, fac, A.ax);
+                A.ay = fmaf(dy, fac, A.ay);
+                A.az = fmaf(dz, fac, A.az);
+            }
+        }
+        // softened pairs (r < 2.8 eps), including the target meeting itself in its own leaf (r = 0)
+        while(soft) {
+            const int j = __ffs(soft) - 1;
+            soft &= soft - 1;
+            const float4 s = W.lst[4 * b + j];
+            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+            if(WRAP) {
+                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
+                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
+                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
+            }
+            const float r = sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
+            const float2 sf = sq_soft_kernel(r, (double) P.f_hs);
+            if(r < 511.f) {
+                const float fl = floorf(r);
+                const float dd = (r - fl) - 0.5f;
+                const float4 w = sq_lds_f4(tab_biased + ((0x4B400000u + (unsigned) (int) fl) << 4));
+                const float fac = s.w * sf.x * fmaf(dd, w.y, w.x);
+                A.ax = fmaf(dx, fac, A.ax);
+                A.ay = fmaf(dy, fac, A.ay);
+                A.az = fmaf(dz, fac, A.az);
+                if(POT) A.ap = fmaf(s.w * sf.y, fmaf(dd, w.w, w.z), A.ap);
             }
         }
     }
@@ -126,29 +195,65 @@ __device__ __forceinline__ void sq_walk_flush(sq_walk_warp_smem & W, int n, cons
     if(POT) { A.dap += (double) A.ap; A.ap = 0.f; }
 }
 
-template <int G, bool POT>
-__global__ void __launch_bounds__(WALK_THREADS, 2)
+// Node constants of the FP32 tiers (one node per lane)
+struct sq_node_f {
+    float cmx, cmy, cmz, cx, cy, cz;
+};
+
+// exact tier: the reference's FP64 test for one (target, node)
+struct sq_exact_par { double box, half, rcut, rcut2, bh2; int relative; };
+__device__ __noinline__ int sq_exact_class(const double4 M, const double4 C, double x, double y, double z, double aold, const sq_exact_par P)
+{
+    const double len = C.w;
+    const double dx = sq_nearest(M.x - x, P.box, P.half);
+    const double dy = sq_nearest(M.y - y, P.box, P.half);
+    const double dz = sq_nearest(M.z - z, P.box, P.half);
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double ex = fabs(sq_nearest(C.x - x, P.box, P.half));
+    const double ey = fabs(sq_nearest(C.y - y, P.box, P.half));
+    const double ez = fabs(sq_nearest(C.z - z, P.box, P.half));
+    // shall_we_discard_node, gravshort2.hpp:152-167
+    if(r2 > P.rcut2) {
+        const double eff = P.rcut + 0.5 * len;
+        if(ex > eff || ey > eff || ez > eff) return 0;
+    }
+    // shall_we_open_node, gravshort2.hpp:172-193
+    if(P.relative && (M.w * len * len > r2 * r2 * aold)) return 2;
+    if(len * len / r2 > P.bh2) return 2;
+    const double inside = 0.6 * len;
+    if(ex < inside && ey < inside && ez < inside) return 2;
+    return 1;
+}
+
+template <bool POT>
+__global__ void __launch_bounds__(WALK_THREADS, 3)
 sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl, const int4 * __restrict__ lk,
                const double * __restrict__ spos, const float * __restrict__ smass,
                const double * __restrict__ tpos, const float * __restrict__ tmass, const double * __restrict__ toldacc,
-               const uint32_t * __restrict__ targets, long long ntargets, const float2 * __restrict__ gtab,
+               const uint32_t * __restrict__ targets, long long ntargets, const float4 * __restrict__ gtab,
                double * __restrict__ accel, double * __restrict__ pot, unsigned long long * __restrict__ stats,
                int * __restrict__ group_counter, const sq_walk_par P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2 * ftab = reinterpret_cast<float2 *>(smem_raw);
-    float2 * ptab = ftab + SQ_NTAB;
-    sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + 2 * SQ_NTAB * sizeof(float2));
-    for(int i = threadIdx.x; i < 2 * SQ_NTAB; i += blockDim.x)
-        ftab[i] = gtab[i];
-    __syncthreads();
-
-    constexpr int S = 32 / G;
+    float4 * tab = reinterpret_cast<float4 *>(smem_raw);
+    sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + SQ_NTAB * sizeof(float4));
+    for(int i = threadIdx.x; i < SQ_NTAB; i += blockDim.x)
+        tab[i] = gtab[i];
     const unsigned lane = sq_lane();
-    const int tl = lane % G, sl = lane / G;
     sq_walk_warp_smem & W = Wall[threadIdx.x >> 5];
+    for(int i = lane; i < LIST_CAP; i += 32) {
+        W.lst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        W.lmask[i] = 0u;
+    }
+    __syncthreads();
+    // table addresses biased so that the mantissa bits of (x + 1.5*2^23) index them directly
+    const unsigned tab_biased = (unsigned) __cvta_generic_to_shared(tab) - (0x4B400000u << 4);
+
+    const int G = P.gw;
+    const int S = 32 / G;
+    const int tl = lane & (G - 1), sl = lane / G;
     const long long ngroups = (ntargets + G - 1) / G;
-    unsigned long long st_int = 0, st_ent = 0, st_tst = 0;
+    unsigned long long st_int = 0, st_ent = 0, st_tst = 0, st_pair = 0, st_exact = 0;
 
     for(;;) {
         long long g = 0;
@@ -168,32 +273,39 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         // group bounding box over the valid targets
         double lox = valid ? px : 1e300, loy = valid ? py : 1e300, loz = valid ? pz : 1e300;
         double hix = valid ? px : -1e300, hiy = valid ? py : -1e300, hiz = valid ? pz : -1e300;
+        double amin = valid ? aold : 1e300, amax = valid ? aold : 0.0;
         #pragma unroll
         for(int o = 16; o >= 1; o >>= 1) {
             lox = fmin(lox, __shfl_xor_sync(SQ_FULL, lox, o)); hix = fmax(hix, __shfl_xor_sync(SQ_FULL, hix, o));
             loy = fmin(loy, __shfl_xor_sync(SQ_FULL, loy, o)); hiy = fmax(hiy, __shfl_xor_sync(SQ_FULL, hiy, o));
             loz = fmin(loz, __shfl_xor_sync(SQ_FULL, loz, o)); hiz = fmax(hiz, __shfl_xor_sync(SQ_FULL, hiz, o));
+            amin = fmin(amin, __shfl_xor_sync(SQ_FULL, amin, o)); amax = fmax(amax, __shfl_xor_sync(SQ_FULL, amax, o));
         }
         const double gcx = 0.5 * (lox + hix), gcy = 0.5 * (loy + hiy), gcz = 0.5 * (loz + hiz);
-        const double ghx = 0.5 * (hix - lox), ghy = 0.5 * (hiy - loy), ghz = 0.5 * (hiz - loz);
+        // half extents in table units, rounded up
+        const float ghx = (float) (0.5 * (hix - lox) * P.s) * 1.000001f + 1e-30f;
+        const float ghy = (float) (0.5 * (hiy - loy) * P.s) * 1.000001f + 1e-30f;
+        const float ghz = (float) (0.5 * (hiz - loz) * P.s) * 1.000001f + 1e-30f;
+        const float ghm = fmaxf(ghx, fmaxf(ghy, ghz));
+        // errtol*|a_old| in the scaled system: M l^2 > r^4 a  <=>  M' l'^2 > r'^4 a / (munit s^2); BH mode: never
+        const double ascale = P.minv / (P.s * P.s);
+        const float ta = P.relative ? (float) (aold * ascale) : __int_as_float(0x7f800000);
+        const float ta_lo = P.relative ? (float) (amin * ascale) * (1.f - SQ_EPS) : __int_as_float(0x7f800000);
+        const float ta_hi = P.relative ? (float) (amax * ascale) * (1.f + SQ_EPS) : __int_as_float(0x7f800000);
+        const float tx = (float) ((px - gcx) * P.s), ty = (float) ((py - gcy) * P.s), tz = (float) ((pz - gcz) * P.s);
         __syncwarp();
-        if(sl == 0) {
-            W.tx[tl] = px; W.ty[tl] = py; W.tz[tl] = pz; W.ta[tl] = aold;
-        }
-        const float txr = (float) (px - gcx), tyr = (float) (py - gcy), tzr = (float) (pz - gcz);
+        if(sl == 0) W.tgt[tl] = make_float4(tx, ty, tz, ta);
         // pairs may straddle the periodic image once group extent + table range reaches half the box
-        const bool pairwrap = 2.0 * fmax(ghx, fmax(ghy, ghz)) + (double) P.f_range >= P.half;
-        sq_walk_acc<G, POT> A;
+        const bool pairwrap = 2.f * ghm + P.f_range >= P.f_halfs;
+        sq_walk_acc<POT> A;
         A.ax = A.ay = A.az = A.ap = 0.f;
         A.dax = A.day = A.daz = A.dap = 0.0;
-        A.nint = 0;
         int top = 0, nlist = 0;
         if(lane == 0) W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
         top = 1;
         __syncwarp();
 
         while(top > 0) {
-            // pop: as many as fit while keeping room for 8 children each
             // wide pops only while a depth-first descent (<= 7 entries per level) still fits above them
             int k = (STACK_CAP - STACK_RESERVE - top) / 7;
             k = k < 1 ? 1 : k;
@@ -210,45 +322,112 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
             __syncwarp();
             unsigned acc_mask = 0, open_mask = 0;
             int4 L = make_int4(0, 0, -1, 0);
-            double4 M = make_double4(0, 0, 0, 0);
+            float n_mass = 0.f;
+            sq_node_f N;
+            N.cmx = N.cmy = N.cmz = 0.f;
             if(have) {
                 L = lk[node];
-                M = cm[node];
+                const double4 M = cm[node];
                 const double4 C = cl[node];
-                const double len = C.w;
                 st_tst++;
-                // group-level discard (gravshort2.hpp:152-167 holds for every target if it holds for the box)
-                const double eff = P.rcut + 0.5 * len;
-                const double bx = fabs(sq_nearest(C.x - gcx, P.box, P.half)) - ghx;
-                const double by = fabs(sq_nearest(C.y - gcy, P.box, P.half)) - ghy;
-                const double bz = fabs(sq_nearest(C.z - gcz, P.box, P.half)) - ghz;
-                if(!(bx > eff || by > eff || bz > eff)) {
-                    const double inside = 0.6 * len;
-                    const double ml2 = M.w * len * len;
-                    const double l2 = len * len;
-                    unsigned mm = mask;
-                    while(mm) {
-                        const int t = __ffs(mm) - 1;
-                        mm &= mm - 1;
-                        const double x = W.tx[t], y = W.ty[t], z = W.tz[t];
-                        const double dx = sq_nearest(M.x - x, P.box, P.half);
-                        const double dy = sq_nearest(M.y - y, P.box, P.half);
-                        const double dz = sq_nearest(M.z - z, P.box, P.half);
-                        const double r2 = dx * dx + dy * dy + dz * dz;
-                        const double ex = fabs(sq_nearest(C.x - x, P.box, P.half));
-                        const double ey = fabs(sq_nearest(C.y - y, P.box, P.half));
-                        const double ez = fabs(sq_nearest(C.z - z, P.box, P.half));
-                        // shall_we_discard_node, gravshort2.hpp:152-167
-                        if(r2 > P.rcut2 && (ex > eff || ey > eff || ez > eff))
-                            continue;
-                        // shall_we_open_node, gravshort2.hpp:172-193
-                        bool open = false;
-                        if(P.relative && (ml2 > r2 * r2 * W.ta[t])) open = true;
-                        else if(l2 / r2 > P.bh2) open = true;
-                        else if(ex < inside && ey < inside && ez < inside) open = true;
-                        if(open) open_mask |= 1u << t;
-                        else acc_mask |= 1u << t;
+                const double dmx = sq_nearest(M.x - gcx, P.box, P.half), dmy = sq_nearest(M.y - gcy, P.box, P.half), dmz = sq_nearest(M.z - gcz, P.box, P.half);
+                const double dcx = sq_nearest(C.x - gcx, P.box, P.half), dcy = sq_nearest(C.y - gcy, P.box, P.half), dcz = sq_nearest(C.z - gcz, P.box, P.half);
+                N.cmx = (float) (dmx * P.s); N.cmy = (float) (dmy * P.s); N.cmz = (float) (dmz * P.s);
+                N.cx = (float) (dcx * P.s); N.cy = (float) (dcy * P.s); N.cz = (float) (dcz * P.s);
+                n_mass = (float) (M.w * P.minv);
+                const float len = (float) (C.w * P.s);
+                const float l2 = len * len, ml2 = n_mass * l2;
+                const float acx = fabsf(N.cx), acy = fabsf(N.cy), acz = fabsf(N.cz);
+                const float amx = fabsf(N.cmx), amy = fabsf(N.cmy), amz = fabsf(N.cmz);
+                // rounding-error bounds of the FP32 coordinates / squared distances
+                const float scale = fmaxf(fmaxf(fmaxf(acx, acy), fmaxf(acz, amx)), fmaxf(amy, amz)) + ghm;
+                const float de = 3e-7f * scale;
+                const float R1 = amx + amy + amz + 3.f * ghm;
+                const float dr2 = 4.f * R1 * de + 1e-6f * R1 * R1;
+                const float eff = P.f_rcut + 0.5f * len, ins = 0.6f * len;
+                // thresholds with the relative slack and the coordinate error folded in:
+                //   "A" = the end of the interval that keeps / opens most, "B" = the end that keeps / opens least
+                const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
+                const float efA = eff * (1.f + SQ_EPS) + de, efB = eff * (1.f - SQ_EPS) - de;
+                const float inA = ins * (1.f + SQ_EPS) + de, inB = ins * (1.f - SQ_EPS) - de;
+                const float bhq = l2 / P.f_bh2;
+                const float bhA = bhq * (1.f + SQ_EPS) + dr2, bhB = bhq * (1.f - SQ_EPS) - dr2;
+                const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
+                // a node about half a box away from the group: per-target NEAREST may differ from the group's
+                const bool risky = fmaxf(fmaxf(acx + ghx, acy + ghy), fmaxf(acz + ghz, fmaxf(fmaxf(amx + ghx, amy + ghy), amz + ghz))) >= P.f_halfs * 0.999f;
+                unsigned needk = 0, needo = 0, exact = 0;
+                bool gopen = false;
+                if(risky) exact = mask;
+                else {
+                    // ---- tier 1: the whole group at once (bounding box, min/max |a_old|)
+                    const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
+                    const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
+                    const float r2n = qx * qx + qy * qy + qz * qz, r2f = wx * wx + wy * wy + wz * wz;
+                    const float en = fmaxf(fmaxf(acx - ghx, acy - ghy), acz - ghz);
+                    const float ef = fmaxf(fmaxf(acx + ghx, acy + ghy), acz + ghz);
+                    const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
+                    const bool gk_lo = (r2n <= rcA) || !(en > efA);
+                    const bool gk_hi = (r2f <= rcB) || !(ef > efB);
+                    const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
+                    const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
+                    gopen = go_hi;
+                    if(gk_lo) {
+                        if(gk_hi) {
+                            if(go_lo == go_hi) { if(go_hi) open_mask = mask; else acc_mask = mask; }
+                            else needo = mask;
+                        } else needk = mask;
+                        if(go_lo != go_hi) needo = mask;
                     }
+                }
+                // ---- tier 2a: keep or discard, per target, FP32 with error intervals
+                st_pair += __popc(needk) + __popc(needo);
+                const bool omixed = needo != 0u;
+                unsigned kept = (needk == 0u) ? needo : 0u;
+                while(needk) {
+                    const int t = 31 - __clz(needk);
+                    const unsigned bit = 1u << t;
+                    needk ^= bit;
+                    const float4 T = W.tgt[t];
+                    const float dx = N.cmx - T.x, dy = N.cmy - T.y, dz = N.cmz - T.z;
+                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float em = fmaxf(fmaxf(fabsf(N.cx - T.x), fabsf(N.cy - T.y)), fabsf(N.cz - T.z));
+                    const bool k_lo = (r2 <= rcA) || !(em > efA);
+                    const bool k_hi = (r2 <= rcB) || !(em > efB);
+                    if(k_lo != k_hi) exact |= bit;
+                    else if(k_lo) kept |= bit;
+                }
+                if(!omixed) {
+                    if(gopen) open_mask |= kept; else acc_mask |= kept;
+                    kept = 0;
+                }
+                // ---- tier 2b: open or accept, for the kept targets of nodes whose opening is not uniform
+                while(kept) {
+                    const int t = 31 - __clz(kept);
+                    const unsigned bit = 1u << t;
+                    kept ^= bit;
+                    const float4 T = W.tgt[t];
+                    const float dx = N.cmx - T.x, dy = N.cmy - T.y, dz = N.cmz - T.z;
+                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float em = fmaxf(fmaxf(fabsf(N.cx - T.x), fabsf(N.cy - T.y)), fabsf(N.cz - T.z));
+                    const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
+                    const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
+                    const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
+                    if(o_lo != o_hi) exact |= bit;
+                    else if(o_lo) open_mask |= bit;
+                    else acc_mask |= bit;
+                }
+                // ---- tier 3: the reference's FP64 expressions
+                while(exact) {
+                    const int t = 31 - __clz(exact);
+                    const unsigned bit = 1u << t;
+                    exact ^= bit;
+                    const long long ti = targets ? (long long) targets[t0 + t] : (t0 + t);
+                    sq_exact_par X;
+                    X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
+                    const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
+                    st_exact++;
+                    if(c == 1) acc_mask |= bit;
+                    else if(c == 2) open_mask |= bit;
                 }
             }
             const int type = SQ_INFO_TYPE(L.w);
@@ -260,15 +439,16 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                     if(nlist + tot > LIST_CAP) {
                         __syncwarp();
                         st_ent += nlist;
-                        sq_walk_flush<G, POT>(W, nlist, ftab, ptab, P, txr, tyr, tzr, tl, sl, pairwrap, A);
+                        if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
+                        else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
                         nlist = 0;
                         __syncwarp();
                     }
                     if(acc_mask) {
                         const int p = nlist + __popc(b & sq_lanemask_lt());
-                        W.lst[p] = make_float4((float) sq_nearest(M.x - gcx, P.box, P.half), (float) sq_nearest(M.y - gcy, P.box, P.half),
-                                               (float) sq_nearest(M.z - gcz, P.box, P.half), (float) M.w);
+                        W.lst[p] = make_float4(N.cmx, N.cmy, N.cmz, n_mass);
                         W.lmask[p] = acc_mask;
+                        st_int += __popc(acc_mask);
                     }
                     nlist += tot;
                 }
@@ -288,6 +468,7 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                 int tot;
                 const int off = sq_warp_excl_scan(np, tot);
                 if(tot) {
+                    st_int += (unsigned long long) np * __popc(open_mask);
                     W.s_end[lane] = off + np;
                     W.s_first[lane] = L.x - off;        // particle = s_first + j
                     W.s_mask[lane] = open_mask;
@@ -297,7 +478,8 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                         if(nlist + chunk > LIST_CAP) {
                             __syncwarp();
                             st_ent += nlist;
-                            sq_walk_flush<G, POT>(W, nlist, ftab, ptab, P, txr, tyr, tzr, tl, sl, pairwrap, A);
+                            if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
+                            else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
                             nlist = 0;
                             __syncwarp();
                         }
@@ -311,8 +493,8 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                             }
                             const long long p = (long long) W.s_first[lo] + j;
                             const double sx = spos[3 * p], sy = spos[3 * p + 1], sz = spos[3 * p + 2];
-                            W.lst[nlist + lane] = make_float4((float) sq_nearest(sx - gcx, P.box, P.half), (float) sq_nearest(sy - gcy, P.box, P.half),
-                                                              (float) sq_nearest(sz - gcz, P.box, P.half), smass[p]);
+                            W.lst[nlist + lane] = make_float4((float) (sq_nearest(sx - gcx, P.box, P.half) * P.s), (float) (sq_nearest(sy - gcy, P.box, P.half) * P.s),
+                                                              (float) (sq_nearest(sz - gcz, P.box, P.half) * P.s), (float) ((double) smass[p] * P.minv));
                             W.lmask[nlist + lane] = W.s_mask[lo];
                         }
                         nlist += chunk;
@@ -324,29 +506,27 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         }
         __syncwarp();
         st_ent += nlist;
-        sq_walk_flush<G, POT>(W, nlist, ftab, ptab, P, txr, tyr, tzr, tl, sl, pairwrap, A);
+        if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
+        else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
         // combine the slices of each target
-        #pragma unroll
         for(int o = G; o < 32; o <<= 1) {
             A.dax += __shfl_xor_sync(SQ_FULL, A.dax, o);
             A.day += __shfl_xor_sync(SQ_FULL, A.day, o);
             A.daz += __shfl_xor_sync(SQ_FULL, A.daz, o);
             if(POT) A.dap += __shfl_xor_sync(SQ_FULL, A.dap, o);
-            A.nint += __shfl_xor_sync(SQ_FULL, A.nint, o);
         }
         if(valid && sl == 0) {
             // gravshort2.hpp:88-107
-            accel[3 * tidx] = A.dax * P.G;
-            accel[3 * tidx + 1] = A.day * P.G;
-            accel[3 * tidx + 2] = A.daz * P.G;
+            accel[3 * tidx] = A.dax * P.Ka;
+            accel[3 * tidx + 1] = A.day * P.Ka;
+            accel[3 * tidx + 2] = A.daz * P.Ka;
             if(POT) {
                 const double m = (double) tmass[tidx];
-                double p = A.dap;
+                double p = A.dap * P.Kp;
                 p += m / (P.h / 2.8);
                 p -= 2.8372975 * pow(m, 2.0 / 3) * P.cbrtrho0;
                 pot[tidx] = p * P.G;
             }
-            st_int += A.nint;
         }
         __syncwarp();
     }
@@ -355,11 +535,15 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
     for(int o = 16; o >= 1; o >>= 1) {
         st_int += __shfl_xor_sync(SQ_FULL, st_int, o);
         st_tst += __shfl_xor_sync(SQ_FULL, st_tst, o);
+        st_pair += __shfl_xor_sync(SQ_FULL, st_pair, o);
+        st_exact += __shfl_xor_sync(SQ_FULL, st_exact, o);
     }
     if(lane == 0) {
         atomicAdd(&stats[0], st_int);
         atomicAdd(&stats[1], st_ent);
         atomicAdd(&stats[2], st_tst);
+        atomicAdd(&stats[3], st_pair);
+        atomicAdd(&stats[4], st_exact);
     }
 }
 
@@ -368,7 +552,9 @@ static const double h_sr_x[SQ_NGRAVTAB] = SQ_SHORTRANGE_X_INIT;
 static const double h_sr_pot[SQ_NGRAVTAB] = SQ_SHORTRANGE_POT_INIT;
 static const double h_sr_force[SQ_NGRAVTAB] = SQ_SHORTRANGE_FORCE_INIT;
 
-// GravShortTable, libgadget/gravshort-tree2.cpp:29-69: float tables; here pre-differenced (value, slope)
+// GravShortTable, libgadget/gravshort-tree2.cpp:29-69: float tables.  Device form: entry i holds
+// (value at the middle of [i, i+1], slope), so w(r) = v + (r - i - 1/2) * slope; entry 511 = (0, 0):
+// beyond the table the force is zero (gravity.h:53-54).
 static int sq_walk_table(sq_ctx * c)
 {
     float ft[SQ_NTAB], pt[SQ_NTAB];
@@ -382,11 +568,13 @@ static int sq_walk_table(sq_ctx * c)
             pt[i] = (float) erfc(u);
         }
     }
-    float2 h[2 * SQ_NTAB];
+    float4 h[SQ_NTAB];     // (force value at mid-cell, force slope, potential value at mid-cell, potential slope)
     for(int i = 0; i < SQ_NTAB; i++) {
-        const int j = i + 1 < SQ_NTAB ? i + 1 : i;
-        h[i] = make_float2(ft[i], (float) ((double) ft[j] - (double) ft[i]));
-        h[SQ_NTAB + i] = make_float2(pt[i], (float) ((double) pt[j] - (double) pt[i]));
+        if(i + 1 < SQ_NTAB) {
+            const double sf = (double) ft[i + 1] - (double) ft[i], sp = (double) pt[i + 1] - (double) pt[i];
+            h[i] = make_float4((float) ((double) ft[i] + 0.5 * sf), (float) sf, (float) ((double) pt[i] + 0.5 * sp), (float) sp);
+        } else
+            h[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     SQ_TRY(c->w_table.reserve(sizeof(h)));
     SQ_CUDA(cudaMemcpyAsync(c->w_table.p, h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
@@ -394,24 +582,24 @@ static int sq_walk_table(sq_ctx * c)
     return SQ_OK;
 }
 
-template <int G, bool POT>
+template <bool POT>
 static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets, const sq_walk_par & P)
 {
-    const size_t smem = 2 * SQ_NTAB * sizeof(float2) + WALK_WARPS * sizeof(sq_walk_warp_smem);
-    SQ_CUDA(cudaFuncSetAttribute(sq_walk_kernel<G, POT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const size_t smem = SQ_NTAB * sizeof(float4) + WALK_WARPS * sizeof(sq_walk_warp_smem);
+    SQ_CUDA(cudaFuncSetAttribute(sq_walk_kernel<POT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = 0;
-    SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sq_walk_kernel<G, POT>, WALK_THREADS, smem));
+    SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sq_walk_kernel<POT>, WALK_THREADS, smem));
     if(per_sm < 1) per_sm = 1;
-    const int64_t ngroups = (ntargets + G - 1) / G;
+    const int64_t ngroups = (ntargets + P.gw - 1) / P.gw;
     int64_t grid = (int64_t) c->num_sms * per_sm;
     const int64_t need = (ngroups + WALK_WARPS - 1) / WALK_WARPS;
     if(grid > need) grid = need;
     if(grid < 1) grid = 1;
     const double * spos = c->tree_identity ? c->pos.as<double>() : c->tree_pos.as<double>();
     const float * smass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
-    sq_walk_kernel<G, POT><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
+    sq_walk_kernel<POT><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
             spos, smass, c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(), targets, (long long) ntargets,
-            c->w_table.as<float2>(), c->w_accel.as<double>(), c->w_pot.as<double>(), c->w_stats.as<unsigned long long>(),
+            c->w_table.as<float4>(), c->w_accel.as<double>(), c->w_pot.as<double>(), c->w_stats.as<unsigned long long>(),
             c->w_counter.as<int>(), P);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
@@ -440,11 +628,23 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     P.relative = par.TreeUseBH == 0;
     P.bh2 = par.BHOpeningAngle * par.BHOpeningAngle;
     if(par.TreeUseBH == 0) P.bh2 = par.MaxBHOpeningAngle * par.MaxBHOpeningAngle;
-    P.f_box = (float) par.BoxSize;
-    P.f_invbox = (float) (1.0 / par.BoxSize);
-    P.f_h2 = (float) (P.h * P.h);
-    P.f_inv_cell_dx = (float) (1.0 / (cellsize * SQ_SHORTRANGE_DX));
-    P.f_range = (float) ((SQ_NTAB - 1) * cellsize * SQ_SHORTRANGE_DX);
+    // scaled system of the FP32 tiers: 1 length unit = one step of the split table, 1 mass unit = mean tree particle
+    P.s = 1.0 / (cellsize * SQ_SHORTRANGE_DX);
+    const double munit = (c->tree_total_mass > 0 && c->tree_np > 0) ? c->tree_total_mass / (double) c->tree_np : 1.0;
+    P.minv = 1.0 / munit;
+    P.Ka = par.G * munit * P.s * P.s;
+    P.Kp = munit * P.s;
+    P.gw = sq_walk_group_width;
+    P.f_rcut = (float) (P.rcut * P.s);
+    P.f_rc2_lo = (float) (P.rcut2 * P.s * P.s) * (1.f - SQ_EPS);
+    P.f_rc2_hi = (float) (P.rcut2 * P.s * P.s) * (1.f + SQ_EPS);
+    P.f_bh2 = (float) P.bh2;
+    P.f_hs = (float) (P.h * P.s);
+    P.f_h2 = P.f_hs * P.f_hs;
+    P.f_boxs = (float) (par.BoxSize * P.s);
+    P.f_invboxs = (float) (1.0 / (par.BoxSize * P.s));
+    P.f_halfs = (float) (P.half * P.s);
+    P.f_range = (float) (SQ_NTAB - 1);
 
     const int64_t n = c->n;
     const uint32_t * targets = nullptr;
@@ -463,16 +663,10 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     SQ_CUDA(cudaMemsetAsync(c->w_accel.p, 0, sizeof(double) * 3 * (size_t) n, c->stream));
     if(pot) SQ_CUDA(cudaMemsetAsync(c->w_pot.p, 0, sizeof(double) * (size_t) n, c->stream));
     SQ_CUDA(cudaEventRecord(c->ev[8], c->stream));
-    const int G = sq_walk_group_width;
-    if(ntargets > 0) {
-        int rc;
-        if(G == 8) rc = pot ? sq_walk_launch<8, true>(c, targets, ntargets, P) : sq_walk_launch<8, false>(c, targets, ntargets, P);
-        else if(G == 16) rc = pot ? sq_walk_launch<16, true>(c, targets, ntargets, P) : sq_walk_launch<16, false>(c, targets, ntargets, P);
-        else rc = pot ? sq_walk_launch<32, true>(c, targets, ntargets, P) : sq_walk_launch<32, false>(c, targets, ntargets, P);
-        SQ_TRY(rc);
-    }
+    if(ntargets > 0)
+        SQ_TRY(pot ? sq_walk_launch<true>(c, targets, ntargets, P) : sq_walk_launch<false>(c, targets, ntargets, P));
     SQ_CUDA(cudaEventRecord(c->ev[9], c->stream));
-    unsigned long long h_stats[4] = {0, 0, 0, 0};
+    unsigned long long h_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     SQ_CUDA(cudaMemcpyAsync(h_stats, c->w_stats.p, sizeof(h_stats), cudaMemcpyDeviceToHost, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));
     float ms = 0;
@@ -482,10 +676,12 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     c->walk_ntargets = ntargets;
     if(stats) {
         stats->ntargets = ntargets;
-        stats->ngroups = (ntargets + G - 1) / G;
+        stats->ngroups = (ntargets + P.gw - 1) / P.gw;
         stats->interactions = (int64_t) h_stats[0];
         stats->list_entries = (int64_t) h_stats[1];
         stats->nodes_tested = (int64_t) h_stats[2];
+        stats->pair_tests = (int64_t) h_stats[3];
+        stats->exact_tests = (int64_t) h_stats[4];
         stats->kernel_ms = ms;
     }
     // TreeUseBH > 1: Barnes-Hut on the first call only (gravshort-tree2.cpp:170-171)

@@ -1,0 +1,39 @@
+#!/usr/bin/env python
+"""GPU box check: total interaction count and acceleration parity of the walk against the reference's own CPU code
+(oracle/_ref) on the bench workload at a size the CPU finishes in seconds (TEST TOOL, not product)."""
+import argparse, json, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import bench, helpers as H
+import shenqi_b200 as sq
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--ngrid", type=int, default=64)
+a = ap.parse_args()
+pos, mass, par = bench.workload(a.ngrid, 2 * a.ngrid)
+n = len(pos); box = par["BoxSize"]
+ctx = sq.Context(0)
+P = sq.Params.defaults(box, 2 * a.ngrid, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
+ctx.set_params(P); ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+a0, _, st0 = ctx.grav_short_tree()
+P.TreeUseBH = 0; ctx.set_params(P); ctx.set_old_accel(a0, None)
+a1, _, st1 = ctx.grav_short_tree()
+meansep = box / a.ngrid
+opar = H.default_params(box, 2 * a.ngrid, n, G=par["G"], TreeUseBH=1, TreeRcut=par["TreeRcut"], GravitySoftening=par["GravitySoftening"], rho0=par["rho0"])
+with H.quiet_stdout():
+    H.r_load(pos, mass, box, ids=np.arange(1, n + 1, dtype=np.uint64)); H.ref().ref_sort_particles(); H.r_tree(0.9)
+    _, _, ids = H.r_sorted_particles()
+    r0, _ = H.r_walk(opar, meansep)
+    _, t0 = H.r_counts(opar, meansep)
+    inv = (ids - 1).astype(np.int64)
+    full = np.zeros((n, 3)); full[:] = a0[inv]
+    opar["TreeUseBH"] = 0
+    # counts first: the walk itself overwrites FullTreeGravAccel (the |a_old| input) on a full tree
+    H.ref().ref_set_accels(H.ptr(full), H.ptr(np.zeros((n, 3))))
+    _, t1 = H.r_counts(opar, meansep)
+    r1, _ = H.r_walk(opar, meansep, fulltree=full, gravpm=np.zeros((n, 3)))
+e0 = H.rel_err(a0[inv], r0); e1 = H.rel_err(a1[inv], r1)
+print(json.dumps({"n": n, "bh": {"gpu": st0.interactions, "ref": int(t0), "median": float(np.median(e0)), "p999": float(np.percentile(e0, 99.9))},
+                  "rel": {"gpu": st1.interactions, "ref": int(t1), "median": float(np.median(e1)), "p999": float(np.percentile(e1, 99.9)),
+                          "pair_tests": st1.pair_tests, "exact_tests": st1.exact_tests}}))

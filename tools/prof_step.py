@@ -31,6 +31,6 @@ for _ in range(a.steps):
     if not a.no_pm:
         ctx.gravpm_force_device()
 tm = ctx.timings()
-print(json.dumps({"n": len(pos), "interactions": st.interactions, "list_entries": st.list_entries, "nodes_tested": st.nodes_tested,
+print(json.dumps({"n": len(pos), "interactions": st.interactions, "list_entries": st.list_entries, "nodes_tested": st.nodes_tested, "pair_tests": st.pair_tests, "exact_tests": st.exact_tests,
                   "ngroups": st.ngroups, "walk_ms": st.kernel_ms, "stages": {f: getattr(tm, f) for f, _ in tm._fields_}}))
 ctx.close()
