@@ -268,3 +268,26 @@ def lattice(ncbrt, box):
 
 def rel_err(a, b):
     return np.linalg.norm(a - b, axis=1) / np.maximum(np.linalg.norm(b, axis=1), 1e-300)
+
+
+def direct_sum_27(pos, box, G, h):
+    """periodic direct sum over 27 images with the spline softening of gravshort2.hpp:332-350
+    (force_direct of libgadget/tests/test_gravity.cpp:133-153); unit masses."""
+    n = len(pos)
+    direct = np.zeros((n, 3))
+    for sx in (-1, 0, 1):
+        for sy in (-1, 0, 1):
+            for sz in (-1, 0, 1):
+                off = np.array([sx, sy, sz]) * box
+                for i0 in range(0, n, 512):
+                    d = off[None, None, :] + pos[i0:i0 + 512, None, :] - pos[None, :, :]
+                    r2 = (d ** 2).sum(-1); r = np.sqrt(r2)
+                    with np.errstate(divide="ignore", invalid="ignore"):
+                        fac = 1 / (r2 * r)
+                        u = r / h
+                        f1 = (10.666666666667 + u * u * (32.0 * u - 38.4)) / h ** 3
+                        f2 = (21.333333333333 - 48.0 * u + 38.4 * u * u - 10.666666666667 * u ** 3 - 0.066666666667 / u ** 3) / h ** 3
+                    fac = np.where(r < h, np.where(u < 0.5, f1, f2), fac)
+                    fac[r2 == 0] = 0
+                    direct[i0:i0 + 512] += -(d * fac[..., None]).sum(1) * G
+    return direct

@@ -1,0 +1,327 @@
+"""CPU tests (no GPU): pin the oracle (oracle/libshenqi_oracle.so, the C restatement) against
+  - the reference's golden Peano-Hilbert keys (libgadget/tests/test_peano.cpp:102),
+  - the reference's own code compiled into oracle/_ref/libshenqi_ref.so (keys, sort order, tree topology and
+    moments, grav_short_tree accelerations and interaction counts, grav_short_pair),
+  - committed golden fixtures generated from that reference build (tests/golden/make_golden_walk.py),
+  - the invariants of libgadget/tests/test_forcetree.cpp:21-169 and the force-accuracy thresholds of
+    libgadget/tests/test_gravity.cpp:155-169,
+and check that the C-ABI library loads, exports every symbol include/shenqi_b200.h declares and refuses to run
+without a CUDA device (there is no CPU fallback)."""
+import ctypes, os, re
+import numpy as np
+import pytest
+from helpers import (ROOT, oracle, ref, o_keys, o_sort, o_tree, o_walk, o_pair, o_cic_paint, o_cic_readout, o_pm_force,
+                     canonical_tree, random_clustered, lattice, rel_err, default_params, r_load, r_sorted_particles, r_tree,
+                     r_walk, r_counts, r_pair, direct_sum_27, ptr, c_i64, c_dbl, NODE_DTYPE)
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+needs_ref = pytest.mark.skipif(ref() is None, reason="reference build (oracle/_ref) not present")
+
+
+# ------------------------------------------------------------------------------------------ keys
+def test_oracle_keys_golden():
+    """libgadget/tests/test_peano.cpp:102-117: 4^3 lattice in a box of 4."""
+    gold = np.load(os.path.join(GOLDEN, "peano_keys_4x4x4.npy"))
+    i = np.arange(64)
+    pos = np.stack([i % 4, (i // 4) % 4, (i // 16) % 4], 1).astype(np.float64)
+    assert np.array_equal(o_keys(pos, 4.0), gold)
+
+
+def test_oracle_keys_hilbert_adjacency():
+    """consecutive keys of a full 8^3 integer lattice are face neighbours (a Hilbert curve), all keys distinct."""
+    L = oracle()
+    n = 8
+    g = np.arange(n)
+    xyz = np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3)
+    keys = np.array([L.sqo_peano_hilbert_key(int(x), int(y), int(z), 3) for x, y, z in xyz], np.uint64)
+    assert len(np.unique(keys)) == n ** 3 and keys.max() == n ** 3 - 1
+    order = np.argsort(keys)
+    step = np.abs(np.diff(xyz[order], axis=0)).sum(1)
+    assert np.all(step == 1)
+
+
+@needs_ref
+def test_oracle_keys_match_reference():
+    """new table-driven routine on powers of two (libgadget/tests/test_peano.cpp:120-128) and random positions."""
+    L, R = oracle(), ref()
+    for i in range(0, 21, 4):
+        for j in range(0, 21, 5):
+            for k in range(0, 21, 3):
+                a = (1 << i, 1 << j, 1 << k)
+                assert L.sqo_peano_hilbert_key(*a, 21) == R.ref_peano_hilbert_key(*a, 21)
+    pos = random_clustered(20000, 250000.0, 3)
+    rk = np.zeros(len(pos), np.uint64)
+    R.ref_peano_keys(ptr(pos), c_i64(len(pos)), c_dbl(250000.0), ptr(rk))
+    assert np.array_equal(o_keys(pos, 250000.0), rk)
+
+
+# ------------------------------------------------------------------------------------------ sort
+def test_oracle_sort_order():
+    """libgadget/tests/test_slotsmanager.cpp:87-115: types non-decreasing, keys non-decreasing within type, checksum kept."""
+    rng = np.random.default_rng(5)
+    n = 5000
+    keys = rng.integers(0, 1 << 62, n, dtype=np.uint64)
+    keys[::7] = keys[0]                       # ties
+    types = rng.integers(0, 6, n).astype(np.uint8)
+    perm = o_sort(keys, types)
+    assert np.array_equal(np.sort(perm), np.arange(n))
+    t, k = types[perm], keys[perm]
+    assert np.all(np.diff(t.astype(int)) >= 0)
+    same = t[1:] == t[:-1]
+    assert np.all(k[1:][same] >= k[:-1][same])
+    assert o_sort(np.zeros(0, np.uint64)).shape == (0,)
+
+
+@needs_ref
+def test_oracle_sort_matches_reference():
+    n, box = 30000, 8.0
+    pos = random_clustered(n, box, 7)
+    ids = np.arange(1, n + 1, dtype=np.uint64)
+    r_load(pos, np.ones(n, np.float32), box, ids)
+    ref().ref_sort_particles()
+    _, _, rid = r_sorted_particles()
+    keys = o_keys(pos, box)
+    perm = o_sort(keys)
+    # identical key sequence; identical permutation wherever keys are distinct
+    assert np.array_equal(keys[perm], keys[(rid - 1).astype(np.int64)])
+    distinct = np.concatenate([[True], np.diff(keys[perm]) != 0]) & np.concatenate([np.diff(keys[perm]) != 0, [True]])
+    assert np.array_equal(ids[perm][distinct], rid[distinct])
+
+
+# ------------------------------------------------------------------------------------------ tree
+def _tree_invariants(nodes, first, pos, mass, box):
+    """libgadget/tests/test_forcetree.cpp:21-169: every particle in exactly one leaf, octant geometry, len halves,
+    mass conservation up the father chain, centre of mass inside the cell."""
+    n = len(pos)
+    ctype = (nodes["flags"] >> 3) & 3
+    leaves = np.nonzero(ctype == 0)[0]
+    seen = np.zeros(n, np.int64)
+    for j in range(8):
+        sel = leaves[nodes["noccupied"][leaves] > j]
+        p = nodes["suns"][sel, j]
+        seen[p] += 1
+        # the particle lies inside its leaf cube
+        d = np.abs(pos[p] - nodes["center"][sel])
+        assert np.all(d <= nodes["len"][sel, None] / 2 * (1 + 1e-12))
+    assert np.all(seen == 1)
+    inner = np.nonzero(ctype == 1)[0]
+    for j in range(8):
+        sel = inner[nodes["suns"][inner, j] >= 0]
+        ch = nodes["suns"][sel, j] - first
+        assert np.all(nodes["len"][ch] == nodes["len"][sel] / 2)
+        assert np.all(nodes["father"][ch] == sel + first)
+        assert np.all(np.abs(np.abs(nodes["center"][ch] - nodes["center"][sel]) - nodes["len"][sel, None] / 4) <= 1e-12 * box)
+    assert abs(nodes["mass"][0] - mass.astype(np.float64).sum()) < 1e-9 * mass.sum()
+    has = nodes["mass"] > 0
+    assert np.all(np.abs(nodes["cofm"][has] - nodes["center"][has]) <= nodes["len"][has, None] / 2 * (1 + 1e-9))
+    # internal mass = sum of children
+    csum = np.zeros(len(nodes))
+    for j in range(8):
+        sel = inner[nodes["suns"][inner, j] >= 0]
+        csum[sel] += nodes["mass"][nodes["suns"][sel, j] - first]
+    assert np.allclose(csum[inner], nodes["mass"][inner], rtol=1e-12)
+
+
+@pytest.mark.parametrize("kind", ["random", "close", "lattice"])
+def test_oracle_tree_invariants(kind):
+    box = 8.0
+    if kind == "random":
+        pos = random_clustered(16 ** 3 * 2, box, 0)
+    elif kind == "close":
+        nc = 16; i = np.arange(nc ** 3)
+        pos = np.stack([4. + (i // nc // nc) / 5000., 4. + ((i // nc) % nc) / 5000., 4. + (i % nc) / 5000.], 1)
+    else:
+        pos = lattice(16, box)
+    mass = (1 + np.random.default_rng(1).random(len(pos))).astype(np.float32)
+    perm = o_sort(o_keys(pos, box))
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    nodes, first = o_tree(spos, smass, box, shortcut=False)
+    _tree_invariants(nodes, first, spos, smass, box)
+
+
+@needs_ref
+@pytest.mark.parametrize("kind", ["random", "zeldovich"])
+def test_oracle_tree_matches_reference(kind):
+    box = 8.0
+    if kind == "random":
+        pos = random_clustered(20000, box, 2)
+    else:
+        rng = np.random.default_rng(4)
+        pos = np.mod(lattice(24, box) + 0.5 * box / 24 + 0.2 * (box / 24) * rng.standard_normal((24 ** 3, 3)), box)
+    n = len(pos)
+    mass = (1 + np.random.default_rng(3).random(n)).astype(np.float32)
+    ids = np.arange(1, n + 1, dtype=np.uint64)
+    r_load(pos, mass, box, ids)
+    ref().ref_sort_particles()
+    spos, smass, sid = r_sorted_particles()
+    rn, rfirst, _ = r_tree(0.9)
+    on, ofirst = o_tree(spos, smass, box)
+    cr = canonical_tree(rn, rfirst, sid.astype(np.int64), box)
+    co = canonical_tree(on, ofirst, sid.astype(np.int64), box)
+    assert np.array_equal(cr[0], co[0]) and np.array_equal(cr[1], co[1])
+    scale = np.abs(cr[2]).max(axis=0)
+    assert (np.abs(cr[2] - co[2]) / scale).max() < 1e-12
+    ref().ref_tree_free()
+
+
+# ------------------------------------------------------------------------------------------ walk
+@needs_ref
+def test_oracle_walk_matches_reference():
+    """grav_short_tree twice (Barnes-Hut, then relative criterion) as libgadget/tests/test_gravity.cpp:237-240;
+    new-vs-old style bound of runtests.cpp:425-426 (1e-5) -- here the port agrees to round-off."""
+    box, n, nmesh = 8.0, 16 ** 3 * 2, 48
+    pos = random_clustered(n, box, 1)
+    mass = np.ones(n, np.float32)
+    meansep = box / round(n ** (1 / 3.))
+    par = default_params(box, nmesh, n, TreeUseBH=1, TreeRcut=7.0)
+    r_load(pos, mass, box, np.arange(1, n + 1, dtype=np.uint64))
+    ref().ref_sort_particles()
+    spos, smass, sid = r_sorted_particles()
+    rn, rfirst, _ = r_tree(0.9)
+    _, rt0 = r_counts(par, meansep)
+    ra0, _ = r_walk(par, meansep)
+    on, ofirst = o_tree(spos, smass, box)
+    oa0, _, _, ot0 = o_walk(on, ofirst, spos, smass, np.zeros(n), par)
+    assert ot0 == rt0
+    assert rel_err(oa0, ra0).max() < 1e-9
+    par2 = dict(par, TreeUseBH=0)
+    ref().ref_set_accels(ptr(ra0), ptr(np.zeros((n, 3))))
+    _, rt1 = r_counts(par2, meansep)
+    ra1, _ = r_walk(par2, meansep, fulltree=ra0, gravpm=np.zeros((n, 3)))
+    oa1, _, _, ot1 = o_walk(on, ofirst, spos, smass, np.linalg.norm(ra0, axis=1) / par["G"], par2)
+    assert ot1 == rt1
+    assert rel_err(oa1, ra1).max() < 1e-9
+    # direct sum: gravshort-pair.c
+    rp, _ = r_pair(par, meansep)
+    op, _ = o_pair(spos, smass, par)
+    assert rel_err(op, rp).max() < 1e-9
+    ref().ref_tree_free()
+
+
+# ------------------------------------------------------------------------------------------ golden fixture
+def golden_walk():
+    return np.load(os.path.join(GOLDEN, "walk_ref.npz"))
+
+
+def test_oracle_against_golden_reference_outputs():
+    """tests/golden/walk_ref.npz holds outputs of the reference's own code (tests/golden/make_golden_walk.py):
+    the oracle must reproduce keys, order, tree cells, moments, interaction counts and accelerations.
+    This is the pin that travels to machines without /root/reference."""
+    g = golden_walk()
+    pos, mass, box = g["pos"], g["mass"], 8.0
+    n = len(pos)
+    keys = o_keys(pos, box)
+    assert np.array_equal(keys, g["keys"])
+    perm = o_sort(keys)
+    assert np.array_equal(keys[perm], keys[(g["sorted_ids"] - 1).astype(np.int64)])
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    nodes, first = o_tree(spos, smass, box)
+    cells, parts, moms = canonical_tree(nodes, first, perm + 1, box)
+    assert np.array_equal(cells, g["cells"]) and np.array_equal(parts, g["leaf_parts"])
+    assert (np.abs(moms - g["moments"]) / np.abs(g["moments"]).max(axis=0)).max() < 1e-12
+    par = default_params(box, 48, n, TreeUseBH=1, TreeRcut=7.0, GravitySoftening=float(g["softening"]))
+    a0, _, _, t0 = o_walk(nodes, first, spos, smass, np.zeros(n), par)
+    assert t0 == int(g["count_bh"])
+    assert rel_err(a0, g["acc_bh"][perm]).max() < 1e-9
+    a1, _, _, t1 = o_walk(nodes, first, spos, smass, np.linalg.norm(g["acc_bh"][perm], axis=1) / par["G"], dict(par, TreeUseBH=0))
+    assert t1 == int(g["count_rel"])
+    assert rel_err(a1, g["acc_rel"][perm]).max() < 1e-9
+    ap, _ = o_pair(spos, smass, par)
+    assert rel_err(ap, g["acc_pair"][perm]).max() < 1e-9
+
+
+def test_oracle_walk_vs_pair_error():
+    """run_gravity_test style (runtests.cpp:286-315): fully open tree == direct sum; default tree within ErrTol."""
+    g = golden_walk()
+    pos, mass, box = g["pos"], g["mass"], 8.0
+    n = len(pos)
+    perm = o_sort(o_keys(pos, box))
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    nodes, first = o_tree(spos, smass, box)
+    par = default_params(box, 48, n, TreeUseBH=1, TreeRcut=7.0, GravitySoftening=float(g["softening"]))
+    ap, _ = o_pair(spos, smass, par)
+    a_open, _, _, _ = o_walk(nodes, first, spos, smass, np.zeros(n), dict(par, BHOpeningAngle=0.0, ErrTolForceAcc=0.0))
+    e = np.abs(np.linalg.norm(a_open, axis=1) / np.linalg.norm(ap, axis=1) - 1)
+    # runtests.cpp:286-287 bounds the error on tree + PM; on the short-range part alone particles whose net
+    # short-range force nearly cancels are noisy (the open tree also sums sources beyond Rcut), so bound the bulk
+    assert np.percentile(e, 95) <= 0.1 and np.median(e) < 1e-3
+    a1, _, _, _ = o_walk(nodes, first, spos, smass, np.linalg.norm(g["acc_bh"][perm], axis=1) / par["G"], dict(par, TreeUseBH=0))
+    e1 = np.abs(np.linalg.norm(a1, axis=1) / np.linalg.norm(a_open, axis=1) - 1)
+    assert e1.mean() <= 1.2 * par["ErrTolForceAcc"]          # runtests.cpp:314-315
+
+
+# ------------------------------------------------------------------------------------------ PM
+def test_oracle_cic_conserves_mass_and_reads_back():
+    box, nmesh, n = 8.0, 16, 3000
+    rng = np.random.default_rng(8)
+    pos = rng.random((n, 3)) * box
+    pos[0] = [0.0, box - 1e-9, box / 2]                     # wrap-around corners
+    mass = (1 + rng.random(n)).astype(np.float32)
+    mesh = o_cic_paint(pos, mass, box, nmesh)
+    assert abs(mesh.sum() - mass.astype(np.float64).sum()) < 1e-9 * mass.sum()
+    assert np.allclose(o_cic_readout(np.ones((nmesh,) * 3), pos, box, nmesh), 1.0, rtol=1e-12)
+    # a linear field is reproduced exactly by trilinear readout away from the periodic seam
+    xs = (np.arange(nmesh) * box / nmesh)[:, None, None] * np.ones((nmesh,) * 3)
+    inner = (pos[:, 0] < box - box / nmesh)
+    assert np.allclose(o_cic_readout(xs, pos, box, nmesh)[inner], pos[inner, 0], rtol=1e-10, atol=1e-10)
+
+
+def test_oracle_tree_plus_pm_vs_direct_sum():
+    """libgadget/tests/test_gravity.cpp:155-169, 197-247: 16^3 particles, box 8, Nmesh 48, Asmth 1.5, Rcut 7:
+    PM + tree against an O(N^2) periodic (27 images) direct sum; maxerr < 3 ErrTol-ish bound on the mean."""
+    box, nmesh = 8.0, 48
+    n = 12 ** 3
+    # clustered set (test_forcetree.cpp:404-430): for a uniform set the 27-image sum lacks the neutralising background
+    pos = random_clustered(n, box, 0)
+    mass = np.ones(n, np.float32)
+    par = default_params(box, nmesh, n, TreeUseBH=1, TreeRcut=7.0)
+    perm = o_sort(o_keys(pos, box))
+    spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+    nodes, first = o_tree(spos, smass, box)
+    a0, _, _, _ = o_walk(nodes, first, spos, smass, np.zeros(n), par)
+    _, gpm = o_pm_force(spos, smass, box, nmesh, 1.5, par["G"])
+    a1, _, _, _ = o_walk(nodes, first, spos, smass, np.linalg.norm(a0 + gpm, axis=1) / par["G"], dict(par, TreeUseBH=0))
+    tot = a1 + gpm
+    direct = direct_sum_27(spos, box, par["G"], 2.8 * par["GravitySoftening"])
+    # metric of test_gravity.cpp:155-169 (check_accns): component error in units of the mean |acceleration component|
+    err = np.abs(tot - direct) / np.abs(direct).mean()
+    assert err.max() < 0.05 and err.mean() < 0.005, (err.max(), err.mean())
+
+
+# ------------------------------------------------------------------------------------------ C ABI
+def declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "shenqi_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(sq_[a-z0-9_]+)\s*\(", hdr)))
+
+
+def test_abi_exports_every_declared_symbol():
+    import shenqi_b200 as sq
+    L = sq.load_library()
+    names = declared_symbols()
+    assert len(names) >= 25
+    for nm in names:
+        assert hasattr(L, nm), "libshenqi_b200.so does not export %s" % nm
+    assert set(sq.api.EXPORTS) <= set(names)
+    assert b"sm_100a" in L.sq_version()
+
+
+def test_abi_struct_sizes_match_reference_layouts():
+    import shenqi_b200 as sq
+    assert sq.NODE_DTYPE.itemsize == 120 and sq.PARTICLE_DTYPE.itemsize == 160     # forcetree.h:38-66, partmanager.h:9-71
+    lay = sq.api.AosLayout()
+    sq.load_library().sq_default_aos_layout(ctypes.byref(lay))
+    assert (lay.stride, lay.off_pos, lay.off_mass, lay.off_fulltreegravaccel, lay.off_gravpm, lay.off_id, lay.off_potential) == (160, 0, 28, 64, 88, 136, 152)
+    if ref() is not None:
+        assert ref().ref_sizeof_particle() == 160 and ref().ref_sizeof_node() == 120
+
+
+def test_no_cpu_fallback():
+    """without a CUDA device the product must fail loudly (SQ_ERR_NO_DEVICE), never compute on the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import shenqi_b200 as sq
+    with pytest.raises(sq.ShenqiError) as e:
+        sq.Context(0)
+    assert "no CPU path" in str(e.value) or "-1" in str(e.value)
