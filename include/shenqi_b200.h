@@ -15,6 +15,7 @@
  *   sq_tree_build            force_tree_full / force_tree_active_moments (libgadget/forcetree.h:127-140)
  *   sq_tree_export_nodes     the struct NODE image other modules walk (libgadget/forcetree.h:38-66)
  *   sq_tree_walk             grav_short_tree (libgadget/gravity.h:89, gravshort-tree2.cpp:141)
+ *   sq_set_walk_raw          the GravTreeParams argument of grav_short_tree_cuda (libgadget/gravshort2.hpp:21-55, 440-443)
  *   sq_pm_force              gravpm_force -> petapm_force (libgadget/gravity.h:86, petapm.cpp:472)
  */
 #ifndef SHENQI_B200_H
@@ -83,6 +84,26 @@ typedef struct sq_tree_info {
     int     geo_mismatch;      /* 1 if some particle's geometric octants differ from its key digits (handled) */
 } sq_tree_info;
 
+/* The parameters of ONE grav_short_tree call exactly as the reference hands them to its GPU hook
+ * grav_short_tree_cuda(): the fields of class GravTreeParams (libgadget/gravshort2.hpp:21-55) and the two
+ * float tables of GravShortTable (libgadget/gravity.h:32-61).  When set, sq_tree_walk uses these instead of
+ * deriving them from sq_params (cellsize = BoxSize/Nmesh, Rcut = TreeRcut*Asmth*cellsize, ...). */
+typedef struct sq_walk_raw {
+    double BoxSize;
+    double cellsize;           /* BoxSize / Nmesh */
+    double Rcut;               /* TreeRcut * Asmth * cellsize */
+    double G;
+    double cbrtrho0;
+    double ForceSoftening;     /* 2.8 * epsilon */
+    double ErrTolForceAcc;
+    double BHOpeningAngle2;    /* already MaxBHOpeningAngle^2 when TreeUseBH == 0 */
+    int TreeUseBH;
+    int ntab;                  /* NGRAVTAB = 512 */
+    const float * force_table; /* shortrange_table[ntab] */
+    const float * pot_table;   /* shortrange_table_potential[ntab] */
+    double table_dx;           /* table step in mesh cells (0.029354...) */
+} sq_walk_raw;
+
 const char * sq_last_error(void);
 const char * sq_version(void);
 
@@ -90,6 +111,8 @@ int sq_ctx_create(sq_ctx ** ctx, int device);
 void sq_ctx_destroy(sq_ctx * ctx);
 int sq_set_params(sq_ctx * ctx, const sq_params * par);
 int sq_sync(sq_ctx * ctx);
+/* raw == NULL clears the override. */
+int sq_set_walk_raw(sq_ctx * ctx, const sq_walk_raw * raw);
 
 /* ---- particles ------------------------------------------------------------------------------- */
 void sq_default_aos_layout(sq_aos_layout * lay);

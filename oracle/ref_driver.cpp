@@ -218,6 +218,10 @@ static struct gravshort_tree_params ref_make_treepar(double ErrTolForceAcc, doub
 }
 
 /* grav_short_tree on all particles (tree must be built). accel: N x 3 (already x G). Returns seconds. */
+/* UseGPU argument of grav_short_tree: honoured only by builds with USE_CUDA (tests/dropin links the B200 hook) */
+static int RefUseGPU = 0;
+void ref_set_use_gpu(int v) { RefUseGPU = v; }
+
 double ref_grav_short_tree(int Nmesh, double Asmth, double G, double ErrTolForceAcc, double BHOpeningAngle,
         double MaxBHOpeningAngle, int TreeUseBH, double Rcut, double FracSoft, double MeanSeparation,
         int windowtype, double rho0, double * accel)
@@ -227,7 +231,7 @@ double ref_grav_short_tree(int Nmesh, double Asmth, double G, double ErrTolForce
     gravshort_set_softenings(MeanSeparation);
     ActiveParticles act = init_empty_active_particles(PartManager);
     double t0 = MPI_Wtime();
-    grav_short_tree(&act, &pm, &RefTree, (MyFloat (*)[3]) accel, rho0, 0, false);
+    grav_short_tree(&act, &pm, &RefTree, (MyFloat (*)[3]) accel, rho0, 0, RefUseGPU != 0);
     return MPI_Wtime() - t0;
 }
 

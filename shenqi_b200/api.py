@@ -61,7 +61,7 @@ class Timings(ctypes.Structure):
                                      "pm_paint_ms", "pm_fft_ms", "pm_transfer_ms", "pm_readout_ms")] + [("kernel_launches", c_i64)]
 
 
-EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_sync", "sq_default_aos_layout",
+EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_set_walk_raw", "sq_sync", "sq_default_aos_layout",
            "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
            "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak"]

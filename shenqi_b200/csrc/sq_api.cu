@@ -132,6 +132,20 @@ int sq_set_params(sq_ctx * c, const sq_params * par)
     return SQ_OK;
 }
 
+int sq_set_walk_raw(sq_ctx * c, const sq_walk_raw * raw)
+{
+    if(!c) return SQ_ERR_ARG;
+    if(!raw) { c->have_raw = false; return SQ_OK; }
+    if(raw->ntab != SQ_NTAB || !raw->force_table || !raw->pot_table) { sq_set_error("sq_set_walk_raw: tables of %d entries expected (NGRAVTAB)", SQ_NTAB); return SQ_ERR_ARG; }
+    if(!(raw->cellsize > 0) || !(raw->BoxSize > 0) || !(raw->G > 0) || !(raw->table_dx > 0)) { sq_set_error("sq_set_walk_raw: BoxSize, cellsize, G and table_dx must be positive"); return SQ_ERR_ARG; }
+    c->raw = *raw;
+    memcpy(c->raw_ft, raw->force_table, sizeof(float) * SQ_NTAB);
+    memcpy(c->raw_pt, raw->pot_table, sizeof(float) * SQ_NTAB);
+    c->raw.force_table = c->raw_ft; c->raw.pot_table = c->raw_pt;
+    c->have_raw = true;
+    return SQ_OK;
+}
+
 int sq_sync(sq_ctx * c)
 {
     if(!c) return SQ_ERR_ARG;

@@ -85,6 +85,9 @@ struct sq_ctx {
     cudaEvent_t ev[16] = {};
     sq_params par = {};
     bool have_params = false;
+    sq_walk_raw raw = {};
+    bool have_raw = false;
+    float raw_ft[SQ_NTAB], raw_pt[SQ_NTAB];
     int64_t kernel_launches = 0;
     sq_timings tm = {};
 

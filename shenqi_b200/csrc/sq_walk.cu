@@ -560,7 +560,10 @@ static int sq_walk_table(sq_ctx * c)
     float ft[SQ_NTAB], pt[SQ_NTAB];
     for(int i = 0; i < SQ_NTAB; i++) {
         const double u = h_sr_x[i] * 0.5 / c->par.Asmth;
-        if(c->par.WindowType == 1) {
+        if(c->have_raw) {
+            ft[i] = c->raw_ft[i];
+            pt[i] = c->raw_pt[i];
+        } else if(c->par.WindowType == 1) {
             ft[i] = (float) h_sr_force[i];
             pt[i] = (float) h_sr_pot[i];
         } else {
@@ -628,11 +631,22 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     P.relative = par.TreeUseBH == 0;
     P.bh2 = par.BHOpeningAngle * par.BHOpeningAngle;
     if(par.TreeUseBH == 0) P.bh2 = par.MaxBHOpeningAngle * par.MaxBHOpeningAngle;
+    double table_dx = SQ_SHORTRANGE_DX;
+    double cell = cellsize;
+    if(c->have_raw) {
+        // the reference's own GravTreeParams (gravshort2.hpp:21-55), as handed to grav_short_tree_cuda
+        const sq_walk_raw & R = c->raw;
+        cell = R.cellsize; table_dx = R.table_dx;
+        P.box = R.BoxSize; P.half = 0.5 * R.BoxSize;
+        P.rcut = R.Rcut; P.rcut2 = R.Rcut * R.Rcut;
+        P.h = R.ForceSoftening; P.G = R.G; P.cbrtrho0 = R.cbrtrho0; P.errtol = R.ErrTolForceAcc;
+        P.relative = R.TreeUseBH == 0; P.bh2 = R.BHOpeningAngle2;
+    }
     // scaled system of the FP32 tiers: 1 length unit = one step of the split table, 1 mass unit = mean tree particle
-    P.s = 1.0 / (cellsize * SQ_SHORTRANGE_DX);
+    P.s = 1.0 / (cell * table_dx);
     const double munit = (c->tree_total_mass > 0 && c->tree_np > 0) ? c->tree_total_mass / (double) c->tree_np : 1.0;
     P.minv = 1.0 / munit;
-    P.Ka = par.G * munit * P.s * P.s;
+    P.Ka = P.G * munit * P.s * P.s;
     P.Kp = munit * P.s;
     P.gw = sq_walk_group_width;
     P.f_rcut = (float) (P.rcut * P.s);
@@ -641,8 +655,8 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     P.f_bh2 = (float) P.bh2;
     P.f_hs = (float) (P.h * P.s);
     P.f_h2 = P.f_hs * P.f_hs;
-    P.f_boxs = (float) (par.BoxSize * P.s);
-    P.f_invboxs = (float) (1.0 / (par.BoxSize * P.s));
+    P.f_boxs = (float) (P.box * P.s);
+    P.f_invboxs = (float) (1.0 / (P.box * P.s));
     P.f_halfs = (float) (P.half * P.s);
     P.f_range = (float) (SQ_NTAB - 1);
 
@@ -685,6 +699,6 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
         stats->kernel_ms = ms;
     }
     // TreeUseBH > 1: Barnes-Hut on the first call only (gravshort-tree2.cpp:170-171)
-    if(c->par.TreeUseBH > 1) c->par.TreeUseBH = 0;
+    if(c->par.TreeUseBH > 1 && !c->have_raw) c->par.TreeUseBH = 0;
     return SQ_OK;
 }

@@ -22,7 +22,7 @@ def ctx():
 
 def make_params(box, nmesh, n, **kw):
     import shenqi_b200 as sq
-    soft = (box / round(n ** (1 / 3.))) / 30.
+    soft = kw.pop("GravitySoftening", (box / round(n ** (1 / 3.))) / 30.)
     return sq.Params.defaults(box, nmesh, soft, **kw)
 
 
@@ -352,3 +352,32 @@ def test_tree_plus_pm_vs_direct_sum(ctx):
     # for this particle set the reference algorithm itself reaches max 0.023 / mean 0.0025 of the mean acceleration
     # (the test_gravity.cpp:165-166 bounds 3 ErrTol / 0.8 ErrTol are for its own mt19937 sample); sanity bounds:
     assert err.max() < 0.05 and err.mean() < 0.005, (err.max(), err.mean())
+
+
+def test_golden_reference_fixture(ctx):
+    """tests/golden/walk_ref.npz = outputs of the reference's own code (tests/golden/make_golden_walk.py): keys, sort
+    order, tree cells, interaction counts (bit-exact) and accelerations (median <= 1e-5, p99.9 <= 1e-4)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "walk_ref.npz"))
+    pos, mass, box = g["pos"], g["mass"], 8.0
+    n = len(pos)
+    P = make_params(box, 48, n, TreeUseBH=1, TreeRcut=7.0, GravitySoftening=float(g["softening"]))
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    assert np.array_equal(ctx.keys(), g["keys"])
+    sk, perm = ctx.sorted_keys_perm()
+    assert np.array_equal(sk, g["keys"][(g["sorted_ids"] - 1).astype(np.int64)])
+    info = ctx.tree_build()
+    nodes, first = ctx.tree_nodes(firstnode=n, upload_order=True)
+    cells, parts, moms = canonical_tree(nodes, first, np.arange(1, n + 1), box)
+    assert np.array_equal(cells, g["cells"]) and np.array_equal(parts, g["leaf_parts"])
+    assert (np.abs(moms - g["moments"]) / np.abs(g["moments"]).max(axis=0)).max() < 1e-12
+    a0, _, st0 = ctx.grav_short_tree()
+    assert st0.interactions == int(g["count_bh"])
+    assert_accel_parity(a0, g["acc_bh"])
+    P.TreeUseBH = 0
+    ctx.set_params(P)
+    ctx.set_old_accel(g["acc_bh"], None)
+    a1, _, st1 = ctx.grav_short_tree()
+    assert st1.interactions == int(g["count_rel"])
+    assert_accel_parity(a1, g["acc_rel"])
