@@ -6,42 +6,55 @@
 // GravTreeOutput::postprocess (gravshort2.hpp:88-107).
 //
 // Design (not the reference's thread-per-particle depth-first walk):
-//   * One warp walks the tree for a GROUP of G Peano-Hilbert-adjacent active particles (G = 32, 16, 8;
-//     the 32/G lane slices of a target split the interaction list between them).
-//   * The warp shares ONE node stack and ONE interaction list, both in shared memory.  A stack entry is
-//     (node, mask): mask = the targets of the group that reach this node, i.e. opened every ancestor.
-//     Per step the warp pops up to 32 entries, one per lane; node records come in as coalesced 128-bit
-//     loads (children of a node are contiguous).
-//   * Every (target, node) decision is the reference's own (discard: r2 vs Rcut and the Rcut+len/2 box;
-//     open: relative criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle, inside-0.6-len box), but it is
-//     reached in three tiers so that FP64 is the exception:
-//       1. group tier (FP32 interval arithmetic over the group's bounding box and its min/max |a_old|):
-//          if both ends of the interval give the same class, the whole mask is discarded / accepted /
-//          opened at once;
-//       2. target tier (FP32, coordinates relative to the group centre in units of the split-table
-//          spacing, masses in units of the mean particle mass): the class is evaluated at both ends of
-//          the rounding-error interval of (r2, max-axis distance); equal -> decided;
-//       3. exact tier: the reference's FP64 expressions with per-target NEAREST() for the pairs whose
-//          interval straddles a threshold, and for nodes half a box away from the group.
-//     The decision function is monotone in (r2, emax), so equal classes at the interval ends prove the
-//     FP64 class.  The interaction count therefore equals the reference's exactly.
-//   * Accepted nodes and the particles of opened leaves go to the interaction list with their masks;
-//     children are pushed with the open mask.
-//   * Evaluation is FP32: rsqrt, spline softening (rare, FP64), the erfc/"exact" split factor from a
-//     shared-memory-resident table of (value at mid-point offset, slope) pairs -> one 64-bit LDS + one FMA.
-//     Distances are already in table units, so the table coordinate costs nothing.  Partial sums are
-//     carried in FP32 for one list flush (<= LIST_CAP entries) and then added to FP64 accumulators.
+//   * One warp walks the tree for a GROUP of 32 Peano-Hilbert-adjacent active particles with ONE node stack in
+//     shared memory.  A stack entry is (node, mask): mask = the targets of the group that reach this node, i.e.
+//     opened every ancestor.  Per step the warp pops up to 32 entries, one node per lane (three 128-bit loads).
+//   * Every (target, node) decision is the reference's own (discard: the Rcut + len/2 box; open: relative
+//     criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle, inside-0.6-len box), reached in tiers so that FP64 is
+//     the exception:
+//       1. group tier (FP32 interval arithmetic over the group's bounding box and its min/max |a_old|);
+//       1b. keep/discard for boundary nodes by BUCKET MASKS: per axis the targets are binned into 64 buckets over
+//          the group's extent and S[i] = mask of the targets in buckets below i is tabulated once per group;
+//          the targets inside [c - eff, c + eff] are then two table reads per bound, exact up to the targets in
+//          the two boundary buckets, which fall to tier 2;
+//       2. target tier (FP32, coordinates relative to the group centre in units of the split-table step, masses in
+//          units of the mean particle mass): the class is evaluated at both ends of the rounding-error interval
+//          of (r2, max-axis distance); equal -> decided;
+//       3. exact tier: the reference's FP64 expressions with per-target NEAREST() for the pairs whose interval
+//          straddles a threshold, and for nodes half a box away from the group.
+//     The decision function is monotone in (r2, emax), so equal classes at the interval ends prove the FP64
+//     class.  The interaction count therefore equals the reference's exactly.
+//   * Accepted nodes and the particles of opened leaves go to FOUR interaction lists, one per OCTET of targets
+//     (lanes 8q..8q+7), each with an 8-bit mask: an octet's bounding box is much smaller than the group's, so
+//     the masked evaluation wastes fewer lanes (62 % useful instead of 41 %) while the walk is still shared by 32
+//     targets.  The four octets evaluate their own lists in lock step: one 128-bit LDS with one address per
+//     quarter warp costs the same as a warp-wide broadcast (measured, tools/ubench).
+//   * Evaluation is FP32: rsqrt, the erfc/"exact" split factor from a shared-memory table REPLICATED 16x so that
+//     every lane of a half warp reads its own bank pair (conflict-free: 2.2 clk per lookup instead of 4.9,
+//     measured).  Distances are already in table units, so the table coordinate costs nothing.  Sources that
+//     may come within the softening length of a target (inside the group's box grown by h), and everything when
+//     the periodic image can differ per pair (tiny boxes), go to a short "near" list evaluated by a careful
+//     loop (spline softening gravshort2.hpp:332-350, self pair r = 0, per-pair wrap); the fast loop has neither.
+//     Partial sums are FP32 for one list flush (<= 64 entries), then added to FP64 accumulators.
 //   * Epilogue = postprocess: x G, potential self terms; results written in sorted order.
 #include "sq_common.cuh"
 #include "shortrange_table.h"
 #include <math.h>
 
-#define WALK_WARPS 8
+#define WALK_WARPS 16
 #define WALK_THREADS (WALK_WARPS * 32)
-#define STACK_CAP 512
+#define STACK_CAP 384
 #define STACK_RESERVE 160   /* 7 siblings x 22 levels: room a depth-first descent can always need */
-#define LIST_CAP 128        /* multiple of 4 */
+#define OL_CAP 64           /* entries per octet list (multiple of 4, >= 32) */
+#define NEAR_CAP 32
+#define NBUCK 64            /* buckets per axis over the group's extent */
+#define NCUM (NBUCK + 5)
+#define TAB_ROWS (SQ_NTAB + 1)
+#define TAB_COPIES 16
+#define TAB_BYTES (TAB_ROWS * TAB_COPIES * 8)
 #define SQ_EPS 4e-6f        /* relative slack on every FP32 threshold (>> 2^-24 rounding chains) */
+#define SQ_FAR 3.0e4f       /* padding entries: far beyond the table, zero mask */
+#define SQ_MAGIC 12582912.f /* 1.5 * 2^23: adding it rounds to the nearest integer, kept in the mantissa */
 
 struct sq_walk_par {
     // exact tier (reference expressions, FP64)
@@ -50,24 +63,42 @@ struct sq_walk_par {
     double s, minv, Ka, Kp;       // accel = Ka * sum, potential = Kp * sum (+ self terms)
     double G, cbrtrho0;
     int relative;                 // TreeUseBH == 0
-    int gw;                       // targets per warp: 32, 16 or 8
+    int gw;                       // targets per warp: 32, 16 or 8 (lanes beyond stay idle)
     // FP32 tiers (table units)
     float f_rcut, f_rc2_lo, f_rc2_hi, f_bh2, f_h2, f_hs, f_boxs, f_invboxs, f_halfs, f_range;
 };
 
 struct sq_walk_warp_smem {
-    float4 tgt[32];               // x, y, z relative to the group centre (table units), w = errtol*|a_old| scaled
+    float4 ol[4][OL_CAP];         // octet interaction lists: x, y, z relative to the group centre (table units), mass
+    float4 nl[NEAR_CAP];          // near list (careful loop)
+    float4 tgt[32];               // targets: x, y, z, errtol*|a_old| scaled
     int2 stack[STACK_CAP];
-    float4 lst[LIST_CAP];
-    unsigned lmask[LIST_CAP];
+    unsigned nm[NEAR_CAP];
+    unsigned cum[3][NCUM + 3];    // bucket prefix masks S[i] = targets with bucket < i - 1
+    unsigned char om[4][OL_CAP];  // 8-bit masks of the octet lists
     int s_end[32], s_first[32];
     unsigned s_mask[32];
 };
 
+__device__ __forceinline__ float2 sq_lds_f2(unsigned addr)
+{
+    float2 v;       // only used on the split table, constant after the kernel prologue
+    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+// one MUFU.RSQ (the caller keeps the argument away from 0 and denormals)
+__device__ __forceinline__ float sq_rsqrt(float x)
+{
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // spline-softened force and potential factors, gravshort2.hpp:332-350 (FP64: rare branch).
 // r, h in table units; returns (fac, facpot) per unit mass in the scaled system.
-__device__ __noinline__ float2 sq_soft_kernel(float r, double h)
+__device__ __noinline__ float2 sq_soft_kernel(float r, float hf)
 {
+    const double h = (double) hf;
     const double h_inv = 1.0 / h;
     const double h3_inv = h_inv * h_inv * h_inv;
     const double u = (double) r * h_inv;
@@ -81,124 +112,6 @@ __device__ __noinline__ float2 sq_soft_kernel(float r, double h)
     }
     return make_float2((float) f, (float) (h_inv * wp));
 }
-
-template <bool POT>
-struct sq_walk_acc {
-    float ax, ay, az, ap;
-    double dax, day, daz, dap;
-};
-
-__device__ __forceinline__ float2 sq_lds_f2(unsigned addr)
-{
-    float2 v;
-    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ float4 sq_lds_f4(unsigned addr)
-{
-    float4 v;
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
-    return v;
-}
-// one MUFU.RSQ (the caller keeps the argument away from 0 and denormals)
-__device__ __forceinline__ float sq_rsqrt(float x)
-{
-    float y;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-
-// Evaluate list entries [0, n) for this lane's target (slice sl of S takes the 4-entry blocks sl, sl+S, ...).
-template <bool POT, bool WRAP>
-__device__ __forceinline__ void sq_walk_flush(sq_walk_warp_smem & W, int n, unsigned tab_biased,
-                                              const sq_walk_par & P, float tx, float ty, float tz, int tl, int sl, int S,
-                                              sq_walk_acc<POT> & A)
-{
-    const int nb = (n + 3) >> 2;
-    {
-        const int pad = (nb << 2) - n;
-        if((int) sq_lane() < pad) W.lmask[n + sq_lane()] = 0u;
-    }
-    __syncwarp();
-    const unsigned lbit = 1u << tl;
-    const uint4 * mk4 = reinterpret_cast<const uint4 *>(W.lmask);
-    const float h2 = P.f_h2;
-    for(int b = sl; b < nb; b += S) {
-        const uint4 mk = mk4[b];
-        unsigned soft = 0;
-        #pragma unroll
-        for(int j = 0; j < 4; j++) {
-            const float4 s = W.lst[4 * b + j];
-            const unsigned m = j == 0 ? mk.x : (j == 1 ? mk.y : (j == 2 ? mk.z : mk.w));
-            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
-            if(WRAP) {
-                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
-                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
-                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
-            }
-            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-            const bool on = (m & lbit) != 0u;
-            const bool far = r2 >= h2;
-            const float mm = (on && far) ? s.w : 0.f;
-            if(on && !far) soft |= 1u << j;
-            // softened pairs (r2 < h2) take the slow path below; clamping keeps rsqrt finite for them
-            const float rinv = sq_rsqrt(fmaxf(r2, h2));
-            // table coordinate: distances are in table units.  xq = r - 1/2; round-to-nearest of xq = floor(r)
-            // (gravity.h:50-60: i = r/cellsize/dx, zero beyond the table, linear interpolation)
-            const float xq = fminf(fmaf(r2, rinv, -0.5f), 511.f);
-            const float t = xq + 12582912.f;
-            const float d = xq - (t - 12582912.f);
-            const unsigned off = (unsigned) __float_as_int(t) << 4;
-            const float rinv2 = rinv * rinv;
-            if(POT) {
-                const float4 w = sq_lds_f4(tab_biased + off);
-                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
-                A.ax = fmaf(dx, fac, A.ax);
-                A.ay = fmaf(dy, fac, A.ay);
-                A.az = fmaf(dz, fac, A.az);
-                A.ap = fmaf(-mm * rinv, fmaf(d, w.w, w.z), A.ap);
-            } else {
-                const float2 w = sq_lds_f2(tab_biased + off);
-                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
-                A.ax = fmaf(dx, fac, A.ax);
-                A.ay = fmaf(dy, fac, A.ay);
-                A.az = fmaf(dz, fac, A.az);
-            }
-        }
-        // softened pairs (r < 2.8 eps), including the target meeting itself in its own leaf (r = 0)
-        while(soft) {
-            const int j = __ffs(soft) - 1;
-            soft &= soft - 1;
-            const float4 s = W.lst[4 * b + j];
-            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
-            if(WRAP) {
-                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
-                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
-                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
-            }
-            const float r = sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
-            const float2 sf = sq_soft_kernel(r, (double) P.f_hs);
-            if(r < 511.f) {
-                const float fl = floorf(r);
-                const float dd = (r - fl) - 0.5f;
-                const float4 w = sq_lds_f4(tab_biased + ((0x4B400000u + (unsigned) (int) fl) << 4));
-                const float fac = s.w * sf.x * fmaf(dd, w.y, w.x);
-                A.ax = fmaf(dx, fac, A.ax);
-                A.ay = fmaf(dy, fac, A.ay);
-                A.az = fmaf(dz, fac, A.az);
-                if(POT) A.ap = fmaf(s.w * sf.y, fmaf(dd, w.w, w.z), A.ap);
-            }
-        }
-    }
-    A.dax += (double) A.ax; A.day += (double) A.ay; A.daz += (double) A.az;
-    A.ax = A.ay = A.az = 0.f;
-    if(POT) { A.dap += (double) A.ap; A.ap = 0.f; }
-}
-
-// Node constants of the FP32 tiers (one node per lane)
-struct sq_node_f {
-    float cmx, cmy, cmz, cx, cy, cz;
-};
 
 // exact tier: the reference's FP64 test for one (target, node)
 struct sq_exact_par { double box, half, rcut, rcut2, bh2; int relative; };
@@ -225,33 +138,135 @@ __device__ __noinline__ int sq_exact_class(const double4 M, const double4 C, dou
     return 1;
 }
 
+// bucket of coordinate x (monotone non-decreasing in x): 0 below the group's extent, 1..NBUCK inside, NBUCK+1 above
+__device__ __forceinline__ int sq_bucket(float x, float inv, float off)
+{
+    return __float2int_rz(fminf(fmaxf(fmaf(x, inv, off), 0.f), (float) (NBUCK + 1)));
+}
+
+// ---- fast evaluation: the four octets run their own lists in lock step (lane = target 8q + lane%8).
+// Every genuine entry is farther than the softening length from every target of the group (the others are in
+// the near list), padding entries are SQ_FAR away, so r2 > 0 and no softening / wrap test is needed here.
+// Table: (gravity.h:50-60) i = floor(r), linear interpolation, zero from row 511 on.
+//   !POT: row i = (value at the middle of [i, i+1], slope); row 511 = (0, 0)
+//    POT: row i = (force[i], potential[i]); rows i and i+1 are read; the r < 511 test zeroes the tail
 template <bool POT>
-__global__ void __launch_bounds__(WALK_THREADS, 3)
+__device__ __forceinline__ void sq_eval_octets(const sq_walk_warp_smem & W, int nmax4, unsigned tabaddr, float tx, float ty, float tz,
+                                               int q, unsigned bit0, float & ax, float & ay, float & az, float & ap)
+{
+    const float4 * lst = W.ol[q];
+    const unsigned * mk = reinterpret_cast<const unsigned *>(W.om[q]);
+    const int nb = nmax4 >> 2;
+    for(int b = 0; b < nb; b++) {
+        const unsigned m4 = mk[b];
+        #pragma unroll
+        for(int j = 0; j < 4; j++) {
+            const float4 s = lst[4 * b + j];
+            const float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            const bool on = (m4 & (bit0 << (8 * j))) != 0u;
+            const float rinv = sq_rsqrt(r2);
+            // xq = r - 1/2; round-to-nearest of xq = floor(r); d = r - floor(r) - 1/2
+            const float xq = fminf(fmaf(r2, rinv, -0.5f), 511.f);
+            const float t = xq + SQ_MAGIC;
+            const float d = xq - (t - SQ_MAGIC);
+            const unsigned addr = ((unsigned) __float_as_int(t) << 7) + tabaddr;
+            const float rinv2 = rinv * rinv;
+            if(POT) {
+                const float2 e0 = sq_lds_f2(addr), e1 = sq_lds_f2(addr + 128);
+                const float fr = d + 0.5f;
+                const float wf = fmaf(fr, e1.x - e0.x, e0.x), wp = fmaf(fr, e1.y - e0.y, e0.y);
+                const float mm = (on && r2 < 261121.f) ? s.w : 0.f;
+                const float fac = (mm * rinv2) * (rinv * wf);
+                ax = fmaf(dx, fac, ax);
+                ay = fmaf(dy, fac, ay);
+                az = fmaf(dz, fac, az);
+                ap = fmaf(-mm * rinv, wp, ap);
+            } else {
+                const float2 w = sq_lds_f2(addr);
+                const float mm = on ? s.w : 0.f;
+                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
+                ax = fmaf(dx, fac, ax);
+                ay = fmaf(dy, fac, ay);
+                az = fmaf(dz, fac, az);
+            }
+        }
+    }
+}
+
+// ---- careful evaluation of the near list (lane = target, entries broadcast): softened pairs (r < 2.8 eps),
+// the target meeting itself in its own leaf (r = 0, as in the reference), per-pair periodic wrap.
+template <bool POT>
+__device__ __forceinline__ void sq_eval_near(const sq_walk_warp_smem & W, int nn, unsigned tabrow0, const sq_walk_par & P, bool pairwrap,
+                                             float tx, float ty, float tz, unsigned lane, float & ax, float & ay, float & az, float & ap)
+{
+    for(int k = 0; k < nn; k++) {
+        const float4 s = W.nl[k];
+        const unsigned m = W.nm[k];
+        if((m >> lane) & 1u) {
+            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+            if(pairwrap) {
+                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
+                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
+                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
+            }
+            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            float r, fac, facpot;
+            if(r2 >= P.f_h2) {
+                const float rinv = sq_rsqrt(r2);
+                r = r2 * rinv; fac = rinv * rinv * rinv; facpot = -rinv;
+            } else {
+                r = sqrtf(r2);
+                const float2 sf = sq_soft_kernel(r, P.f_hs);
+                fac = sf.x; facpot = sf.y;
+            }
+            if(r < 511.f) {
+                const float fl = floorf(r);
+                const float fr = r - fl;
+                const unsigned addr = tabrow0 + ((unsigned) (int) fl << 7);
+                float wf, wp = 0.f;
+                if(POT) {
+                    const float2 e0 = sq_lds_f2(addr), e1 = sq_lds_f2(addr + 128);
+                    wf = fmaf(fr, e1.x - e0.x, e0.x); wp = fmaf(fr, e1.y - e0.y, e0.y);
+                } else {
+                    const float2 w = sq_lds_f2(addr);
+                    wf = fmaf(fr - 0.5f, w.y, w.x);
+                }
+                const float f = s.w * fac * wf;
+                ax = fmaf(dx, f, ax);
+                ay = fmaf(dy, f, ay);
+                az = fmaf(dz, f, az);
+                if(POT) ap = fmaf(s.w * facpot, wp, ap);
+            }
+        }
+    }
+}
+
+template <bool POT>
+__global__ void __launch_bounds__(WALK_THREADS, 1)
 sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl, const int4 * __restrict__ lk,
                const double * __restrict__ spos, const float * __restrict__ smass,
                const double * __restrict__ tpos, const float * __restrict__ tmass, const double * __restrict__ toldacc,
-               const uint32_t * __restrict__ targets, long long ntargets, const float4 * __restrict__ gtab,
+               const uint32_t * __restrict__ targets, long long ntargets, const float2 * __restrict__ gtab,
                double * __restrict__ accel, double * __restrict__ pot, unsigned long long * __restrict__ stats,
                int * __restrict__ group_counter, const sq_walk_par P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4 * tab = reinterpret_cast<float4 *>(smem_raw);
-    sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + SQ_NTAB * sizeof(float4));
-    for(int i = threadIdx.x; i < SQ_NTAB; i += blockDim.x)
-        tab[i] = gtab[i];
+    float2 * tab = reinterpret_cast<float2 *>(smem_raw);
+    sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + TAB_BYTES);
+    // 16 copies of every table row side by side: copy c of row i at byte i*128 + c*8
+    for(int i = threadIdx.x; i < TAB_ROWS * TAB_COPIES; i += blockDim.x)
+        tab[i] = gtab[i / TAB_COPIES];
     const unsigned lane = sq_lane();
     sq_walk_warp_smem & W = Wall[threadIdx.x >> 5];
-    for(int i = lane; i < LIST_CAP; i += 32) {
-        W.lst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        W.lmask[i] = 0u;
-    }
     __syncthreads();
-    // table addresses biased so that the mantissa bits of (x + 1.5*2^23) index them directly
-    const unsigned tab_biased = (unsigned) __cvta_generic_to_shared(tab) - (0x4B400000u << 4);
+    const unsigned tabrow0 = (unsigned) __cvta_generic_to_shared(tab) + (lane & 15u) * 8u;
+    // biased so that the mantissa bits of (x + 1.5*2^23) index the rows directly
+    const unsigned tabaddr = tabrow0 - (0x4B400000u << 7);
+    const int q = (int) (lane >> 3);
+    const unsigned bit0 = 1u << (lane & 7u);
 
     const int G = P.gw;
-    const int S = 32 / G;
-    const int tl = lane & (G - 1), sl = lane / G;
     const long long ngroups = (ntargets + G - 1) / G;
     unsigned long long st_int = 0, st_ent = 0, st_tst = 0, st_pair = 0, st_exact = 0;
 
@@ -262,11 +277,11 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         if(g >= ngroups) break;
         const long long t0 = g * G;
         const int nt = (int) ((ntargets - t0) < G ? (ntargets - t0) : G);
-        const bool valid = tl < nt;
+        const bool valid = (int) lane < nt;
         long long tidx = 0;
         double px = 0, py = 0, pz = 0, aold = 0;
         if(valid) {
-            tidx = targets ? (long long) targets[t0 + tl] : (t0 + tl);
+            tidx = targets ? (long long) targets[t0 + lane] : (t0 + lane);
             px = tpos[3 * tidx]; py = tpos[3 * tidx + 1]; pz = tpos[3 * tidx + 2];
             aold = P.errtol * toldacc[tidx];
         }
@@ -292,167 +307,188 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         const float ta = P.relative ? (float) (aold * ascale) : __int_as_float(0x7f800000);
         const float ta_lo = P.relative ? (float) (amin * ascale) * (1.f - SQ_EPS) : __int_as_float(0x7f800000);
         const float ta_hi = P.relative ? (float) (amax * ascale) * (1.f + SQ_EPS) : __int_as_float(0x7f800000);
-        const float tx = (float) ((px - gcx) * P.s), ty = (float) ((py - gcy) * P.s), tz = (float) ((pz - gcz) * P.s);
+        // idle lanes sit far away so that they never see r = 0
+        const float tx = valid ? (float) ((px - gcx) * P.s) : 2.f * SQ_FAR;
+        const float ty = valid ? (float) ((py - gcy) * P.s) : 2.f * SQ_FAR;
+        const float tz = valid ? (float) ((pz - gcz) * P.s) : 2.f * SQ_FAR;
         __syncwarp();
-        if(sl == 0) W.tgt[tl] = make_float4(tx, ty, tz, ta);
+        W.tgt[lane] = make_float4(tx, ty, tz, ta);
+        // ---- bucket prefix masks, per axis: S[i] = targets whose bucket is below i - 1
+        const float bwx = fmaxf(ghx, 1e-3f), bwy = fmaxf(ghy, 1e-3f), bwz = fmaxf(ghz, 1e-3f);
+        const float invx = (0.999f * NBUCK) / (2.f * bwx), invy = (0.999f * NBUCK) / (2.f * bwy), invz = (0.999f * NBUCK) / (2.f * bwz);
+        const float offx = fmaf(bwx, invx, 1.f), offy = fmaf(bwy, invy, 1.f), offz = fmaf(bwz, invz, 1.f);
+        // a bound is resolved to +-1 bucket only while the FP32 uncertainty stays below 0.9 bucket widths
+        const float wmin = 0.9f / fmaxf(invx, fmaxf(invy, invz));
+        for(int i = lane; i < 3 * (NCUM + 3); i += 32)
+            (&W.cum[0][0])[i] = 0u;
+        __syncwarp();
+        if(valid) {
+            atomicOr(&W.cum[0][sq_bucket(tx, invx, offx) + 2], 1u << lane);
+            atomicOr(&W.cum[1][sq_bucket(ty, invy, offy) + 2], 1u << lane);
+            atomicOr(&W.cum[2][sq_bucket(tz, invz, offz) + 2], 1u << lane);
+        }
+        __syncwarp();
+        #pragma unroll
+        for(int a = 0; a < 3; a++) {
+            const int i0 = 3 * (int) lane;
+            unsigned v0 = 0, v1 = 0, v2 = 0;
+            if(i0 + 2 < NCUM + 3) { v0 = W.cum[a][i0]; v1 = v0 | W.cum[a][i0 + 1]; v2 = v1 | W.cum[a][i0 + 2]; }
+            unsigned x = v2;
+            #pragma unroll
+            for(int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(SQ_FULL, x, o);
+                if((int) lane >= o) x |= y;
+            }
+            unsigned ex = __shfl_up_sync(SQ_FULL, x, 1);
+            if(lane == 0) ex = 0u;
+            if(i0 + 2 < NCUM + 3) { W.cum[a][i0] = ex | v0; W.cum[a][i0 + 1] = ex | v1; W.cum[a][i0 + 2] = ex | v2; }
+        }
+        // sources inside this box may come within the softening length of a target -> near list
+        const float nhx = ghx + P.f_hs * 1.001f + 1e-3f, nhy = ghy + P.f_hs * 1.001f + 1e-3f, nhz = ghz + P.f_hs * 1.001f + 1e-3f;
         // pairs may straddle the periodic image once group extent + table range reaches half the box
         const bool pairwrap = 2.f * ghm + P.f_range >= P.f_halfs;
-        sq_walk_acc<POT> A;
-        A.ax = A.ay = A.az = A.ap = 0.f;
-        A.dax = A.day = A.daz = A.dap = 0.0;
-        int top = 0, nlist = 0;
+        float ax = 0.f, ay = 0.f, az = 0.f, ap = 0.f;
+        double dax = 0.0, day = 0.0, daz = 0.0, dap = 0.0;
+        int top = 1, n0 = 0, n1 = 0, n2 = 0, n3 = 0, nn = 0;
         if(lane == 0) W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
-        top = 1;
         __syncwarp();
 
-        while(top > 0) {
-            // wide pops only while a depth-first descent (<= 7 entries per level) still fits above them
-            int k = (STACK_CAP - STACK_RESERVE - top) / 7;
-            k = k < 1 ? 1 : k;
-            k = k > 32 ? 32 : k;
-            k = k > top ? top : k;
-            top -= k;
-            const bool have = (int) lane < k;
-            int node = 0;
-            unsigned mask = 0;
-            if(have) {
-                const int2 e = W.stack[top + lane];
-                node = e.x; mask = (unsigned) e.y;
-            }
-            __syncwarp();
+        for(;;) {
+            // the last pass (empty stack) only drains the lists
+            const bool drain = top == 0;
             unsigned acc_mask = 0, open_mask = 0;
             int4 L = make_int4(0, 0, -1, 0);
-            float n_mass = 0.f;
-            sq_node_f N;
-            N.cmx = N.cmy = N.cmz = 0.f;
-            if(have) {
-                L = lk[node];
-                const double4 M = cm[node];
-                const double4 C = cl[node];
-                st_tst++;
-                const double dmx = sq_nearest(M.x - gcx, P.box, P.half), dmy = sq_nearest(M.y - gcy, P.box, P.half), dmz = sq_nearest(M.z - gcz, P.box, P.half);
-                const double dcx = sq_nearest(C.x - gcx, P.box, P.half), dcy = sq_nearest(C.y - gcy, P.box, P.half), dcz = sq_nearest(C.z - gcz, P.box, P.half);
-                N.cmx = (float) (dmx * P.s); N.cmy = (float) (dmy * P.s); N.cmz = (float) (dmz * P.s);
-                N.cx = (float) (dcx * P.s); N.cy = (float) (dcy * P.s); N.cz = (float) (dcz * P.s);
-                n_mass = (float) (M.w * P.minv);
-                const float len = (float) (C.w * P.s);
-                const float l2 = len * len, ml2 = n_mass * l2;
-                const float acx = fabsf(N.cx), acy = fabsf(N.cy), acz = fabsf(N.cz);
-                const float amx = fabsf(N.cmx), amy = fabsf(N.cmy), amz = fabsf(N.cmz);
-                // rounding-error bounds of the FP32 coordinates / squared distances
-                const float scale = fmaxf(fmaxf(fmaxf(acx, acy), fmaxf(acz, amx)), fmaxf(amy, amz)) + ghm;
-                const float de = 3e-7f * scale;
-                const float R1 = amx + amy + amz + 3.f * ghm;
-                const float dr2 = 4.f * R1 * de + 1e-6f * R1 * R1;
-                const float eff = P.f_rcut + 0.5f * len, ins = 0.6f * len;
-                // thresholds with the relative slack and the coordinate error folded in:
-                //   "A" = the end of the interval that keeps / opens most, "B" = the end that keeps / opens least
-                const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
-                const float efA = eff * (1.f + SQ_EPS) + de, efB = eff * (1.f - SQ_EPS) - de;
-                const float inA = ins * (1.f + SQ_EPS) + de, inB = ins * (1.f - SQ_EPS) - de;
-                const float bhq = l2 / P.f_bh2;
-                const float bhA = bhq * (1.f + SQ_EPS) + dr2, bhB = bhq * (1.f - SQ_EPS) - dr2;
-                const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
-                // a node about half a box away from the group: per-target NEAREST may differ from the group's
-                const bool risky = fmaxf(fmaxf(acx + ghx, acy + ghy), fmaxf(acz + ghz, fmaxf(fmaxf(amx + ghx, amy + ghy), amz + ghz))) >= P.f_halfs * 0.999f;
-                unsigned needk = 0, needo = 0, exact = 0;
-                bool gopen = false;
-                if(risky) exact = mask;
-                else {
-                    // ---- tier 1: the whole group at once (bounding box, min/max |a_old|)
-                    const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
-                    const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
-                    const float r2n = qx * qx + qy * qy + qz * qz, r2f = wx * wx + wy * wy + wz * wz;
-                    const float en = fmaxf(fmaxf(acx - ghx, acy - ghy), acz - ghz);
-                    const float ef = fmaxf(fmaxf(acx + ghx, acy + ghy), acz + ghz);
-                    const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
-                    const bool gk_lo = (r2n <= rcA) || !(en > efA);
-                    const bool gk_hi = (r2f <= rcB) || !(ef > efB);
-                    const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
-                    const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
-                    gopen = go_hi;
-                    if(gk_lo) {
-                        if(gk_hi) {
-                            if(go_lo == go_hi) { if(go_hi) open_mask = mask; else acc_mask = mask; }
-                            else needo = mask;
-                        } else needk = mask;
-                        if(go_lo != go_hi) needo = mask;
+            float4 nodeE = make_float4(0.f, 0.f, 0.f, 0.f);
+            if(!drain) {
+                // wide pops only while a depth-first descent (<= 7 entries per level) still fits above them
+                int k = (STACK_CAP - STACK_RESERVE - top) / 7;
+                k = k < 1 ? 1 : k;
+                k = k > 32 ? 32 : k;
+                k = k > top ? top : k;
+                top -= k;
+                const bool have = (int) lane < k;
+                int node = 0;
+                unsigned mask = 0;
+                if(have) {
+                    const int2 e = W.stack[top + lane];
+                    node = e.x; mask = (unsigned) e.y;
+                }
+                __syncwarp();
+                if(have) {
+                    L = lk[node];
+                    const double4 M = cm[node];
+                    const double4 C = cl[node];
+                    st_tst++;
+                    const double dmx = sq_nearest(M.x - gcx, P.box, P.half), dmy = sq_nearest(M.y - gcy, P.box, P.half), dmz = sq_nearest(M.z - gcz, P.box, P.half);
+                    const double dcx = sq_nearest(C.x - gcx, P.box, P.half), dcy = sq_nearest(C.y - gcy, P.box, P.half), dcz = sq_nearest(C.z - gcz, P.box, P.half);
+                    const float cmx = (float) (dmx * P.s), cmy = (float) (dmy * P.s), cmz = (float) (dmz * P.s);
+                    const float cx = (float) (dcx * P.s), cy = (float) (dcy * P.s), cz = (float) (dcz * P.s);
+                    const float n_mass = (float) (M.w * P.minv);
+                    nodeE = make_float4(cmx, cmy, cmz, n_mass);
+                    const float len = (float) (C.w * P.s);
+                    const float l2 = len * len, ml2 = n_mass * l2;
+                    const float acx = fabsf(cx), acy = fabsf(cy), acz = fabsf(cz);
+                    const float amx = fabsf(cmx), amy = fabsf(cmy), amz = fabsf(cmz);
+                    // rounding-error bounds of the FP32 coordinates / squared distances
+                    const float scale = fmaxf(fmaxf(fmaxf(acx, acy), fmaxf(acz, amx)), fmaxf(amy, amz)) + ghm;
+                    const float de = 3e-7f * scale;
+                    const float R1 = amx + amy + amz + 3.f * ghm;
+                    const float dr2 = 4.f * R1 * de + 1e-6f * R1 * R1;
+                    const float eff = P.f_rcut + 0.5f * len, ins = 0.6f * len;
+                    // thresholds with the relative slack and the coordinate error folded in:
+                    //   "A" = the end of the interval that keeps / opens most, "B" = the end that keeps / opens least
+                    const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
+                    const float efA = eff * (1.f + SQ_EPS) + de, efB = eff * (1.f - SQ_EPS) - de;
+                    const float inA = ins * (1.f + SQ_EPS) + de, inB = ins * (1.f - SQ_EPS) - de;
+                    const float bhq = l2 / P.f_bh2;
+                    const float bhA = bhq * (1.f + SQ_EPS) + dr2, bhB = bhq * (1.f - SQ_EPS) - dr2;
+                    const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
+                    // a node about half a box away from the group: per-target NEAREST may differ from the group's
+                    const bool risky = fmaxf(fmaxf(acx + ghx, acy + ghy), fmaxf(acz + ghz, fmaxf(fmaxf(amx + ghx, amy + ghy), amz + ghz))) >= P.f_halfs * 0.999f;
+                    unsigned exact = 0, kept = 0, amb = 0;
+                    if(risky) exact = mask;
+                    else {
+                        // ---- keep or discard (shall_we_discard_node).  With the centre of mass inside the cell,
+                        // "r2 <= Rcut^2" implies the box test, so the box decides; otherwise every target is tested.
+                        const float en = fmaxf(fmaxf(acx - ghx, acy - ghy), acz - ghz);
+                        const float ef = fmaxf(fmaxf(acx + ghx, acy + ghy), acz + ghz);
+                        const float hl = 0.5f * len * (1.f + 1e-5f) + de;
+                        const bool cmin = fabsf(cmx - cx) <= hl && fabsf(cmy - cy) <= hl && fabsf(cmz - cz) <= hl;
+                        if(!cmin) amb = mask;
+                        else if(en > efA) { }                       // outside every target's box
+                        else if(!(ef > efB)) kept = mask;           // inside every target's box
+                        else if(de + eff * SQ_EPS < wmin) {
+                            // tier 1b: bucket masks, exact up to the targets in the boundary buckets
+                            const int bxl = sq_bucket(cx - eff, invx, offx), bxu = sq_bucket(cx + eff, invx, offx);
+                            const int byl = sq_bucket(cy - eff, invy, offy), byu = sq_bucket(cy + eff, invy, offy);
+                            const int bzl = sq_bucket(cz - eff, invz, offz), bzu = sq_bucket(cz + eff, invz, offz);
+                            const unsigned sure = ~W.cum[0][bxl + 3] & W.cum[0][bxu] & ~W.cum[1][byl + 3] & W.cum[1][byu] & ~W.cum[2][bzl + 3] & W.cum[2][bzu];
+                            const unsigned maybe = ~W.cum[0][bxl] & W.cum[0][bxu + 3] & ~W.cum[1][byl] & W.cum[1][byu + 3] & ~W.cum[2][bzl] & W.cum[2][bzu + 3];
+                            kept = sure & mask;
+                            amb = maybe & ~sure & mask;
+                        } else amb = mask;
+                        // ---- tier 2a: keep or discard, per target, FP32 with error intervals
+                        st_pair += __popc(amb);
+                        while(amb) {
+                            const int t = 31 - __clz(amb);
+                            const unsigned bit = 1u << t;
+                            amb ^= bit;
+                            const float4 T = W.tgt[t];
+                            const float dx = cmx - T.x, dy = cmy - T.y, dz = cmz - T.z;
+                            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                            const float em = fmaxf(fmaxf(fabsf(cx - T.x), fabsf(cy - T.y)), fabsf(cz - T.z));
+                            const bool k_lo = (r2 <= rcA) || !(em > efA);
+                            const bool k_hi = (r2 <= rcB) || !(em > efB);
+                            if(k_lo != k_hi) exact |= bit;
+                            else if(k_lo) kept |= bit;
+                        }
+                        // ---- open or accept (shall_we_open_node): the whole group at once if both ends of the
+                        // interval over the group's box and min/max |a_old| agree, else tier 2b per target
+                        if(kept) {
+                            const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
+                            const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
+                            const float r2n = qx * qx + qy * qy + qz * qz, r2f = wx * wx + wy * wy + wz * wz;
+                            const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
+                            const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
+                            const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
+                            if(go_lo == go_hi) {
+                                if(go_hi) open_mask = kept; else acc_mask = kept;
+                            } else {
+                                st_pair += __popc(kept);
+                                while(kept) {
+                                    const int t = 31 - __clz(kept);
+                                    const unsigned bit = 1u << t;
+                                    kept ^= bit;
+                                    const float4 T = W.tgt[t];
+                                    const float dx = cmx - T.x, dy = cmy - T.y, dz = cmz - T.z;
+                                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                                    const float em = fmaxf(fmaxf(fabsf(cx - T.x), fabsf(cy - T.y)), fabsf(cz - T.z));
+                                    const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
+                                    const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
+                                    const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
+                                    if(o_lo != o_hi) exact |= bit;
+                                    else if(o_lo) open_mask |= bit;
+                                    else acc_mask |= bit;
+                                }
+                            }
+                        }
                     }
-                }
-                // ---- tier 2a: keep or discard, per target, FP32 with error intervals
-                st_pair += __popc(needk) + __popc(needo);
-                const bool omixed = needo != 0u;
-                unsigned kept = (needk == 0u) ? needo : 0u;
-                while(needk) {
-                    const int t = 31 - __clz(needk);
-                    const unsigned bit = 1u << t;
-                    needk ^= bit;
-                    const float4 T = W.tgt[t];
-                    const float dx = N.cmx - T.x, dy = N.cmy - T.y, dz = N.cmz - T.z;
-                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                    const float em = fmaxf(fmaxf(fabsf(N.cx - T.x), fabsf(N.cy - T.y)), fabsf(N.cz - T.z));
-                    const bool k_lo = (r2 <= rcA) || !(em > efA);
-                    const bool k_hi = (r2 <= rcB) || !(em > efB);
-                    if(k_lo != k_hi) exact |= bit;
-                    else if(k_lo) kept |= bit;
-                }
-                if(!omixed) {
-                    if(gopen) open_mask |= kept; else acc_mask |= kept;
-                    kept = 0;
-                }
-                // ---- tier 2b: open or accept, for the kept targets of nodes whose opening is not uniform
-                while(kept) {
-                    const int t = 31 - __clz(kept);
-                    const unsigned bit = 1u << t;
-                    kept ^= bit;
-                    const float4 T = W.tgt[t];
-                    const float dx = N.cmx - T.x, dy = N.cmy - T.y, dz = N.cmz - T.z;
-                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                    const float em = fmaxf(fmaxf(fabsf(N.cx - T.x), fabsf(N.cy - T.y)), fabsf(N.cz - T.z));
-                    const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
-                    const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
-                    const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
-                    if(o_lo != o_hi) exact |= bit;
-                    else if(o_lo) open_mask |= bit;
-                    else acc_mask |= bit;
-                }
-                // ---- tier 3: the reference's FP64 expressions
-                while(exact) {
-                    const int t = 31 - __clz(exact);
-                    const unsigned bit = 1u << t;
-                    exact ^= bit;
-                    const long long ti = targets ? (long long) targets[t0 + t] : (t0 + t);
-                    sq_exact_par X;
-                    X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
-                    const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
-                    st_exact++;
-                    if(c == 1) acc_mask |= bit;
-                    else if(c == 2) open_mask |= bit;
+                    // ---- tier 3: the reference's FP64 expressions
+                    while(exact) {
+                        const int t = 31 - __clz(exact);
+                        const unsigned bit = 1u << t;
+                        exact ^= bit;
+                        const long long ti = targets ? (long long) targets[t0 + t] : (t0 + t);
+                        sq_exact_par X;
+                        X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
+                        const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
+                        st_exact++;
+                        if(c == 1) acc_mask |= bit;
+                        else if(c == 2) open_mask |= bit;
+                    }
                 }
             }
             const int type = SQ_INFO_TYPE(L.w);
-            // ---- accepted nodes -> interaction list
-            {
-                const unsigned b = __ballot_sync(SQ_FULL, acc_mask != 0);
-                const int tot = __popc(b);
-                if(tot) {
-                    if(nlist + tot > LIST_CAP) {
-                        __syncwarp();
-                        st_ent += nlist;
-                        if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-                        else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-                        nlist = 0;
-                        __syncwarp();
-                    }
-                    if(acc_mask) {
-                        const int p = nlist + __popc(b & sq_lanemask_lt());
-                        W.lst[p] = make_float4(N.cmx, N.cmy, N.cmz, n_mass);
-                        W.lmask[p] = acc_mask;
-                        st_int += __popc(acc_mask);
-                    }
-                    nlist += tot;
-                }
-            }
             // ---- opened internal nodes -> push children with the open mask (pseudo nodes are skipped: gravshort2.hpp:305-314)
             {
                 const int nch = (open_mask && type == 1) ? L.y : 0;
@@ -462,69 +498,115 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                     W.stack[top + off + j] = make_int2(L.x + j, (int) open_mask);
                 top += tot;
             }
-            // ---- opened leaves -> their particles join the list (gravshort2.hpp:291-303)
+            // ---- opened leaves -> their particles are sources (gravshort2.hpp:291-303)
+            int tot_leaf;
             {
                 const int np = (open_mask && type == 0) ? L.y : 0;
-                int tot;
-                const int off = sq_warp_excl_scan(np, tot);
-                if(tot) {
+                const int off = sq_warp_excl_scan(np, tot_leaf);
+                if(tot_leaf) {
                     st_int += (unsigned long long) np * __popc(open_mask);
                     W.s_end[lane] = off + np;
                     W.s_first[lane] = L.x - off;        // particle = s_first + j
                     W.s_mask[lane] = open_mask;
-                    __syncwarp();
-                    for(int base = 0; base < tot; base += 32) {
-                        const int chunk = (tot - base) < 32 ? (tot - base) : 32;
-                        if(nlist + chunk > LIST_CAP) {
-                            __syncwarp();
-                            st_ent += nlist;
-                            if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-                            else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-                            nlist = 0;
-                            __syncwarp();
-                        }
-                        const int j = base + lane;
-                        if(j < tot) {
-                            // first source lane whose end is past j
-                            int lo = 0, hi = 31;
-                            while(lo < hi) {
-                                const int mid = (lo + hi) >> 1;
-                                if(W.s_end[mid] > j) hi = mid; else lo = mid + 1;
-                            }
-                            const long long p = (long long) W.s_first[lo] + j;
-                            const double sx = spos[3 * p], sy = spos[3 * p + 1], sz = spos[3 * p + 2];
-                            W.lst[nlist + lane] = make_float4((float) (sq_nearest(sx - gcx, P.box, P.half) * P.s), (float) (sq_nearest(sy - gcy, P.box, P.half) * P.s),
-                                                              (float) (sq_nearest(sz - gcz, P.box, P.half) * P.s), (float) ((double) smass[p] * P.minv));
-                            W.lmask[nlist + lane] = W.s_mask[lo];
-                        }
-                        nlist += chunk;
-                    }
-                    __syncwarp();
                 }
             }
+            st_int += __popc(acc_mask);
+            const unsigned anyacc = __ballot_sync(SQ_FULL, acc_mask != 0u);
             __syncwarp();
+            // ---- sources join the lists, 32 per round: round 0 = accepted nodes, then the leaf particles
+            const int nrounds = 1 + ((tot_leaf + 31) >> 5);
+            for(int rd = 0; rd < nrounds; rd++) {
+                bool v = false;
+                float4 e = nodeE;
+                unsigned m = acc_mask;
+                if(rd == 0) {
+                    if(!drain && anyacc == 0u) continue;
+                    v = acc_mask != 0u;
+                } else {
+                    const int j = ((rd - 1) << 5) + (int) lane;
+                    if(j < tot_leaf) {
+                        // first source lane whose end is past j
+                        int lo = 0, hi = 31;
+                        while(lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            if(W.s_end[mid] > j) hi = mid; else lo = mid + 1;
+                        }
+                        const long long p = (long long) W.s_first[lo] + j;
+                        const double sx = spos[3 * p], sy = spos[3 * p + 1], sz = spos[3 * p + 2];
+                        e = make_float4((float) (sq_nearest(sx - gcx, P.box, P.half) * P.s), (float) (sq_nearest(sy - gcy, P.box, P.half) * P.s),
+                                        (float) (sq_nearest(sz - gcz, P.box, P.half) * P.s), (float) ((double) smass[p] * P.minv));
+                        m = W.s_mask[lo];
+                        v = true;
+                    }
+                }
+                // ---- near list
+                const bool near = v && (pairwrap || (fabsf(e.x) <= nhx && fabsf(e.y) <= nhy && fabsf(e.z) <= nhz));
+                const unsigned bn = __ballot_sync(SQ_FULL, near);
+                if(bn != 0u || (drain && nn > 0)) {
+                    const int cn = __popc(bn);
+                    if(nn + cn > NEAR_CAP || drain) {
+                        __syncwarp();
+                        sq_eval_near<POT>(W, nn, tabrow0, P, pairwrap, tx, ty, tz, lane, ax, ay, az, ap);
+                        st_ent += nn;
+                        nn = 0;
+                        __syncwarp();
+                    }
+                    if(near) {
+                        const int p = nn + __popc(bn & sq_lanemask_lt());
+                        W.nl[p] = e;
+                        W.nm[p] = m;
+                    }
+                    nn += cn;
+                }
+                // ---- octet lists
+                const bool isfar = v && !near;
+                const unsigned b0 = __ballot_sync(SQ_FULL, isfar && (m & 0x000000ffu));
+                const unsigned b1 = __ballot_sync(SQ_FULL, isfar && (m & 0x0000ff00u));
+                const unsigned b2 = __ballot_sync(SQ_FULL, isfar && (m & 0x00ff0000u));
+                const unsigned b3 = __ballot_sync(SQ_FULL, isfar && (m & 0xff000000u));
+                const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
+                if(n0 + c0 > OL_CAP || n1 + c1 > OL_CAP || n2 + c2 > OL_CAP || n3 + c3 > OL_CAP || (drain && (n0 | n1 | n2 | n3) != 0)) {
+                    const int nmax = max(max(n0, n1), max(n2, n3));
+                    const int nmax4 = (nmax + 3) & ~3;
+                    // pad the shorter lists up to the common length
+                    const int nq = q == 0 ? n0 : (q == 1 ? n1 : (q == 2 ? n2 : n3));
+                    for(int kk = nq + (int) (lane & 7u); kk < nmax4; kk += 8) {
+                        W.ol[q][kk] = make_float4(SQ_FAR, SQ_FAR, SQ_FAR, 0.f);
+                        W.om[q][kk] = 0;
+                    }
+                    __syncwarp();
+                    sq_eval_octets<POT>(W, nmax4, tabaddr, tx, ty, tz, q, bit0, ax, ay, az, ap);
+                    st_ent += nmax4;
+                    dax += (double) ax; day += (double) ay; daz += (double) az;
+                    ax = ay = az = 0.f;
+                    if(POT) { dap += (double) ap; ap = 0.f; }
+                    n0 = n1 = n2 = n3 = 0;
+                    __syncwarp();
+                }
+                if(isfar) {
+                    const unsigned lt = sq_lanemask_lt();
+                    if(m & 0x000000ffu) { const int p = n0 + __popc(b0 & lt); W.ol[0][p] = e; W.om[0][p] = (unsigned char) (m & 0xffu); }
+                    if(m & 0x0000ff00u) { const int p = n1 + __popc(b1 & lt); W.ol[1][p] = e; W.om[1][p] = (unsigned char) ((m >> 8) & 0xffu); }
+                    if(m & 0x00ff0000u) { const int p = n2 + __popc(b2 & lt); W.ol[2][p] = e; W.om[2][p] = (unsigned char) ((m >> 16) & 0xffu); }
+                    if(m & 0xff000000u) { const int p = n3 + __popc(b3 & lt); W.ol[3][p] = e; W.om[3][p] = (unsigned char) (m >> 24); }
+                }
+                n0 += c0; n1 += c1; n2 += c2; n3 += c3;
+            }
+            __syncwarp();
+            if(drain) break;
         }
-        __syncwarp();
-        st_ent += nlist;
-        if(pairwrap) sq_walk_flush<POT, true>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-        else sq_walk_flush<POT, false>(W, nlist, tab_biased, P, tx, ty, tz, tl, sl, S, A);
-        // combine the slices of each target
-        for(int o = G; o < 32; o <<= 1) {
-            A.dax += __shfl_xor_sync(SQ_FULL, A.dax, o);
-            A.day += __shfl_xor_sync(SQ_FULL, A.day, o);
-            A.daz += __shfl_xor_sync(SQ_FULL, A.daz, o);
-            if(POT) A.dap += __shfl_xor_sync(SQ_FULL, A.dap, o);
-        }
-        if(valid && sl == 0) {
+        dax += (double) ax; day += (double) ay; daz += (double) az;
+        if(POT) dap += (double) ap;
+        if(valid) {
             // gravshort2.hpp:88-107
-            accel[3 * tidx] = A.dax * P.Ka;
-            accel[3 * tidx + 1] = A.day * P.Ka;
-            accel[3 * tidx + 2] = A.daz * P.Ka;
+            accel[3 * tidx] = dax * P.Ka;
+            accel[3 * tidx + 1] = day * P.Ka;
+            accel[3 * tidx + 2] = daz * P.Ka;
             if(POT) {
-                const double m = (double) tmass[tidx];
-                double p = A.dap * P.Kp;
-                p += m / (P.h / 2.8);
-                p -= 2.8372975 * pow(m, 2.0 / 3) * P.cbrtrho0;
+                const double mt = (double) tmass[tidx];
+                double p = dap * P.Kp;
+                p += mt / (P.h / 2.8);
+                p -= 2.8372975 * pow(mt, 2.0 / 3) * P.cbrtrho0;
                 pot[tidx] = p * P.G;
             }
         }
@@ -546,15 +628,15 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         atomicAdd(&stats[4], st_exact);
     }
 }
-
 // ------------------------------------------------------------------------------------ host side
 static const double h_sr_x[SQ_NGRAVTAB] = SQ_SHORTRANGE_X_INIT;
 static const double h_sr_pot[SQ_NGRAVTAB] = SQ_SHORTRANGE_POT_INIT;
 static const double h_sr_force[SQ_NGRAVTAB] = SQ_SHORTRANGE_FORCE_INIT;
 
-// GravShortTable, libgadget/gravshort-tree2.cpp:29-69: float tables.  Device form: entry i holds
-// (value at the middle of [i, i+1], slope), so w(r) = v + (r - i - 1/2) * slope; entry 511 = (0, 0):
-// beyond the table the force is zero (gravity.h:53-54).
+// GravShortTable, libgadget/gravshort-tree2.cpp:29-69: float tables; lookup gravity.h:50-60 (i = floor(r / dx),
+// linear interpolation between rows i and i+1, nothing from row 511 on).  Two device forms, TAB_ROWS float2 rows:
+//   force only:  row i = (force value at the middle of [i, i+1], slope), rows 511.. = (0, 0)
+//   force + pot: row i = (force[i], potential[i]), row 512 = (0, 0)
 static int sq_walk_table(sq_ctx * c)
 {
     float ft[SQ_NTAB], pt[SQ_NTAB];
@@ -571,13 +653,15 @@ static int sq_walk_table(sq_ctx * c)
             pt[i] = (float) erfc(u);
         }
     }
-    float4 h[SQ_NTAB];     // (force value at mid-cell, force slope, potential value at mid-cell, potential slope)
-    for(int i = 0; i < SQ_NTAB; i++) {
+    float2 h[2][TAB_ROWS];
+    for(int i = 0; i < TAB_ROWS; i++) {
+        h[0][i] = make_float2(0.f, 0.f);
+        h[1][i] = make_float2(0.f, 0.f);
         if(i + 1 < SQ_NTAB) {
-            const double sf = (double) ft[i + 1] - (double) ft[i], sp = (double) pt[i + 1] - (double) pt[i];
-            h[i] = make_float4((float) ((double) ft[i] + 0.5 * sf), (float) sf, (float) ((double) pt[i] + 0.5 * sp), (float) sp);
-        } else
-            h[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const double sf = (double) ft[i + 1] - (double) ft[i];
+            h[0][i] = make_float2((float) ((double) ft[i] + 0.5 * sf), (float) sf);
+        }
+        if(i < SQ_NTAB) h[1][i] = make_float2(ft[i], pt[i]);
     }
     SQ_TRY(c->w_table.reserve(sizeof(h)));
     SQ_CUDA(cudaMemcpyAsync(c->w_table.p, h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
@@ -588,7 +672,7 @@ static int sq_walk_table(sq_ctx * c)
 template <bool POT>
 static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets, const sq_walk_par & P)
 {
-    const size_t smem = SQ_NTAB * sizeof(float4) + WALK_WARPS * sizeof(sq_walk_warp_smem);
+    const size_t smem = TAB_BYTES + WALK_WARPS * sizeof(sq_walk_warp_smem);
     SQ_CUDA(cudaFuncSetAttribute(sq_walk_kernel<POT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = 0;
     SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sq_walk_kernel<POT>, WALK_THREADS, smem));
@@ -602,7 +686,7 @@ static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets
     const float * smass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
     sq_walk_kernel<POT><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
             spos, smass, c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(), targets, (long long) ntargets,
-            c->w_table.as<float4>(), c->w_accel.as<double>(), c->w_pot.as<double>(), c->w_stats.as<unsigned long long>(),
+            c->w_table.as<float2>() + (POT ? TAB_ROWS : 0), c->w_accel.as<double>(), c->w_pot.as<double>(), c->w_stats.as<unsigned long long>(),
             c->w_counter.as<int>(), P);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
