@@ -311,7 +311,7 @@ def main():
             "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None,
                          "flop_per_interaction": FLOP_PER_INTERACTION, "peak_source": "FFMA microbenchmark in this run (sq_measure_fp32_peak)",
-                         "lane_efficiency": interactions / float(max(1, np.mean([s.list_entries for s in stats]) * args.group_width))},
+                         "lane_efficiency": interactions / float(max(1, np.mean([s.list_entries for s in stats]) * 32))},
             "roofline_hbm": {"peak_gbs": hbm_peak, "peak_source": peak_src, "stages": hbm},
             "e2e": {"value": e2e_value, "unit": "particles/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * de / e2e_steps},
             "gpu_launches": int(launches), "clocks": clocks}

@@ -113,7 +113,7 @@ struct sq_ctx {
     bool tree_built = false, tree_full = false, tree_identity = true;
 
     // ---- walk
-    sq_buf w_accel, w_pot, w_stats, w_targets, w_table, w_out_accel, w_out_pot, w_counter;
+    sq_buf w_accel, w_pot, w_stats, w_targets, w_table, w_out_accel, w_out_pot, w_counter, w_icm, w_icl, w_ipart;
     bool walk_done = false;
     int64_t walk_ntargets = 0;
 

@@ -6,36 +6,33 @@
 // GravTreeOutput::postprocess (gravshort2.hpp:88-107).
 //
 // Design (not the reference's thread-per-particle depth-first walk):
-//   * One warp walks the tree for a GROUP of 32 Peano-Hilbert-adjacent active particles with ONE node stack in
-//     shared memory.  A stack entry is (node, mask): mask = the targets of the group that reach this node, i.e.
-//     opened every ancestor.  Per step the warp pops up to 32 entries, one node per lane (three 128-bit loads).
+//   * One warp walks the tree for a GROUP of G Peano-Hilbert-adjacent active particles (G = 8, 16 or 32) with ONE
+//     node stack and ONE interaction list in shared memory.  A stack entry is (node, mask): mask = the targets of
+//     the group that reach this node, i.e. opened every ancestor.  Per step the warp pops up to 32 entries, one
+//     node per lane.  For the evaluation the warp is G targets x S = 32/G slices: slice s takes list entries
+//     s, s+S, ...; smaller groups have a tighter bounding box, so fewer masked-off (target, source) slots.
+//   * Coordinates are 32-bit fixed point (box / 2^32): node centres, centres of mass and particle positions are
+//     quantised once per walk by sq_walk_prep_*; a group-relative coordinate is one integer subtraction (which
+//     is also the periodic NEAREST()), one I2F and one multiply - no FP64 on the walk's hot path.  Node records
+//     are two 128-bit loads + the link record; a source particle is one 128-bit load.
 //   * Every (target, node) decision is the reference's own (discard: the Rcut + len/2 box; open: relative
 //     criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle, inside-0.6-len box), reached in tiers so that FP64 is
 //     the exception:
 //       1. group tier (FP32 interval arithmetic over the group's bounding box and its min/max |a_old|);
-//       1b. keep/discard for boundary nodes by BUCKET MASKS: per axis the targets are binned into 64 buckets over
-//          the group's extent and S[i] = mask of the targets in buckets below i is tabulated once per group;
-//          the targets inside [c - eff, c + eff] are then two table reads per bound, exact up to the targets in
-//          the two boundary buckets, which fall to tier 2;
 //       2. target tier (FP32, coordinates relative to the group centre in units of the split-table step, masses in
-//          units of the mean particle mass): the class is evaluated at both ends of the rounding-error interval
-//          of (r2, max-axis distance); equal -> decided;
-//       3. exact tier: the reference's FP64 expressions with per-target NEAREST() for the pairs whose interval
-//          straddles a threshold, and for nodes half a box away from the group.
+//          units of the mean particle mass): the class is evaluated at both ends of the error interval
+//          (rounding + quantisation) of (r2, max-axis distance); equal -> decided;
+//       3. exact tier: the reference's FP64 expressions on the original FP64 data with per-target NEAREST() for
+//          the pairs whose interval straddles a threshold, and for nodes half a box away from the group.
 //     The decision function is monotone in (r2, emax), so equal classes at the interval ends prove the FP64
 //     class.  The interaction count therefore equals the reference's exactly.
-//   * Accepted nodes and the particles of opened leaves go to FOUR interaction lists, one per OCTET of targets
-//     (lanes 8q..8q+7), each with an 8-bit mask: an octet's bounding box is much smaller than the group's, so
-//     the masked evaluation wastes fewer lanes (62 % useful instead of 41 %) while the walk is still shared by 32
-//     targets.  The four octets evaluate their own lists in lock step: one 128-bit LDS with one address per
-//     quarter warp costs the same as a warp-wide broadcast (measured, tools/ubench).
 //   * Evaluation is FP32: rsqrt, the erfc/"exact" split factor from a shared-memory table REPLICATED 16x so that
 //     every lane of a half warp reads its own bank pair (conflict-free: 2.2 clk per lookup instead of 4.9,
-//     measured).  Distances are already in table units, so the table coordinate costs nothing.  Sources that
-//     may come within the softening length of a target (inside the group's box grown by h), and everything when
-//     the periodic image can differ per pair (tiny boxes), go to a short "near" list evaluated by a careful
-//     loop (spline softening gravshort2.hpp:332-350, self pair r = 0, per-pair wrap); the fast loop has neither.
-//     Partial sums are FP32 for one list flush (<= 64 entries), then added to FP64 accumulators.
+//     measured by tools/ubench).  Distances are already in table units, so the table coordinate costs nothing.
+//     Sources that may come within the softening length of a target (inside the group's box grown by h), and
+//     everything when the periodic image can differ per pair (tiny boxes), go to a short "near" list evaluated
+//     by a careful loop (spline softening gravshort2.hpp:332-350, self pair r = 0, per-pair wrap); the fast
+//     loop has neither.  Partial sums are FP32 for one list flush (<= 128 entries), then FP64 accumulators.
 //   * Epilogue = postprocess: x G, potential self terms; results written in sorted order.
 #include "sq_common.cuh"
 #include "shortrange_table.h"
@@ -45,10 +42,9 @@
 #define WALK_THREADS (WALK_WARPS * 32)
 #define STACK_CAP 384
 #define STACK_RESERVE 160   /* 7 siblings x 22 levels: room a depth-first descent can always need */
-#define OL_CAP 64           /* entries per octet list (multiple of 4, >= 32) */
+#define LIST_CAP 128        /* interaction-list entries per flush */
+#define LIST_PAD 16         /* room to pad the last steps (4 steps x S entries) */
 #define NEAR_CAP 32
-#define NBUCK 64            /* buckets per axis over the group's extent */
-#define NCUM (NBUCK + 5)
 #define TAB_ROWS (SQ_NTAB + 1)
 #define TAB_COPIES 16
 #define TAB_BYTES (TAB_ROWS * TAB_COPIES * 8)
@@ -62,23 +58,29 @@ struct sq_walk_par {
     // scaling: lengths x s (table units), masses x minv
     double s, minv, Ka, Kp;       // accel = Ka * sum, potential = Kp * sum (+ self terms)
     double G, cbrtrho0;
+    double qinv;                  // 2^32 / box: FP64 position -> fixed point
     int relative;                 // TreeUseBH == 0
-    int gw;                       // targets per warp: 32, 16 or 8 (lanes beyond stay idle)
     // FP32 tiers (table units)
-    float f_rcut, f_rc2_lo, f_rc2_hi, f_bh2, f_h2, f_hs, f_boxs, f_invboxs, f_halfs, f_range;
+    float qs;                     // table units per fixed-point unit
+    float f_rcut, f_rc2_lo, f_rc2_hi, f_invbh2, f_h2, f_hs, f_boxs, f_invboxs, f_halfs, f_range;
 };
 
 struct sq_walk_warp_smem {
-    float4 ol[4][OL_CAP];         // octet interaction lists: x, y, z relative to the group centre (table units), mass
-    float4 nl[NEAR_CAP];          // near list (careful loop)
-    float4 tgt[32];               // targets: x, y, z, errtol*|a_old| scaled
+    float4 lst[LIST_CAP + LIST_PAD];   // interaction list: x, y, z relative to the group centre (table units), mass
+    float4 nl[NEAR_CAP];               // near list (careful loop)
+    float4 tgt[32];                    // targets: x, y, z, errtol*|a_old| scaled
     int2 stack[STACK_CAP];
+    unsigned mw[LIST_CAP + LIST_PAD];  // mask words, one per evaluation step: bit (s*G + t) = entry of slice s reaches target t
     unsigned nm[NEAR_CAP];
-    unsigned cum[3][NCUM + 3];    // bucket prefix masks S[i] = targets with bucket < i - 1
-    unsigned char om[4][OL_CAP];  // 8-bit masks of the octet lists
     int s_end[32], s_first[32];
     unsigned s_mask[32];
 };
+
+// FP64 position -> 32-bit fixed point, periodic (two's complement wrap = the box)
+__host__ __device__ __forceinline__ unsigned sq_quant(double x, double qinv)
+{
+    return (unsigned) (long long) floor(x * qinv);
+}
 
 __device__ __forceinline__ float2 sq_lds_f2(unsigned addr)
 {
@@ -138,33 +140,30 @@ __device__ __noinline__ int sq_exact_class(const double4 M, const double4 C, dou
     return 1;
 }
 
-// bucket of coordinate x (monotone non-decreasing in x): 0 below the group's extent, 1..NBUCK inside, NBUCK+1 above
-__device__ __forceinline__ int sq_bucket(float x, float inv, float off)
-{
-    return __float2int_rz(fminf(fmaxf(fmaf(x, inv, off), 0.f), (float) (NBUCK + 1)));
-}
 
-// ---- fast evaluation: the four octets run their own lists in lock step (lane = target 8q + lane%8).
-// Every genuine entry is farther than the softening length from every target of the group (the others are in
-// the near list), padding entries are SQ_FAR away, so r2 > 0 and no softening / wrap test is needed here.
-// Table: (gravity.h:50-60) i = floor(r), linear interpolation, zero from row 511 on.
+// ---- fast evaluation: lane = (slice s, target t); step i gives slice s the entry i*S + s (one 128-bit LDS with one
+// address per slice costs the same as a warp-wide broadcast) and mask word i, whose bit `lane` says whether that
+// entry reaches this lane's target.  Every genuine entry is farther than the softening length from every target of
+// the group (the others are in the near list), padding entries are SQ_FAR away, so r2 > 0 and no softening or
+// wrap test is needed.  Table (gravity.h:50-60): i = floor(r), linear interpolation, zero from row 511 on.
 //   !POT: row i = (value at the middle of [i, i+1], slope); row 511 = (0, 0)
 //    POT: row i = (force[i], potential[i]); rows i and i+1 are read; the r < 511 test zeroes the tail
-template <bool POT>
-__device__ __forceinline__ void sq_eval_octets(const sq_walk_warp_smem & W, int nmax4, unsigned tabaddr, float tx, float ty, float tz,
-                                               int q, unsigned bit0, float & ax, float & ay, float & az, float & ap)
+template <bool POT, int S>
+__device__ __forceinline__ void sq_eval_list(const sq_walk_warp_smem & W, int nsteps4, unsigned tabaddr, float tx, float ty, float tz,
+                                             int s, unsigned lanebit, float & ax, float & ay, float & az, float & ap)
 {
-    const float4 * lst = W.ol[q];
-    const unsigned * mk = reinterpret_cast<const unsigned *>(W.om[q]);
-    const int nb = nmax4 >> 2;
+    const uint4 * mw4 = reinterpret_cast<const uint4 *>(W.mw);
+    const float4 * lst = W.lst + s;
+    const int nb = nsteps4 >> 2;
     for(int b = 0; b < nb; b++) {
-        const unsigned m4 = mk[b];
+        const uint4 w4 = mw4[b];
         #pragma unroll
         for(int j = 0; j < 4; j++) {
-            const float4 s = lst[4 * b + j];
-            const float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+            const float4 src = lst[(4 * b + j) * S];
+            const unsigned wj = j == 0 ? w4.x : (j == 1 ? w4.y : (j == 2 ? w4.z : w4.w));
+            const float dx = src.x - tx, dy = src.y - ty, dz = src.z - tz;
             const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-            const bool on = (m4 & (bit0 << (8 * j))) != 0u;
+            const bool on = (wj & lanebit) != 0u;
             const float rinv = sq_rsqrt(r2);
             // xq = r - 1/2; round-to-nearest of xq = floor(r); d = r - floor(r) - 1/2
             const float xq = fminf(fmaf(r2, rinv, -0.5f), 511.f);
@@ -176,7 +175,7 @@ __device__ __forceinline__ void sq_eval_octets(const sq_walk_warp_smem & W, int 
                 const float2 e0 = sq_lds_f2(addr), e1 = sq_lds_f2(addr + 128);
                 const float fr = d + 0.5f;
                 const float wf = fmaf(fr, e1.x - e0.x, e0.x), wp = fmaf(fr, e1.y - e0.y, e0.y);
-                const float mm = (on && r2 < 261121.f) ? s.w : 0.f;
+                const float mm = (on && r2 < 261121.f) ? src.w : 0.f;
                 const float fac = (mm * rinv2) * (rinv * wf);
                 ax = fmaf(dx, fac, ax);
                 ay = fmaf(dy, fac, ay);
@@ -184,7 +183,7 @@ __device__ __forceinline__ void sq_eval_octets(const sq_walk_warp_smem & W, int 
                 ap = fmaf(-mm * rinv, wp, ap);
             } else {
                 const float2 w = sq_lds_f2(addr);
-                const float mm = on ? s.w : 0.f;
+                const float mm = on ? src.w : 0.f;
                 const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
                 ax = fmaf(dx, fac, ax);
                 ay = fmaf(dy, fac, ay);
@@ -194,17 +193,17 @@ __device__ __forceinline__ void sq_eval_octets(const sq_walk_warp_smem & W, int 
     }
 }
 
-// ---- careful evaluation of the near list (lane = target, entries broadcast): softened pairs (r < 2.8 eps),
+// ---- careful evaluation of the near list (slice s takes entries s, s+S, ...): softened pairs (r < 2.8 eps),
 // the target meeting itself in its own leaf (r = 0, as in the reference), per-pair periodic wrap.
-template <bool POT>
+template <bool POT, int S>
 __device__ __forceinline__ void sq_eval_near(const sq_walk_warp_smem & W, int nn, unsigned tabrow0, const sq_walk_par & P, bool pairwrap,
-                                             float tx, float ty, float tz, unsigned lane, float & ax, float & ay, float & az, float & ap)
+                                             float tx, float ty, float tz, int s, int t, float & ax, float & ay, float & az, float & ap)
 {
-    for(int k = 0; k < nn; k++) {
-        const float4 s = W.nl[k];
+    for(int k = s; k < nn; k += S) {
+        const float4 src = W.nl[k];
         const unsigned m = W.nm[k];
-        if((m >> lane) & 1u) {
-            float dx = s.x - tx, dy = s.y - ty, dz = s.z - tz;
+        if((m >> t) & 1u) {
+            float dx = src.x - tx, dy = src.y - ty, dz = src.z - tz;
             if(pairwrap) {
                 dx -= P.f_boxs * rintf(dx * P.f_invboxs);
                 dy -= P.f_boxs * rintf(dy * P.f_invboxs);
@@ -232,25 +231,35 @@ __device__ __forceinline__ void sq_eval_near(const sq_walk_warp_smem & W, int nn
                     const float2 w = sq_lds_f2(addr);
                     wf = fmaf(fr - 0.5f, w.y, w.x);
                 }
-                const float f = s.w * fac * wf;
+                const float f = src.w * fac * wf;
                 ax = fmaf(dx, f, ax);
                 ay = fmaf(dy, f, ay);
                 az = fmaf(dz, f, az);
-                if(POT) ap = fmaf(s.w * facpot, wp, ap);
+                if(POT) ap = fmaf(src.w * facpot, wp, ap);
             }
         }
     }
 }
 
-template <bool POT>
+// mask field of list entry p inside the per-step mask words (G bits per entry, S entries per word)
+template <int G>
+__device__ __forceinline__ void sq_store_field(unsigned * mw, int p, unsigned m)
+{
+    if(G == 8) reinterpret_cast<unsigned char *>(mw)[p] = (unsigned char) m;
+    else if(G == 16) reinterpret_cast<unsigned short *>(mw)[p] = (unsigned short) m;
+    else mw[p] = m;
+}
+
+template <bool POT, int G>
 __global__ void __launch_bounds__(WALK_THREADS, 1)
-sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl, const int4 * __restrict__ lk,
-               const double * __restrict__ spos, const float * __restrict__ smass,
+sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, const int4 * __restrict__ lk,
+               const double4 * __restrict__ cm, const double4 * __restrict__ cl, const uint4 * __restrict__ ipart,
                const double * __restrict__ tpos, const float * __restrict__ tmass, const double * __restrict__ toldacc,
                const uint32_t * __restrict__ targets, long long ntargets, const float2 * __restrict__ gtab,
                double * __restrict__ accel, double * __restrict__ pot, unsigned long long * __restrict__ stats,
                int * __restrict__ group_counter, const sq_walk_par P)
 {
+    constexpr int S = 32 / G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 * tab = reinterpret_cast<float2 *>(smem_raw);
     sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + TAB_BYTES);
@@ -263,10 +272,10 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
     const unsigned tabrow0 = (unsigned) __cvta_generic_to_shared(tab) + (lane & 15u) * 8u;
     // biased so that the mantissa bits of (x + 1.5*2^23) index the rows directly
     const unsigned tabaddr = tabrow0 - (0x4B400000u << 7);
-    const int q = (int) (lane >> 3);
-    const unsigned bit0 = 1u << (lane & 7u);
+    const int t = (int) (lane & (G - 1)), s = (int) (lane / G);
+    const unsigned lanebit = 1u << lane;
+    const float INF = __int_as_float(0x7f800000);
 
-    const int G = P.gw;
     const long long ngroups = (ntargets + G - 1) / G;
     unsigned long long st_int = 0, st_ent = 0, st_tst = 0, st_pair = 0, st_exact = 0;
 
@@ -277,79 +286,51 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         if(g >= ngroups) break;
         const long long t0 = g * G;
         const int nt = (int) ((ntargets - t0) < G ? (ntargets - t0) : G);
-        const bool valid = (int) lane < nt;
+        const bool valid = t < nt;
         long long tidx = 0;
-        double px = 0, py = 0, pz = 0, aold = 0;
+        unsigned ix = 0, iy = 0, iz = 0;
+        float ta = INF;
         if(valid) {
-            tidx = targets ? (long long) targets[t0 + lane] : (t0 + lane);
-            px = tpos[3 * tidx]; py = tpos[3 * tidx + 1]; pz = tpos[3 * tidx + 2];
-            aold = P.errtol * toldacc[tidx];
+            tidx = targets ? (long long) targets[t0 + t] : (t0 + t);
+            ix = sq_quant(tpos[3 * tidx], P.qinv); iy = sq_quant(tpos[3 * tidx + 1], P.qinv); iz = sq_quant(tpos[3 * tidx + 2], P.qinv);
+            // errtol*|a_old| in the scaled system: M l^2 > r^4 a  <=>  M' l'^2 > r'^4 a / (munit s^2); BH mode: never
+            if(P.relative) ta = (float) (P.errtol * toldacc[tidx] * (P.minv / (P.s * P.s)));
         }
-        // group bounding box over the valid targets
-        double lox = valid ? px : 1e300, loy = valid ? py : 1e300, loz = valid ? pz : 1e300;
-        double hix = valid ? px : -1e300, hiy = valid ? py : -1e300, hiz = valid ? pz : -1e300;
-        double amin = valid ? aold : 1e300, amax = valid ? aold : 0.0;
+        // group bounding box in fixed point, relative to the first target (always valid)
+        const unsigned ix0 = __shfl_sync(SQ_FULL, ix, 0), iy0 = __shfl_sync(SQ_FULL, iy, 0), iz0 = __shfl_sync(SQ_FULL, iz, 0);
+        const int rx = valid ? (int) (ix - ix0) : 0, ry = valid ? (int) (iy - iy0) : 0, rz = valid ? (int) (iz - iz0) : 0;
+        int mnx = rx, mxx = rx, mny = ry, mxy = ry, mnz = rz, mxz = rz;
+        float ta_lo = valid ? ta : INF, ta_hi = valid ? ta : 0.f;
         #pragma unroll
-        for(int o = 16; o >= 1; o >>= 1) {
-            lox = fmin(lox, __shfl_xor_sync(SQ_FULL, lox, o)); hix = fmax(hix, __shfl_xor_sync(SQ_FULL, hix, o));
-            loy = fmin(loy, __shfl_xor_sync(SQ_FULL, loy, o)); hiy = fmax(hiy, __shfl_xor_sync(SQ_FULL, hiy, o));
-            loz = fmin(loz, __shfl_xor_sync(SQ_FULL, loz, o)); hiz = fmax(hiz, __shfl_xor_sync(SQ_FULL, hiz, o));
-            amin = fmin(amin, __shfl_xor_sync(SQ_FULL, amin, o)); amax = fmax(amax, __shfl_xor_sync(SQ_FULL, amax, o));
+        for(int o = G / 2; o >= 1; o >>= 1) {
+            mnx = min(mnx, __shfl_xor_sync(SQ_FULL, mnx, o)); mxx = max(mxx, __shfl_xor_sync(SQ_FULL, mxx, o));
+            mny = min(mny, __shfl_xor_sync(SQ_FULL, mny, o)); mxy = max(mxy, __shfl_xor_sync(SQ_FULL, mxy, o));
+            mnz = min(mnz, __shfl_xor_sync(SQ_FULL, mnz, o)); mxz = max(mxz, __shfl_xor_sync(SQ_FULL, mxz, o));
+            ta_lo = fminf(ta_lo, __shfl_xor_sync(SQ_FULL, ta_lo, o)); ta_hi = fmaxf(ta_hi, __shfl_xor_sync(SQ_FULL, ta_hi, o));
         }
-        const double gcx = 0.5 * (lox + hix), gcy = 0.5 * (loy + hiy), gcz = 0.5 * (loz + hiz);
+        ta_lo *= (1.f - SQ_EPS);
+        ta_hi = P.relative ? ta_hi * (1.f + SQ_EPS) : INF;
+        // extents as unsigned differences: a group may span more than half the box (then everything is "risky")
+        const unsigned exx = (unsigned) mxx - (unsigned) mnx, exy = (unsigned) mxy - (unsigned) mny, exz = (unsigned) mxz - (unsigned) mnz;
+        const unsigned gcix = ix0 + (unsigned) mnx + (exx >> 1), gciy = iy0 + (unsigned) mny + (exy >> 1), gciz = iz0 + (unsigned) mnz + (exz >> 1);
         // half extents in table units, rounded up
-        const float ghx = (float) (0.5 * (hix - lox) * P.s) * 1.000001f + 1e-30f;
-        const float ghy = (float) (0.5 * (hiy - loy) * P.s) * 1.000001f + 1e-30f;
-        const float ghz = (float) (0.5 * (hiz - loz) * P.s) * 1.000001f + 1e-30f;
+        const float ghx = (float) exx * (0.5f * 1.000001f) * P.qs + 2.f * P.qs;
+        const float ghy = (float) exy * (0.5f * 1.000001f) * P.qs + 2.f * P.qs;
+        const float ghz = (float) exz * (0.5f * 1.000001f) * P.qs + 2.f * P.qs;
         const float ghm = fmaxf(ghx, fmaxf(ghy, ghz));
-        // errtol*|a_old| in the scaled system: M l^2 > r^4 a  <=>  M' l'^2 > r'^4 a / (munit s^2); BH mode: never
-        const double ascale = P.minv / (P.s * P.s);
-        const float ta = P.relative ? (float) (aold * ascale) : __int_as_float(0x7f800000);
-        const float ta_lo = P.relative ? (float) (amin * ascale) * (1.f - SQ_EPS) : __int_as_float(0x7f800000);
-        const float ta_hi = P.relative ? (float) (amax * ascale) * (1.f + SQ_EPS) : __int_as_float(0x7f800000);
         // idle lanes sit far away so that they never see r = 0
-        const float tx = valid ? (float) ((px - gcx) * P.s) : 2.f * SQ_FAR;
-        const float ty = valid ? (float) ((py - gcy) * P.s) : 2.f * SQ_FAR;
-        const float tz = valid ? (float) ((pz - gcz) * P.s) : 2.f * SQ_FAR;
+        const float tx = valid ? (float) (int) (ix - gcix) * P.qs : 2.f * SQ_FAR;
+        const float ty = valid ? (float) (int) (iy - gciy) * P.qs : 2.f * SQ_FAR;
+        const float tz = valid ? (float) (int) (iz - gciz) * P.qs : 2.f * SQ_FAR;
         __syncwarp();
-        W.tgt[lane] = make_float4(tx, ty, tz, ta);
-        // ---- bucket prefix masks, per axis: S[i] = targets whose bucket is below i - 1
-        const float bwx = fmaxf(ghx, 1e-3f), bwy = fmaxf(ghy, 1e-3f), bwz = fmaxf(ghz, 1e-3f);
-        const float invx = (0.999f * NBUCK) / (2.f * bwx), invy = (0.999f * NBUCK) / (2.f * bwy), invz = (0.999f * NBUCK) / (2.f * bwz);
-        const float offx = fmaf(bwx, invx, 1.f), offy = fmaf(bwy, invy, 1.f), offz = fmaf(bwz, invz, 1.f);
-        // a bound is resolved to +-1 bucket only while the FP32 uncertainty stays below 0.9 bucket widths
-        const float wmin = 0.9f / fmaxf(invx, fmaxf(invy, invz));
-        for(int i = lane; i < 3 * (NCUM + 3); i += 32)
-            (&W.cum[0][0])[i] = 0u;
-        __syncwarp();
-        if(valid) {
-            atomicOr(&W.cum[0][sq_bucket(tx, invx, offx) + 2], 1u << lane);
-            atomicOr(&W.cum[1][sq_bucket(ty, invy, offy) + 2], 1u << lane);
-            atomicOr(&W.cum[2][sq_bucket(tz, invz, offz) + 2], 1u << lane);
-        }
-        __syncwarp();
-        #pragma unroll
-        for(int a = 0; a < 3; a++) {
-            const int i0 = 3 * (int) lane;
-            unsigned v0 = 0, v1 = 0, v2 = 0;
-            if(i0 + 2 < NCUM + 3) { v0 = W.cum[a][i0]; v1 = v0 | W.cum[a][i0 + 1]; v2 = v1 | W.cum[a][i0 + 2]; }
-            unsigned x = v2;
-            #pragma unroll
-            for(int o = 1; o < 32; o <<= 1) {
-                const unsigned y = __shfl_up_sync(SQ_FULL, x, o);
-                if((int) lane >= o) x |= y;
-            }
-            unsigned ex = __shfl_up_sync(SQ_FULL, x, 1);
-            if(lane == 0) ex = 0u;
-            if(i0 + 2 < NCUM + 3) { W.cum[a][i0] = ex | v0; W.cum[a][i0 + 1] = ex | v1; W.cum[a][i0 + 2] = ex | v2; }
-        }
+        if(s == 0) W.tgt[t] = make_float4(tx, ty, tz, ta);
         // sources inside this box may come within the softening length of a target -> near list
         const float nhx = ghx + P.f_hs * 1.001f + 1e-3f, nhy = ghy + P.f_hs * 1.001f + 1e-3f, nhz = ghz + P.f_hs * 1.001f + 1e-3f;
         // pairs may straddle the periodic image once group extent + table range reaches half the box
         const bool pairwrap = 2.f * ghm + P.f_range >= P.f_halfs;
         float ax = 0.f, ay = 0.f, az = 0.f, ap = 0.f;
         double dax = 0.0, day = 0.0, daz = 0.0, dap = 0.0;
-        int top = 1, n0 = 0, n1 = 0, n2 = 0, n3 = 0, nn = 0;
+        int top = 1, nlist = 0, nn = 0;
         if(lane == 0) W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
         __syncwarp();
 
@@ -376,115 +357,87 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                 __syncwarp();
                 if(have) {
                     L = lk[node];
-                    const double4 M = cm[node];
-                    const double4 C = cl[node];
+                    const uint4 A = icm[node], B = icl[node];
                     st_tst++;
-                    const double dmx = sq_nearest(M.x - gcx, P.box, P.half), dmy = sq_nearest(M.y - gcy, P.box, P.half), dmz = sq_nearest(M.z - gcz, P.box, P.half);
-                    const double dcx = sq_nearest(C.x - gcx, P.box, P.half), dcy = sq_nearest(C.y - gcy, P.box, P.half), dcz = sq_nearest(C.z - gcz, P.box, P.half);
-                    const float cmx = (float) (dmx * P.s), cmy = (float) (dmy * P.s), cmz = (float) (dmz * P.s);
-                    const float cx = (float) (dcx * P.s), cy = (float) (dcy * P.s), cz = (float) (dcz * P.s);
-                    const float n_mass = (float) (M.w * P.minv);
+                    const float cmx = (float) (int) (A.x - gcix) * P.qs, cmy = (float) (int) (A.y - gciy) * P.qs, cmz = (float) (int) (A.z - gciz) * P.qs;
+                    const float cx = (float) (int) (B.x - gcix) * P.qs, cy = (float) (int) (B.y - gciy) * P.qs, cz = (float) (int) (B.z - gciz) * P.qs;
+                    const float n_mass = __uint_as_float(A.w), len = __uint_as_float(B.w);
                     nodeE = make_float4(cmx, cmy, cmz, n_mass);
-                    const float len = (float) (C.w * P.s);
                     const float l2 = len * len, ml2 = n_mass * l2;
                     const float acx = fabsf(cx), acy = fabsf(cy), acz = fabsf(cz);
                     const float amx = fabsf(cmx), amy = fabsf(cmy), amz = fabsf(cmz);
-                    // rounding-error bounds of the FP32 coordinates / squared distances
+                    // error bounds of the FP32 coordinates (rounding + fixed-point quantisation) / squared distances
                     const float scale = fmaxf(fmaxf(fmaxf(acx, acy), fmaxf(acz, amx)), fmaxf(amy, amz)) + ghm;
-                    const float de = 3e-7f * scale;
+                    const float de = fmaf(3e-7f, scale, 2.5f * P.qs);
                     const float R1 = amx + amy + amz + 3.f * ghm;
                     const float dr2 = 4.f * R1 * de + 1e-6f * R1 * R1;
-                    const float eff = P.f_rcut + 0.5f * len, ins = 0.6f * len;
+                    const float eff = fmaf(0.5f, len, P.f_rcut), ins = 0.6f * len;
                     // thresholds with the relative slack and the coordinate error folded in:
                     //   "A" = the end of the interval that keeps / opens most, "B" = the end that keeps / opens least
                     const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
-                    const float efA = eff * (1.f + SQ_EPS) + de, efB = eff * (1.f - SQ_EPS) - de;
-                    const float inA = ins * (1.f + SQ_EPS) + de, inB = ins * (1.f - SQ_EPS) - de;
-                    const float bhq = l2 / P.f_bh2;
-                    const float bhA = bhq * (1.f + SQ_EPS) + dr2, bhB = bhq * (1.f - SQ_EPS) - dr2;
+                    const float efA = fmaf(eff, 1.f + SQ_EPS, de), efB = fmaf(eff, 1.f - SQ_EPS, -de);
+                    const float inA = fmaf(ins, 1.f + SQ_EPS, de), inB = fmaf(ins, 1.f - SQ_EPS, -de);
+                    const float bhq = l2 * P.f_invbh2;
+                    const float bhA = fmaf(bhq, 1.f + SQ_EPS, dr2), bhB = fmaf(bhq, 1.f - SQ_EPS, -dr2);
                     const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
                     // a node about half a box away from the group: per-target NEAREST may differ from the group's
                     const bool risky = fmaxf(fmaxf(acx + ghx, acy + ghy), fmaxf(acz + ghz, fmaxf(fmaxf(amx + ghx, amy + ghy), amz + ghz))) >= P.f_halfs * 0.999f;
-                    unsigned exact = 0, kept = 0, amb = 0;
+                    unsigned exact = 0, need = 0;
                     if(risky) exact = mask;
                     else {
-                        // ---- keep or discard (shall_we_discard_node).  With the centre of mass inside the cell,
-                        // "r2 <= Rcut^2" implies the box test, so the box decides; otherwise every target is tested.
+                        // ---- tier 1: the whole group at once (bounding box, min/max |a_old|).  With the centre of
+                        // mass inside the cell "r2 <= Rcut^2" implies the box test, so the box decides keep/discard.
                         const float en = fmaxf(fmaxf(acx - ghx, acy - ghy), acz - ghz);
                         const float ef = fmaxf(fmaxf(acx + ghx, acy + ghy), acz + ghz);
-                        const float hl = 0.5f * len * (1.f + 1e-5f) + de;
+                        const float hl = fmaf(0.5f * (1.f + 1e-5f), len, de);
                         const bool cmin = fabsf(cmx - cx) <= hl && fabsf(cmy - cy) <= hl && fabsf(cmz - cz) <= hl;
-                        if(!cmin) amb = mask;
-                        else if(en > efA) { }                       // outside every target's box
-                        else if(!(ef > efB)) kept = mask;           // inside every target's box
-                        else if(de + eff * SQ_EPS < wmin) {
-                            // tier 1b: bucket masks, exact up to the targets in the boundary buckets
-                            const int bxl = sq_bucket(cx - eff, invx, offx), bxu = sq_bucket(cx + eff, invx, offx);
-                            const int byl = sq_bucket(cy - eff, invy, offy), byu = sq_bucket(cy + eff, invy, offy);
-                            const int bzl = sq_bucket(cz - eff, invz, offz), bzu = sq_bucket(cz + eff, invz, offz);
-                            const unsigned sure = ~W.cum[0][bxl + 3] & W.cum[0][bxu] & ~W.cum[1][byl + 3] & W.cum[1][byu] & ~W.cum[2][bzl + 3] & W.cum[2][bzu];
-                            const unsigned maybe = ~W.cum[0][bxl] & W.cum[0][bxu + 3] & ~W.cum[1][byl] & W.cum[1][byu + 3] & ~W.cum[2][bzl] & W.cum[2][bzu + 3];
-                            kept = sure & mask;
-                            amb = maybe & ~sure & mask;
-                        } else amb = mask;
-                        // ---- tier 2a: keep or discard, per target, FP32 with error intervals
-                        st_pair += __popc(amb);
-                        while(amb) {
-                            const int t = 31 - __clz(amb);
-                            const unsigned bit = 1u << t;
-                            amb ^= bit;
-                            const float4 T = W.tgt[t];
+                        if(!cmin) need = mask;
+                        else if(en > efA) { }                       // outside every target's box: discarded
+                        else {
+                            const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
+                            const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
+                            const float r2n = fmaf(qz, qz, fmaf(qy, qy, qx * qx)), r2f = fmaf(wz, wz, fmaf(wy, wy, wx * wx));
+                            const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
+                            const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
+                            const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
+                            if(!(ef > efB) && go_lo == go_hi) {     // inside every target's box, same opening for all
+                                if(go_hi) open_mask = mask; else acc_mask = mask;
+                            } else need = mask;
+                        }
+                        // ---- tier 2: per target, FP32 with error intervals
+                        st_pair += __popc(need);
+                        while(need) {
+                            const int t2 = 31 - __clz(need);
+                            const unsigned bit = 1u << t2;
+                            need ^= bit;
+                            const float4 T = W.tgt[t2];
                             const float dx = cmx - T.x, dy = cmy - T.y, dz = cmz - T.z;
                             const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
                             const float em = fmaxf(fmaxf(fabsf(cx - T.x), fabsf(cy - T.y)), fabsf(cz - T.z));
                             const bool k_lo = (r2 <= rcA) || !(em > efA);
                             const bool k_hi = (r2 <= rcB) || !(em > efB);
-                            if(k_lo != k_hi) exact |= bit;
-                            else if(k_lo) kept |= bit;
-                        }
-                        // ---- open or accept (shall_we_open_node): the whole group at once if both ends of the
-                        // interval over the group's box and min/max |a_old| agree, else tier 2b per target
-                        if(kept) {
-                            const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
-                            const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
-                            const float r2n = qx * qx + qy * qy + qz * qz, r2f = wx * wx + wy * wy + wz * wz;
-                            const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
-                            const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
-                            const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
-                            if(go_lo == go_hi) {
-                                if(go_hi) open_mask = kept; else acc_mask = kept;
-                            } else {
-                                st_pair += __popc(kept);
-                                while(kept) {
-                                    const int t = 31 - __clz(kept);
-                                    const unsigned bit = 1u << t;
-                                    kept ^= bit;
-                                    const float4 T = W.tgt[t];
-                                    const float dx = cmx - T.x, dy = cmy - T.y, dz = cmz - T.z;
-                                    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                                    const float em = fmaxf(fmaxf(fabsf(cx - T.x), fabsf(cy - T.y)), fabsf(cz - T.z));
-                                    const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
-                                    const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
-                                    const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
-                                    if(o_lo != o_hi) exact |= bit;
-                                    else if(o_lo) open_mask |= bit;
-                                    else acc_mask |= bit;
-                                }
-                            }
+                            const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
+                            const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
+                            const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
+                            if(k_lo != k_hi || (k_lo && o_lo != o_hi)) exact |= bit;
+                            else if(k_lo) { if(o_lo) open_mask |= bit; else acc_mask |= bit; }
                         }
                     }
-                    // ---- tier 3: the reference's FP64 expressions
-                    while(exact) {
-                        const int t = 31 - __clz(exact);
-                        const unsigned bit = 1u << t;
-                        exact ^= bit;
-                        const long long ti = targets ? (long long) targets[t0 + t] : (t0 + t);
+                    // ---- tier 3: the reference's FP64 expressions on the FP64 node and particle data
+                    if(exact) {
+                        const double4 M = cm[node], C = cl[node];
                         sq_exact_par X;
                         X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
-                        const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
-                        st_exact++;
-                        if(c == 1) acc_mask |= bit;
-                        else if(c == 2) open_mask |= bit;
+                        while(exact) {
+                            const int t2 = 31 - __clz(exact);
+                            const unsigned bit = 1u << t2;
+                            exact ^= bit;
+                            const long long ti = targets ? (long long) targets[t0 + t2] : (t0 + t2);
+                            const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
+                            st_exact++;
+                            if(c == 1) acc_mask |= bit;
+                            else if(c == 2) open_mask |= bit;
+                        }
                     }
                 }
             }
@@ -531,10 +484,8 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                             const int mid = (lo + hi) >> 1;
                             if(W.s_end[mid] > j) hi = mid; else lo = mid + 1;
                         }
-                        const long long p = (long long) W.s_first[lo] + j;
-                        const double sx = spos[3 * p], sy = spos[3 * p + 1], sz = spos[3 * p + 2];
-                        e = make_float4((float) (sq_nearest(sx - gcx, P.box, P.half) * P.s), (float) (sq_nearest(sy - gcy, P.box, P.half) * P.s),
-                                        (float) (sq_nearest(sz - gcz, P.box, P.half) * P.s), (float) ((double) smass[p] * P.minv));
+                        const uint4 q4 = ipart[(long long) W.s_first[lo] + j];
+                        e = make_float4((float) (int) (q4.x - gcix) * P.qs, (float) (int) (q4.y - gciy) * P.qs, (float) (int) (q4.z - gciz) * P.qs, __uint_as_float(q4.w));
                         m = W.s_mask[lo];
                         v = true;
                     }
@@ -546,8 +497,8 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                     const int cn = __popc(bn);
                     if(nn + cn > NEAR_CAP || drain) {
                         __syncwarp();
-                        sq_eval_near<POT>(W, nn, tabrow0, P, pairwrap, tx, ty, tz, lane, ax, ay, az, ap);
-                        st_ent += nn;
+                        sq_eval_near<POT, S>(W, nn, tabrow0, P, pairwrap, tx, ty, tz, s, t, ax, ay, az, ap);
+                        st_ent += (nn + S - 1) / S;
                         nn = 0;
                         __syncwarp();
                     }
@@ -558,46 +509,47 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
                     }
                     nn += cn;
                 }
-                // ---- octet lists
+                // ---- interaction list
                 const bool isfar = v && !near;
-                const unsigned b0 = __ballot_sync(SQ_FULL, isfar && (m & 0x000000ffu));
-                const unsigned b1 = __ballot_sync(SQ_FULL, isfar && (m & 0x0000ff00u));
-                const unsigned b2 = __ballot_sync(SQ_FULL, isfar && (m & 0x00ff0000u));
-                const unsigned b3 = __ballot_sync(SQ_FULL, isfar && (m & 0xff000000u));
-                const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
-                if(n0 + c0 > OL_CAP || n1 + c1 > OL_CAP || n2 + c2 > OL_CAP || n3 + c3 > OL_CAP || (drain && (n0 | n1 | n2 | n3) != 0)) {
-                    const int nmax = max(max(n0, n1), max(n2, n3));
-                    const int nmax4 = (nmax + 3) & ~3;
-                    // pad the shorter lists up to the common length
-                    const int nq = q == 0 ? n0 : (q == 1 ? n1 : (q == 2 ? n2 : n3));
-                    for(int kk = nq + (int) (lane & 7u); kk < nmax4; kk += 8) {
-                        W.ol[q][kk] = make_float4(SQ_FAR, SQ_FAR, SQ_FAR, 0.f);
-                        W.om[q][kk] = 0;
+                const unsigned bf = __ballot_sync(SQ_FULL, isfar);
+                const int cf = __popc(bf);
+                if(nlist + cf > LIST_CAP || (drain && nlist > 0)) {
+                    // pad to whole groups of 4 steps: far away, reaching nobody
+                    const int nsteps4 = ((nlist + S - 1) / S + 3) & ~3;
+                    for(int kk = nlist + (int) lane; kk < nsteps4 * S; kk += 32) {
+                        W.lst[kk] = make_float4(SQ_FAR, SQ_FAR, SQ_FAR, 0.f);
+                        sq_store_field<G>(W.mw, kk, 0u);
                     }
                     __syncwarp();
-                    sq_eval_octets<POT>(W, nmax4, tabaddr, tx, ty, tz, q, bit0, ax, ay, az, ap);
-                    st_ent += nmax4;
+                    sq_eval_list<POT, S>(W, nsteps4, tabaddr, tx, ty, tz, s, lanebit, ax, ay, az, ap);
+                    st_ent += nsteps4;
                     dax += (double) ax; day += (double) ay; daz += (double) az;
                     ax = ay = az = 0.f;
                     if(POT) { dap += (double) ap; ap = 0.f; }
-                    n0 = n1 = n2 = n3 = 0;
+                    nlist = 0;
                     __syncwarp();
                 }
                 if(isfar) {
-                    const unsigned lt = sq_lanemask_lt();
-                    if(m & 0x000000ffu) { const int p = n0 + __popc(b0 & lt); W.ol[0][p] = e; W.om[0][p] = (unsigned char) (m & 0xffu); }
-                    if(m & 0x0000ff00u) { const int p = n1 + __popc(b1 & lt); W.ol[1][p] = e; W.om[1][p] = (unsigned char) ((m >> 8) & 0xffu); }
-                    if(m & 0x00ff0000u) { const int p = n2 + __popc(b2 & lt); W.ol[2][p] = e; W.om[2][p] = (unsigned char) ((m >> 16) & 0xffu); }
-                    if(m & 0xff000000u) { const int p = n3 + __popc(b3 & lt); W.ol[3][p] = e; W.om[3][p] = (unsigned char) (m >> 24); }
+                    const int p = nlist + __popc(bf & sq_lanemask_lt());
+                    W.lst[p] = e;
+                    sq_store_field<G>(W.mw, p, m);
                 }
-                n0 += c0; n1 += c1; n2 += c2; n3 += c3;
+                nlist += cf;
             }
             __syncwarp();
             if(drain) break;
         }
         dax += (double) ax; day += (double) ay; daz += (double) az;
         if(POT) dap += (double) ap;
-        if(valid) {
+        // combine the slices of each target
+        #pragma unroll
+        for(int o = G; o < 32; o <<= 1) {
+            dax += __shfl_xor_sync(SQ_FULL, dax, o);
+            day += __shfl_xor_sync(SQ_FULL, day, o);
+            daz += __shfl_xor_sync(SQ_FULL, daz, o);
+            if(POT) dap += __shfl_xor_sync(SQ_FULL, dap, o);
+        }
+        if(valid && s == 0) {
             // gravshort2.hpp:88-107
             accel[3 * tidx] = dax * P.Ka;
             accel[3 * tidx + 1] = day * P.Ka;
@@ -627,6 +579,24 @@ sq_walk_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl,
         atomicAdd(&stats[3], st_pair);
         atomicAdd(&stats[4], st_exact);
     }
+}
+
+// ---- per-walk preparation: fixed-point node and source records
+__global__ void sq_walk_prep_nodes_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl, long long n,
+                                          uint4 * __restrict__ icm, uint4 * __restrict__ icl, double qinv, double s, double minv)
+{
+    for(long long i = blockIdx.x * (long long) blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const double4 M = cm[i], C = cl[i];
+        icm[i] = make_uint4(sq_quant(M.x, qinv), sq_quant(M.y, qinv), sq_quant(M.z, qinv), __float_as_uint((float) (M.w * minv)));
+        icl[i] = make_uint4(sq_quant(C.x, qinv), sq_quant(C.y, qinv), sq_quant(C.z, qinv), __float_as_uint((float) (C.w * s)));
+    }
+}
+__global__ void sq_walk_prep_parts_kernel(const double * __restrict__ pos, const float * __restrict__ mass, long long n,
+                                          uint4 * __restrict__ ipart, double qinv, double minv)
+{
+    for(long long i = blockIdx.x * (long long) blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x)
+        ipart[i] = make_uint4(sq_quant(pos[3 * i], qinv), sq_quant(pos[3 * i + 1], qinv), sq_quant(pos[3 * i + 2], qinv),
+                              __float_as_uint((float) ((double) mass[i] * minv)));
 }
 // ------------------------------------------------------------------------------------ host side
 static const double h_sr_x[SQ_NGRAVTAB] = SQ_SHORTRANGE_X_INIT;
@@ -669,25 +639,23 @@ static int sq_walk_table(sq_ctx * c)
     return SQ_OK;
 }
 
-template <bool POT>
+template <bool POT, int G>
 static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets, const sq_walk_par & P)
 {
     const size_t smem = TAB_BYTES + WALK_WARPS * sizeof(sq_walk_warp_smem);
-    SQ_CUDA(cudaFuncSetAttribute(sq_walk_kernel<POT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    SQ_CUDA(cudaFuncSetAttribute(sq_walk_kernel<POT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = 0;
-    SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sq_walk_kernel<POT>, WALK_THREADS, smem));
+    SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sq_walk_kernel<POT, G>, WALK_THREADS, smem));
     if(per_sm < 1) per_sm = 1;
-    const int64_t ngroups = (ntargets + P.gw - 1) / P.gw;
+    const int64_t ngroups = (ntargets + G - 1) / G;
     int64_t grid = (int64_t) c->num_sms * per_sm;
     const int64_t need = (ngroups + WALK_WARPS - 1) / WALK_WARPS;
     if(grid > need) grid = need;
     if(grid < 1) grid = 1;
-    const double * spos = c->tree_identity ? c->pos.as<double>() : c->tree_pos.as<double>();
-    const float * smass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
-    sq_walk_kernel<POT><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
-            spos, smass, c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(), targets, (long long) ntargets,
-            c->w_table.as<float2>() + (POT ? TAB_ROWS : 0), c->w_accel.as<double>(), c->w_pot.as<double>(), c->w_stats.as<unsigned long long>(),
-            c->w_counter.as<int>(), P);
+    sq_walk_kernel<POT, G><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->w_icm.as<uint4>(), c->w_icl.as<uint4>(), c->t_lk.as<int4>(),
+            c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->w_ipart.as<uint4>(), c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(),
+            targets, (long long) ntargets, c->w_table.as<float2>() + (POT ? TAB_ROWS : 0), c->w_accel.as<double>(), c->w_pot.as<double>(),
+            c->w_stats.as<unsigned long long>(), c->w_counter.as<int>(), P);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
     return SQ_OK;
@@ -732,11 +700,14 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     P.minv = 1.0 / munit;
     P.Ka = P.G * munit * P.s * P.s;
     P.Kp = munit * P.s;
-    P.gw = sq_walk_group_width;
+    const int G = sq_walk_group_width;
+    if(G != 8 && G != 16 && G != 32) { sq_set_error("sq_tree_walk: group width must be 8, 16 or 32"); return SQ_ERR_ARG; }
+    P.qinv = 4294967296.0 / P.box;
+    P.qs = (float) (P.box * P.s / 4294967296.0);
     P.f_rcut = (float) (P.rcut * P.s);
     P.f_rc2_lo = (float) (P.rcut2 * P.s * P.s) * (1.f - SQ_EPS);
     P.f_rc2_hi = (float) (P.rcut2 * P.s * P.s) * (1.f + SQ_EPS);
-    P.f_bh2 = (float) P.bh2;
+    P.f_invbh2 = (float) (1.0 / P.bh2);
     P.f_hs = (float) (P.h * P.s);
     P.f_h2 = P.f_hs * P.f_hs;
     P.f_boxs = (float) (P.box * P.s);
@@ -761,8 +732,23 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     SQ_CUDA(cudaMemsetAsync(c->w_accel.p, 0, sizeof(double) * 3 * (size_t) n, c->stream));
     if(pot) SQ_CUDA(cudaMemsetAsync(c->w_pot.p, 0, sizeof(double) * (size_t) n, c->stream));
     SQ_CUDA(cudaEventRecord(c->ev[8], c->stream));
-    if(ntargets > 0)
-        SQ_TRY(pot ? sq_walk_launch<true>(c, targets, ntargets, P) : sq_walk_launch<false>(c, targets, ntargets, P));
+    if(ntargets > 0) {
+        // fixed-point node and source records for this walk (scales depend on the call's parameters)
+        const double * spos = c->tree_identity ? c->pos.as<double>() : c->tree_pos.as<double>();
+        const float * smass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
+        SQ_TRY(c->w_icm.reserve(sizeof(uint4) * (size_t) (c->tree_numnodes + 1)));
+        SQ_TRY(c->w_icl.reserve(sizeof(uint4) * (size_t) (c->tree_numnodes + 1)));
+        SQ_TRY(c->w_ipart.reserve(sizeof(uint4) * (size_t) (c->tree_np + 1)));
+        sq_walk_prep_nodes_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), (long long) c->tree_numnodes,
+                c->w_icm.as<uint4>(), c->w_icl.as<uint4>(), P.qinv, P.s, P.minv);
+        sq_walk_prep_parts_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(spos, smass, (long long) c->tree_np, c->w_ipart.as<uint4>(), P.qinv, P.minv);
+        c->kernel_launches += 2;
+        SQ_CUDA(cudaGetLastError());
+        int rc;
+        if(pot) rc = G == 8 ? sq_walk_launch<true, 8>(c, targets, ntargets, P) : (G == 16 ? sq_walk_launch<true, 16>(c, targets, ntargets, P) : sq_walk_launch<true, 32>(c, targets, ntargets, P));
+        else rc = G == 8 ? sq_walk_launch<false, 8>(c, targets, ntargets, P) : (G == 16 ? sq_walk_launch<false, 16>(c, targets, ntargets, P) : sq_walk_launch<false, 32>(c, targets, ntargets, P));
+        SQ_TRY(rc);
+    }
     SQ_CUDA(cudaEventRecord(c->ev[9], c->stream));
     unsigned long long h_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     SQ_CUDA(cudaMemcpyAsync(h_stats, c->w_stats.p, sizeof(h_stats), cudaMemcpyDeviceToHost, c->stream));
@@ -774,7 +760,7 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     c->walk_ntargets = ntargets;
     if(stats) {
         stats->ntargets = ntargets;
-        stats->ngroups = (ntargets + P.gw - 1) / P.gw;
+        stats->ngroups = (ntargets + G - 1) / G;
         stats->interactions = (int64_t) h_stats[0];
         stats->list_entries = (int64_t) h_stats[1];
         stats->nodes_tested = (int64_t) h_stats[2];
