@@ -66,12 +66,15 @@ struct sq_walk_par {
 };
 
 struct sq_walk_warp_smem {
-    float4 lst[LIST_CAP + LIST_PAD];   // interaction list: x, y, z relative to the group centre (table units), mass
+    // interaction list, structure of arrays so that one 128-bit LDS brings the same coordinate of 4 consecutive steps
+    // of a slice into an aligned register quad (= two operands of the packed FP32 instructions): the entry at list
+    // position p (step i = p / S, slice p % S) lives at sq_list_slot<S>(p)
+    float lx[LIST_CAP + LIST_PAD], ly[LIST_CAP + LIST_PAD], lz[LIST_CAP + LIST_PAD], lm[LIST_CAP + LIST_PAD];
     float4 nl[NEAR_CAP];               // near list (careful loop)
-    float4 tgt[32];                    // targets: x, y, z, errtol*|a_old| scaled
     int2 stack[STACK_CAP];
     unsigned mw[LIST_CAP + LIST_PAD];  // mask words, one per evaluation step: bit (s*G + t) = entry of slice s reaches target t
     unsigned nm[NEAR_CAP];
+    float4 nrec[32][3];                // tier 2 work list: (cm.xyz, dr2) (centre.xyz, de) (len, M l^2, need mask, -)
     int s_end[32], s_first[32];
     unsigned s_mask[32];
 };
@@ -141,56 +144,81 @@ __device__ __noinline__ int sq_exact_class(const double4 M, const double4 C, dou
 }
 
 
-// ---- fast evaluation: lane = (slice s, target t); step i gives slice s the entry i*S + s (one 128-bit LDS with one
-// address per slice costs the same as a warp-wide broadcast) and mask word i, whose bit `lane` says whether that
-// entry reaches this lane's target.  Every genuine entry is farther than the softening length from every target of
-// the group (the others are in the near list), padding entries are SQ_FAR away, so r2 > 0 and no softening or
-// wrap test is needed.  Table (gravity.h:50-60): i = floor(r), linear interpolation, zero from row 511 on.
+template <int S>
+__device__ __forceinline__ int sq_list_slot(int p)
+{
+    const int i = p / S, sl = p % S;
+    return (((i >> 2) * S + sl) << 2) + (i & 3);
+}
+
+// ---- fast evaluation: lane = (slice s, target t); step i gives slice s the entry i*S + s and mask word i, whose bit
+// `lane` says whether that entry reaches this lane's target.  Two steps at a time in packed FP32 (FADD2 / FMUL2 /
+// FFMA2 of sm_100: two results per issue slot; MUFU, the table reads and the mask selects stay scalar).
+// Every genuine entry is farther than the softening length from every target of the group (the others are in the
+// near list), padding entries are SQ_FAR away, so r2 > 0 and no softening or wrap test is needed.
+// Table (gravity.h:50-60): i = floor(r), linear interpolation, zero from row 511 on.
 //   !POT: row i = (value at the middle of [i, i+1], slope); row 511 = (0, 0)
 //    POT: row i = (force[i], potential[i]); rows i and i+1 are read; the r < 511 test zeroes the tail
+struct sq_acc2 { float2 x, y, z, p; };
+
+template <bool POT>
+__device__ __forceinline__ void sq_eval_pair(float x0, float x1, float y0, float y1, float z0, float z1, float m0, float m1, bool on0, bool on1,
+                                             unsigned tabaddr, float2 ntx, float2 nty, float2 ntz, sq_acc2 & A)
+{
+    const float2 dx = __fadd2_rn(make_float2(x0, x1), ntx), dy = __fadd2_rn(make_float2(y0, y1), nty), dz = __fadd2_rn(make_float2(z0, z1), ntz);
+    const float2 r2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+    const float2 rinv = make_float2(sq_rsqrt(r2.x), sq_rsqrt(r2.y));
+    // xq = r - 1/2; round-to-nearest of xq = floor(r); d = r - floor(r) - 1/2
+    float2 xq = __ffma2_rn(r2, rinv, make_float2(-0.5f, -0.5f));
+    xq.x = fminf(xq.x, 511.f); xq.y = fminf(xq.y, 511.f);
+    const float2 tt = __fadd2_rn(xq, make_float2(SQ_MAGIC, SQ_MAGIC));
+    const float2 fl = __fadd2_rn(tt, make_float2(-SQ_MAGIC, -SQ_MAGIC));
+    const float2 d = __ffma2_rn(fl, make_float2(-1.f, -1.f), xq);
+    const unsigned a0 = ((unsigned) __float_as_int(tt.x) << 7) + tabaddr, a1 = ((unsigned) __float_as_int(tt.y) << 7) + tabaddr;
+    const float2 rinv2 = __fmul2_rn(rinv, rinv);
+    if(POT) {
+        const float2 e00 = sq_lds_f2(a0), e01 = sq_lds_f2(a0 + 128), e10 = sq_lds_f2(a1), e11 = sq_lds_f2(a1 + 128);
+        const float2 fr = __fadd2_rn(d, make_float2(0.5f, 0.5f));
+        const float2 w0 = __ffma2_rn(make_float2(fr.x, fr.x), __ffma2_rn(e00, make_float2(-1.f, -1.f), e01), e00);   // (force, potential) window of entry 0
+        const float2 w1 = __ffma2_rn(make_float2(fr.y, fr.y), __ffma2_rn(e10, make_float2(-1.f, -1.f), e11), e10);
+        const float2 mm = make_float2((on0 && r2.x < 261121.f) ? m0 : 0.f, (on1 && r2.y < 261121.f) ? m1 : 0.f);
+        const float2 mr = __fmul2_rn(mm, rinv);
+        const float2 fac = __fmul2_rn(__fmul2_rn(mr, rinv2), make_float2(w0.x, w1.x));
+        A.x = __ffma2_rn(dx, fac, A.x);
+        A.y = __ffma2_rn(dy, fac, A.y);
+        A.z = __ffma2_rn(dz, fac, A.z);
+        A.p = __ffma2_rn(mr, make_float2(w0.y, w1.y), A.p);       // sign applied at the flush
+    } else {
+        const float2 w0 = sq_lds_f2(a0), w1 = sq_lds_f2(a1);
+        const float2 wf = make_float2(fmaf(d.x, w0.y, w0.x), fmaf(d.y, w1.y, w1.x));
+        const float2 mm = make_float2(on0 ? m0 : 0.f, on1 ? m1 : 0.f);
+        const float2 fac = __fmul2_rn(__fmul2_rn(mm, rinv2), __fmul2_rn(rinv, wf));
+        A.x = __ffma2_rn(dx, fac, A.x);
+        A.y = __ffma2_rn(dy, fac, A.y);
+        A.z = __ffma2_rn(dz, fac, A.z);
+    }
+}
+
 template <bool POT, int S>
 __device__ __forceinline__ void sq_eval_list(const sq_walk_warp_smem & W, int nsteps4, unsigned tabaddr, float tx, float ty, float tz,
                                              int s, unsigned lanebit, float & ax, float & ay, float & az, float & ap)
 {
     const uint4 * mw4 = reinterpret_cast<const uint4 *>(W.mw);
-    const float4 * lst = W.lst + s;
+    const float4 * X = reinterpret_cast<const float4 *>(W.lx) + s, * Y = reinterpret_cast<const float4 *>(W.ly) + s;
+    const float4 * Z = reinterpret_cast<const float4 *>(W.lz) + s, * M = reinterpret_cast<const float4 *>(W.lm) + s;
+    const float2 ntx = make_float2(-tx, -tx), nty = make_float2(-ty, -ty), ntz = make_float2(-tz, -tz);
+    sq_acc2 A;
+    A.x = A.y = A.z = A.p = make_float2(0.f, 0.f);
     const int nb = nsteps4 >> 2;
+    #pragma unroll 2
     for(int b = 0; b < nb; b++) {
         const uint4 w4 = mw4[b];
-        #pragma unroll
-        for(int j = 0; j < 4; j++) {
-            const float4 src = lst[(4 * b + j) * S];
-            const unsigned wj = j == 0 ? w4.x : (j == 1 ? w4.y : (j == 2 ? w4.z : w4.w));
-            const float dx = src.x - tx, dy = src.y - ty, dz = src.z - tz;
-            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-            const bool on = (wj & lanebit) != 0u;
-            const float rinv = sq_rsqrt(r2);
-            // xq = r - 1/2; round-to-nearest of xq = floor(r); d = r - floor(r) - 1/2
-            const float xq = fminf(fmaf(r2, rinv, -0.5f), 511.f);
-            const float t = xq + SQ_MAGIC;
-            const float d = xq - (t - SQ_MAGIC);
-            const unsigned addr = ((unsigned) __float_as_int(t) << 7) + tabaddr;
-            const float rinv2 = rinv * rinv;
-            if(POT) {
-                const float2 e0 = sq_lds_f2(addr), e1 = sq_lds_f2(addr + 128);
-                const float fr = d + 0.5f;
-                const float wf = fmaf(fr, e1.x - e0.x, e0.x), wp = fmaf(fr, e1.y - e0.y, e0.y);
-                const float mm = (on && r2 < 261121.f) ? src.w : 0.f;
-                const float fac = (mm * rinv2) * (rinv * wf);
-                ax = fmaf(dx, fac, ax);
-                ay = fmaf(dy, fac, ay);
-                az = fmaf(dz, fac, az);
-                ap = fmaf(-mm * rinv, wp, ap);
-            } else {
-                const float2 w = sq_lds_f2(addr);
-                const float mm = on ? src.w : 0.f;
-                const float fac = (mm * rinv2) * (rinv * fmaf(d, w.y, w.x));
-                ax = fmaf(dx, fac, ax);
-                ay = fmaf(dy, fac, ay);
-                az = fmaf(dz, fac, az);
-            }
-        }
+        const float4 x4 = X[b * S], y4 = Y[b * S], z4 = Z[b * S], m4 = M[b * S];
+        sq_eval_pair<POT>(x4.x, x4.y, y4.x, y4.y, z4.x, z4.y, m4.x, m4.y, (w4.x & lanebit) != 0u, (w4.y & lanebit) != 0u, tabaddr, ntx, nty, ntz, A);
+        sq_eval_pair<POT>(x4.z, x4.w, y4.z, y4.w, z4.z, z4.w, m4.z, m4.w, (w4.z & lanebit) != 0u, (w4.w & lanebit) != 0u, tabaddr, ntx, nty, ntz, A);
     }
+    ax += A.x.x + A.x.y; ay += A.y.x + A.y.y; az += A.z.x + A.z.y;
+    if(POT) ap -= A.p.x + A.p.y;
 }
 
 // ---- careful evaluation of the near list (slice s takes entries s, s+S, ...): softened pairs (r < 2.8 eps),
@@ -323,7 +351,6 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         const float ty = valid ? (float) (int) (iy - gciy) * P.qs : 2.f * SQ_FAR;
         const float tz = valid ? (float) (int) (iz - gciz) * P.qs : 2.f * SQ_FAR;
         __syncwarp();
-        if(s == 0) W.tgt[t] = make_float4(tx, ty, tz, ta);
         // sources inside this box may come within the softening length of a target -> near list
         const float nhx = ghx + P.f_hs * 1.001f + 1e-3f, nhy = ghy + P.f_hs * 1.001f + 1e-3f, nhz = ghz + P.f_hs * 1.001f + 1e-3f;
         // pairs may straddle the periodic image once group extent + table range reaches half the box
@@ -340,6 +367,9 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             unsigned acc_mask = 0, open_mask = 0;
             int4 L = make_int4(0, 0, -1, 0);
             float4 nodeE = make_float4(0.f, 0.f, 0.f, 0.f);
+            int node = 0;
+            unsigned t2_need = 0, risky_exact = 0;
+            float4 t2_cm = nodeE, t2_cl = nodeE, t2_lm = nodeE;
             if(!drain) {
                 // wide pops only while a depth-first descent (<= 7 entries per level) still fits above them
                 int k = (STACK_CAP - STACK_RESERVE - top) / 7;
@@ -348,7 +378,6 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 k = k > top ? top : k;
                 top -= k;
                 const bool have = (int) lane < k;
-                int node = 0;
                 unsigned mask = 0;
                 if(have) {
                     const int2 e = W.stack[top + lane];
@@ -382,8 +411,8 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                     const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
                     // a node about half a box away from the group: per-target NEAREST may differ from the group's
                     const bool risky = fmaxf(fmaxf(acx + ghx, acy + ghy), fmaxf(acz + ghz, fmaxf(fmaxf(amx + ghx, amy + ghy), amz + ghz))) >= P.f_halfs * 0.999f;
-                    unsigned exact = 0, need = 0;
-                    if(risky) exact = mask;
+                    unsigned need = 0;
+                    if(risky) risky_exact = mask;
                     else {
                         // ---- tier 1: the whole group at once (bounding box, min/max |a_old|).  With the centre of
                         // mass inside the cell "r2 <= Rcut^2" implies the box test, so the box decides keep/discard.
@@ -404,41 +433,83 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                                 if(go_hi) open_mask = mask; else acc_mask = mask;
                             } else need = mask;
                         }
-                        // ---- tier 2: per target, FP32 with error intervals
-                        st_pair += __popc(need);
-                        while(need) {
-                            const int t2 = 31 - __clz(need);
-                            const unsigned bit = 1u << t2;
-                            need ^= bit;
-                            const float4 T = W.tgt[t2];
-                            const float dx = cmx - T.x, dy = cmy - T.y, dz = cmz - T.z;
-                            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                            const float em = fmaxf(fmaxf(fabsf(cx - T.x), fabsf(cy - T.y)), fabsf(cz - T.z));
-                            const bool k_lo = (r2 <= rcA) || !(em > efA);
-                            const bool k_hi = (r2 <= rcB) || !(em > efB);
-                            const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
-                            const bool o_lo = (mlA > r2l * r2l * T.w) || (r2 < bhA) || (em < inA);
-                            const bool o_hi = (mlB > r2h * r2h * T.w) || (r2 < bhB) || (em < inB);
-                            if(k_lo != k_hi || (k_lo && o_lo != o_hi)) exact |= bit;
-                            else if(k_lo) { if(o_lo) open_mask |= bit; else acc_mask |= bit; }
+                        if(need) {
+                            // ---- tier 2 runs transposed below: hand the node over
+                            t2_need = need;
+                            t2_cm = make_float4(cmx, cmy, cmz, dr2);
+                            t2_cl = make_float4(cx, cy, cz, de);
+                            t2_lm = make_float4(len, ml2, 0.f, 0.f);
                         }
                     }
-                    // ---- tier 3: the reference's FP64 expressions on the FP64 node and particle data
-                    if(exact) {
-                        const double4 M = cm[node], C = cl[node];
-                        sq_exact_par X;
-                        X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
-                        while(exact) {
-                            const int t2 = 31 - __clz(exact);
-                            const unsigned bit = 1u << t2;
-                            exact ^= bit;
-                            const long long ti = targets ? (long long) targets[t0 + t2] : (t0 + t2);
-                            const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
-                            st_exact++;
-                            if(c == 1) acc_mask |= bit;
-                            else if(c == 2) open_mask |= bit;
+                }
+            }
+            // ---- tier 2, transposed: lane = (slice s, target t); slice s classifies one handed-over node per step for
+            // all G targets at once (FP32 with error intervals), the masks come back through ballots
+            {
+                const unsigned fb = __ballot_sync(SQ_FULL, t2_need != 0u);
+                if(fb) {
+                    const int nf = __popc(fb);
+                    const int slot = __popc(fb & sq_lanemask_lt());
+                    if(t2_need) {
+                        t2_lm.z = __uint_as_float(t2_need);
+                        W.nrec[slot][0] = t2_cm; W.nrec[slot][1] = t2_cl; W.nrec[slot][2] = t2_lm;
+                    }
+                    st_pair += __popc(t2_need);
+                    __syncwarp();
+                    for(int i0 = 0; i0 < nf; i0 += S) {
+                        const int idx = i0 + s;
+                        const bool act = idx < nf;
+                        const int ii = act ? idx : nf - 1;
+                        const float4 a = W.nrec[ii][0], c4 = W.nrec[ii][1], lm = W.nrec[ii][2];
+                        const float dr2 = a.w, de = c4.w, len = lm.x, ml2 = lm.y;
+                        const bool mine = act && ((__float_as_uint(lm.z) >> t) & 1u);
+                        const float eff = fmaf(0.5f, len, P.f_rcut), ins = 0.6f * len, bhq = len * len * P.f_invbh2;
+                        const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
+                        const float efA = fmaf(eff, 1.f + SQ_EPS, de), efB = fmaf(eff, 1.f - SQ_EPS, -de);
+                        const float inA = fmaf(ins, 1.f + SQ_EPS, de), inB = fmaf(ins, 1.f - SQ_EPS, -de);
+                        const float bhA = fmaf(bhq, 1.f + SQ_EPS, dr2), bhB = fmaf(bhq, 1.f - SQ_EPS, -dr2);
+                        const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
+                        const float dx = a.x - tx, dy = a.y - ty, dz = a.z - tz;
+                        const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                        const float em = fmaxf(fmaxf(fabsf(c4.x - tx), fabsf(c4.y - ty)), fabsf(c4.z - tz));
+                        const bool k_lo = (r2 <= rcA) || !(em > efA);
+                        const bool k_hi = (r2 <= rcB) || !(em > efB);
+                        const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
+                        const bool o_lo = (mlA > r2l * r2l * ta) || (r2 < bhA) || (em < inA);
+                        const bool o_hi = (mlB > r2h * r2h * ta) || (r2 < bhB) || (em < inB);
+                        const bool ex = k_lo != k_hi || (k_lo && o_lo != o_hi);
+                        const unsigned bx = __ballot_sync(SQ_FULL, mine && ex);
+                        const unsigned bo = __ballot_sync(SQ_FULL, mine && !ex && k_lo && o_lo);
+                        const unsigned ba = __ballot_sync(SQ_FULL, mine && !ex && k_lo && !o_lo);
+                        if(act && t == 0) {
+                            const unsigned GM = G == 32 ? 0xffffffffu : ((1u << (G & 31)) - 1u);
+                            W.nrec[idx][2] = make_float4(__uint_as_float((bo >> (G * s)) & GM), __uint_as_float((ba >> (G * s)) & GM),
+                                                         __uint_as_float((bx >> (G * s)) & GM), 0.f);
                         }
                     }
+                    __syncwarp();
+                    if(t2_need) {
+                        const float4 r = W.nrec[slot][2];
+                        open_mask |= __float_as_uint(r.x); acc_mask |= __float_as_uint(r.y); risky_exact |= __float_as_uint(r.z);
+                    }
+                    __syncwarp();
+                }
+            }
+            // ---- tier 3: the reference's FP64 expressions on the FP64 node and particle data
+            if(risky_exact) {
+                unsigned exact = risky_exact;
+                const double4 M = cm[node], C = cl[node];
+                sq_exact_par X;
+                X.box = P.box; X.half = P.half; X.rcut = P.rcut; X.rcut2 = P.rcut2; X.bh2 = P.bh2; X.relative = P.relative;
+                while(exact) {
+                    const int t2 = 31 - __clz(exact);
+                    const unsigned bit = 1u << t2;
+                    exact ^= bit;
+                    const long long ti = targets ? (long long) targets[t0 + t2] : (t0 + t2);
+                    const int c = sq_exact_class(M, C, tpos[3 * ti], tpos[3 * ti + 1], tpos[3 * ti + 2], P.errtol * toldacc[ti], X);
+                    st_exact++;
+                    if(c == 1) acc_mask |= bit;
+                    else if(c == 2) open_mask |= bit;
                 }
             }
             const int type = SQ_INFO_TYPE(L.w);
@@ -517,7 +588,8 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                     // pad to whole groups of 4 steps: far away, reaching nobody
                     const int nsteps4 = ((nlist + S - 1) / S + 3) & ~3;
                     for(int kk = nlist + (int) lane; kk < nsteps4 * S; kk += 32) {
-                        W.lst[kk] = make_float4(SQ_FAR, SQ_FAR, SQ_FAR, 0.f);
+                        const int mp = sq_list_slot<S>(kk);
+                        W.lx[mp] = SQ_FAR; W.ly[mp] = SQ_FAR; W.lz[mp] = SQ_FAR; W.lm[mp] = 0.f;
                         sq_store_field<G>(W.mw, kk, 0u);
                     }
                     __syncwarp();
@@ -531,7 +603,8 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 }
                 if(isfar) {
                     const int p = nlist + __popc(bf & sq_lanemask_lt());
-                    W.lst[p] = e;
+                    const int mp = sq_list_slot<S>(p);
+                    W.lx[mp] = e.x; W.ly[mp] = e.y; W.lz[mp] = e.z; W.lm[mp] = e.w;
                     sq_store_field<G>(W.mw, p, m);
                 }
                 nlist += cf;
