@@ -163,6 +163,42 @@ int sq_pm_force_device(sq_ctx * ctx);
 int sq_pm_paint(sq_ctx * ctx);
 int sq_pm_get_mesh(sq_ctx * ctx, double * mesh);
 
+/* ---- multi-GPU: one rank per GPU (README.rst:67 of the reference), exchanges issued by the host over NCCL ------
+ * Everything below takes DEVICE pointers and runs on the context's stream; the host layer (shenqi_b200/dist.py with
+ * torch.distributed, or a C++ host with raw NCCL) issues the collectives between the calls.
+ * Tree side (stands where the reference exchanges top-leaf moments and exports/imports walks,
+ * libgadget/forcetree.cpp:1144-1282, treewalk2.h:282-373, 742-812): every rank installs the all-gathered, globally
+ * PH-sorted particle set, builds the whole tree and walks only its own range of targets.
+ * PM side (stands behind petapm_force, libgadget/petapm.cpp:371-472, with the region/pencil exchange of
+ * petapm.cpp:692-1107 replaced by routing particles to x-slab owners and the heFFTe transposes, petapm.cpp:281-303,
+ * by an all-to-all between the 2-D and 1-D cuFFT passes). */
+#define SQ_PTR_SORTED_KEYS 0      /* uint64[n]   */
+#define SQ_PTR_SORTED_POS 1       /* double[n][3] */
+#define SQ_PTR_SORTED_MASS 2      /* float[n]    */
+#define SQ_PTR_SORTED_PERM 3      /* uint32[n]: upload index of the particle at sorted position i */
+#define SQ_PTR_WALK_ACCEL 4       /* double[n][3], by sorted position, already x G */
+#define SQ_PTR_WALK_POT 5         /* double[n] */
+#define SQ_PTR_PM_OUT 6           /* double[n][4]: PM potential, fx, fy, fz by sorted position */
+/* Run every later call of this context on the caller's CUDA stream (e.g. torch's current stream). */
+int sq_ctx_set_stream(sq_ctx * ctx, void * cuda_stream);
+int sq_device_ptr(sq_ctx * ctx, int which, void ** ptr, int64_t * count);
+/* sq_upload_particles_soa from device arrays (pos: n x 3 doubles, mass: n floats) */
+int sq_upload_particles_device(sq_ctx * ctx, const double * pos, const float * mass, int64_t n);
+/* 1 if sq_ph_sort found particles whose geometric octants differ from their key digits (exactly on a cell face) */
+int sq_get_geo_mismatch(sq_ctx * ctx, int * flag);
+int sq_set_sorted_device(sq_ctx * ctx, const uint64_t * keys, const double * pos, const float * mass, int64_t n, int geo_mismatch);
+int sq_set_oldacc_range_device(sq_ctx * ctx, int64_t first, int64_t count, const double * oldacc);
+int sq_tree_walk_range(sq_ctx * ctx, int64_t first, int64_t count, sq_walk_stats * stats);
+int sq_pm_slab_route(sq_ctx * ctx, const double * pos, const float * mass, int64_t n, int nranks, double * send4, int32_t * slot, int64_t * counts);
+int sq_pm_slab_unroute(sq_ctx * ctx, const double * back4, const int32_t * slot, int64_t n, double * out4);
+int sq_pm_slab_paint(sq_ctx * ctx, const double * part4, int64_t m, int rank, int nranks, double * slab);
+int sq_pm_slab_fft_fwd(sq_ctx * ctx, double * slab, int nranks, double * work, double * packed);
+int sq_pm_slab_fft_x(sq_ctx * ctx, double * data, int nranks, int inverse);
+int sq_pm_slab_transfer(sq_ctx * ctx, const double * rho, int rank, int nranks, double * out4);
+int sq_pm_slab_fft_inv(sq_ctx * ctx, const double * recv, int nranks, double * work, double * slab);
+int sq_pm_slab_readout(sq_ctx * ctx, const double * part4, int64_t m, int rank, int nranks, const double * s0, const double * s1,
+                       const double * s2, const double * s3, double * out4);
+
 /* ---- timing of the last device stages (CUDA events on the launching stream), milliseconds ------ */
 typedef struct sq_timings {
     double keys_ms, sort_ms, gather_ms, tree_build_ms, tree_moments_ms, walk_ms;

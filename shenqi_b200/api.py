@@ -64,7 +64,12 @@ class Timings(ctypes.Structure):
 EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_set_walk_raw", "sq_sync", "sq_default_aos_layout",
            "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
-           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak"]
+           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
+           "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
+           "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer",
+           "sq_pm_slab_fft_inv", "sq_pm_slab_readout"]
+
+PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
 
 def library_path():
@@ -230,3 +235,61 @@ class Context:
         """Targets per warp in the walk (32, 16 or 8): tuning knob."""
         assert g in (8, 16, 32)
         ctypes.c_int.in_dll(self.L, "sq_walk_group_width").value = g
+
+    # ---- multi-GPU entry points: raw device pointers (ints), see include/shenqi_b200.h and shenqi_b200/dist.py
+    def set_stream(self, cuda_stream):
+        self._check(self.L.sq_ctx_set_stream(self._ctx, ctypes.c_void_p(cuda_stream)))
+
+    def device_ptr(self, which):
+        p = ctypes.c_void_p(); n = c_i64()
+        self._check(self.L.sq_device_ptr(self._ctx, c_int(which), ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def upload_particles_device(self, pos_ptr, mass_ptr, n):
+        self.n = n
+        self._check(self.L.sq_upload_particles_device(self._ctx, ctypes.c_void_p(pos_ptr), ctypes.c_void_p(mass_ptr), c_i64(n)))
+
+    def geo_mismatch(self):
+        f = c_int()
+        self._check(self.L.sq_get_geo_mismatch(self._ctx, ctypes.byref(f)))
+        return f.value
+
+    def set_sorted_device(self, keys_ptr, pos_ptr, mass_ptr, n, geo_mismatch=0):
+        self.n = n
+        self._check(self.L.sq_set_sorted_device(self._ctx, ctypes.c_void_p(keys_ptr), ctypes.c_void_p(pos_ptr), ctypes.c_void_p(mass_ptr), c_i64(n), c_int(geo_mismatch)))
+
+    def set_oldacc_range_device(self, first, count, oldacc_ptr):
+        self._check(self.L.sq_set_oldacc_range_device(self._ctx, c_i64(first), c_i64(count), ctypes.c_void_p(oldacc_ptr)))
+
+    def tree_walk_range(self, first, count):
+        st = WalkStats()
+        self._check(self.L.sq_tree_walk_range(self._ctx, c_i64(first), c_i64(count), ctypes.byref(st)))
+        return st
+
+    def pm_slab_route(self, pos_ptr, mass_ptr, n, nranks, send4_ptr, slot_ptr):
+        counts = (c_i64 * nranks)()
+        self._check(self.L.sq_pm_slab_route(self._ctx, ctypes.c_void_p(pos_ptr), ctypes.c_void_p(mass_ptr), c_i64(n), c_int(nranks),
+                                            ctypes.c_void_p(send4_ptr), ctypes.c_void_p(slot_ptr), counts))
+        return [int(x) for x in counts]
+
+    def pm_slab_unroute(self, back4_ptr, slot_ptr, n, out4_ptr):
+        self._check(self.L.sq_pm_slab_unroute(self._ctx, ctypes.c_void_p(back4_ptr), ctypes.c_void_p(slot_ptr), c_i64(n), ctypes.c_void_p(out4_ptr)))
+
+    def pm_slab_paint(self, part4_ptr, m, rank, nranks, slab_ptr):
+        self._check(self.L.sq_pm_slab_paint(self._ctx, ctypes.c_void_p(part4_ptr), c_i64(m), c_int(rank), c_int(nranks), ctypes.c_void_p(slab_ptr)))
+
+    def pm_slab_fft_fwd(self, slab_ptr, nranks, work_ptr, packed_ptr):
+        self._check(self.L.sq_pm_slab_fft_fwd(self._ctx, ctypes.c_void_p(slab_ptr), c_int(nranks), ctypes.c_void_p(work_ptr), ctypes.c_void_p(packed_ptr)))
+
+    def pm_slab_fft_x(self, data_ptr, nranks, inverse):
+        self._check(self.L.sq_pm_slab_fft_x(self._ctx, ctypes.c_void_p(data_ptr), c_int(nranks), c_int(1 if inverse else 0)))
+
+    def pm_slab_transfer(self, rho_ptr, rank, nranks, out4_ptr):
+        self._check(self.L.sq_pm_slab_transfer(self._ctx, ctypes.c_void_p(rho_ptr), c_int(rank), c_int(nranks), ctypes.c_void_p(out4_ptr)))
+
+    def pm_slab_fft_inv(self, recv_ptr, nranks, work_ptr, slab_ptr):
+        self._check(self.L.sq_pm_slab_fft_inv(self._ctx, ctypes.c_void_p(recv_ptr), c_int(nranks), ctypes.c_void_p(work_ptr), ctypes.c_void_p(slab_ptr)))
+
+    def pm_slab_readout(self, part4_ptr, m, rank, nranks, slab_ptrs, out4_ptr):
+        self._check(self.L.sq_pm_slab_readout(self._ctx, ctypes.c_void_p(part4_ptr), c_i64(m), c_int(rank), c_int(nranks),
+                                              *[ctypes.c_void_p(p) for p in slab_ptrs], ctypes.c_void_p(out4_ptr)))

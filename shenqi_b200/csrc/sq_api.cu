@@ -105,15 +105,16 @@ void sq_ctx_destroy(sq_ctx * c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     sq_pm_destroy(c);
+    sq_dist_destroy(c);
     sq_buf * bufs[] = {&c->pos_in, &c->mass_in, &c->id_in, &c->type_in, &c->oldacc_in, &c->keys_in, &c->pos, &c->mass, &c->oldacc, &c->keys,
                        &c->perm, &c->rank, &c->sort_tmp_keys, &c->sort_tmp_vals, &c->sort_hist, &c->scan_tmp, &c->flag_tmp, &c->t_cm, &c->t_cl,
                        &c->t_lk, &c->t_parent, &c->t_rot, &c->t_lvl, &c->t_counters, &c->tree_keys, &c->tree_order, &c->tree_pos, &c->tree_mass,
                        &c->active_sorted, &c->w_accel, &c->w_pot, &c->w_stats, &c->w_targets, &c->w_table, &c->w_out_accel, &c->w_out_pot,
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
-                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out};
+                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
-    if(c->stream) cudaStreamDestroy(c->stream);
+    if(c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 

@@ -122,6 +122,13 @@ struct sq_ctx {
     cufftHandle plan_r2c = 0, plan_c2r = 0;
     int plan_nmesh = 0;
     bool pm_done = false;
+
+    // ---- multi-GPU (sq_dist.cu)
+    bool own_stream = true;
+    int64_t range_first = 0, range_count = -1;      // sq_tree_walk_range: targets = this range of the sorted set
+    cufftHandle slab_r2c = 0, slab_c2r = 0, slab_x = 0;
+    int slab_N = 0, slab_P = 0;
+    sq_buf slab_tab, route_tmp;
 };
 
 static inline int sq_div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }
@@ -160,3 +167,5 @@ int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_
 int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
 int sq_pm_run(sq_ctx * c, bool paint_only);
 void sq_pm_destroy(sq_ctx * c);
+void sq_dist_destroy(sq_ctx * c);
+int sq_walk_range_targets(sq_ctx * c, sq_buf * out);

@@ -794,6 +794,11 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     if(active) {
         SQ_TRY(sq_active_to_sorted(c, active, nactive, &c->w_targets, &ntargets));
         targets = c->w_targets.as<uint32_t>();
+    } else if(c->range_count >= 0) {
+        // sq_tree_walk_range: this rank's share of a globally sorted set
+        SQ_TRY(sq_walk_range_targets(c, &c->w_targets));
+        targets = c->w_targets.as<uint32_t>();
+        ntargets = c->range_count;
     }
     const bool pot = c->tree_full;     // update_potential = tree->full_particle_tree_flag (gravshort-tree2.cpp:148)
     SQ_TRY(c->w_accel.reserve(sizeof(double) * 3 * (size_t) (n + 1)));

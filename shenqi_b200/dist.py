@@ -1,0 +1,334 @@
+"""Multi-GPU short-range TreePM step: one rank per GPU, exchanges over torch.distributed (NCCL on NVLink / NVSwitch;
+gloo on CPU for the tests of this host logic).  SURVEY.md section 8e.
+
+What is exchanged (and what the reference exchanges at the same place):
+  * tree: every rank sorts its own particles, the sorted (key, pos, mass) ranges are all-gathered in rank order
+    (= global Peano-Hilbert order, ranks own consecutive key ranges as after the reference's domain decomposition),
+    every rank builds the whole tree and walks only its own targets.  The reference instead exchanges top-leaf
+    moments (forcetree.cpp:1144-1282) and exports each boundary walk to the owner of the pseudo node and imports
+    the partial result (treewalk2.h:282-373, 742-812); results are identical because the global tree is the same
+    oct-tree.  The replicated fixed-point tree costs 16 B per particle + 48 B per node per GPU: 1024^3 particles fit.
+  * PM: x-slabs.  Particles go to the owner of their x-plane (all-to-all of 32-byte records), are painted there,
+    the one ghost plane goes to the next rank; the 3-D FFT is 2-D per plane, one all-to-all transpose, 1-D along x
+    (forward once, backward for the potential and the three force components); results return by the reverse
+    all-to-all.  The reference exchanges painted cells as z-pencils between domain owner and FFT owner
+    (petapm.cpp:692-1107) around heFFTe's own transposes (petapm.cpp:281-303).
+
+The compute between the exchanges is behind a small backend interface: `CudaBackend` (below) calls the C ABI of
+libshenqi_b200.so with device pointers of torch tensors; the CPU tests pass a numpy backend built on the oracle.
+"""
+import torch
+import torch.distributed as dist
+
+
+class Comm:
+    """The collectives the step needs, on whatever backend the default process group has."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.nccl = dist.is_initialized() and dist.get_backend(group) == "nccl"
+        self.bytes_sent = 0
+
+    def allgather_ints(self, vals, device):
+        """vals: list of python ints of this rank -> [world][len(vals)] list"""
+        t = torch.tensor(vals, dtype=torch.int64, device=device)
+        if self.world == 1:
+            return [list(vals)]
+        out = torch.empty(self.world * len(vals), dtype=torch.int64, device=device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        return out.view(self.world, len(vals)).tolist()
+
+    def allgather_rows(self, t, counts):
+        """t: [counts[rank], ...] -> concatenation over ranks in rank order"""
+        if self.world == 1:
+            return t
+        mx = max(counts)
+        pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad[: t.shape[0]] = t
+        out = torch.empty((self.world * mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, pad, group=self.group)
+        self.bytes_sent += pad.numel() * pad.element_size() * (self.world - 1)
+        if all(c == mx for c in counts):
+            return out
+        out = out.view((self.world, mx) + tuple(t.shape[1:]))
+        return torch.cat([out[r, : counts[r]] for r in range(self.world)], 0)
+
+    def alltoall_rows(self, send, send_counts, recv_counts):
+        """send: rows grouped by destination rank (send_counts[r] rows to rank r) -> rows grouped by source rank"""
+        if self.world == 1:
+            return send
+        recv = torch.empty((sum(recv_counts),) + tuple(send.shape[1:]), dtype=send.dtype, device=send.device)
+        self.bytes_sent += (send.shape[0] - send_counts[self.rank]) * send[0:1].numel() * send.element_size()
+        if self.nccl:
+            dist.all_to_all_single(recv, send.contiguous(), list(recv_counts), list(send_counts), group=self.group)
+            return recv
+        self._p2p_alltoall(list(torch.split(send, list(send_counts))), list(torch.split(recv, list(recv_counts))))
+        return recv
+
+    def alltoall_equal(self, send):
+        """send: [world, ...] block q goes to rank q -> [world, ...] block p came from rank p"""
+        if self.world == 1:
+            return send
+        send = send.contiguous()
+        recv = torch.empty_like(send)
+        self.bytes_sent += send.numel() * send.element_size() * (self.world - 1) // self.world
+        if self.nccl and not send.is_complex():
+            dist.all_to_all_single(recv, send, group=self.group)
+        elif self.nccl:
+            dist.all_to_all_single(torch.view_as_real(recv), torch.view_as_real(send), group=self.group)
+        else:
+            self._p2p_alltoall([send[q] for q in range(self.world)], [recv[q] for q in range(self.world)])
+        return recv
+
+    def _p2p_alltoall(self, sends, recvs):
+        # gloo has no all-to-all: pairwise exchange, lower rank sends first
+        recvs[self.rank].copy_(sends[self.rank])
+        for k in range(1, self.world):
+            dst = (self.rank + k) % self.world
+            src = (self.rank - k) % self.world
+            s = sends[dst].contiguous()
+            r = torch.empty_like(recvs[src]) if not recvs[src].is_contiguous() else recvs[src]
+            if s.is_complex():
+                s = torch.view_as_real(s); rr = torch.view_as_real(r)
+            else:
+                rr = r
+            ops = []
+            if s.numel():
+                ops.append(dist.P2POp(dist.isend, s, dst, self.group))
+            if rr.numel():
+                ops.append(dist.P2POp(dist.irecv, rr, src, self.group))
+            for w in (dist.batch_isend_irecv(ops) if ops else []):
+                w.wait()
+            if r is not recvs[src]:
+                recvs[src].copy_(r)
+
+    def shift(self, t, step):
+        """send t to rank + step, return what rank - step sent (periodic)"""
+        if self.world == 1:
+            return t.clone()
+        t = t.contiguous()
+        out = torch.empty_like(t)
+        dst, src = (self.rank + step) % self.world, (self.rank - step) % self.world
+        self.bytes_sent += t.numel() * t.element_size()
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, t, dst, self.group), dist.P2POp(dist.irecv, out, src, self.group)]):
+            w.wait()
+        return out
+
+    def barrier(self):
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
+
+class DistGravity:
+    """One rank of the distributed force step.  `backend` does the local compute (CudaBackend or the tests' CPU one)."""
+
+    def __init__(self, backend, comm=None):
+        self.B = backend
+        self.comm = comm or Comm()
+        self.rank, self.world = self.comm.rank, self.comm.world
+
+    # ------------------------------------------------------------------ short-range tree force
+    def tree_force(self, pos, mass, oldacc=None):
+        """pos [n,3] f64, mass [n] f32: this rank's particles (it must own a consecutive Peano-Hilbert key range, ranks in
+        key order); oldacc [n] = |FullTreeGravAccel + GravPM| / G for the relative criterion or None.
+        Returns (accel [n,3] already x G, potential [n] or None, stats) in the caller's particle order."""
+        B, C = self.B, self.comm
+        n = pos.shape[0]
+        srt = B.sort_local(pos, mass)
+        kmin = int(srt["keys"][0].item()) if n else 2 ** 63 - 1
+        kmax = int(srt["keys"][-1].item()) if n else -1
+        info = C.allgather_ints([n, kmin, kmax, int(srt["geo"])], B.device)
+        counts = [r[0] for r in info]
+        last = -1
+        for r in info:      # keys are 63-bit, so the int64 view orders like the uint64 keys
+            if r[0] and r[1] < last:
+                raise ValueError("ranks must own consecutive Peano-Hilbert key ranges in rank order (domain decomposition)")
+            if r[0]:
+                last = r[2]
+        gk = C.allgather_rows(srt["keys"], counts)
+        gp = C.allgather_rows(srt["pos"], counts)
+        gm = C.allgather_rows(srt["mass"], counts)
+        B.install_global(gk, gp, gm, max(r[3] for r in info))
+        self.tree_info = B.tree_build()
+        first = sum(counts[: self.rank])
+        perm = srt["perm"]
+        if oldacc is not None:
+            B.set_oldacc_range(first, oldacc[perm].contiguous())
+        acc_s, pot_s, st = B.walk_range(first, n)
+        accel = torch.empty_like(acc_s)
+        accel[perm] = acc_s
+        pot = None
+        if pot_s is not None:
+            pot = torch.empty_like(pot_s)
+            pot[perm] = pot_s
+        return accel, pot, st
+
+    # ------------------------------------------------------------------ particle-mesh force
+    def pm_force(self, pos, mass):
+        """Returns out4 [n,4] = (PM potential, fx, fy, fz) for this rank's particles, in their order."""
+        B, C = self.B, self.comm
+        P, r = self.world, self.rank
+        N = B.nmesh
+        if N % P or N % 2:
+            raise ValueError("Nmesh %d must be even and divisible by the number of ranks %d" % (N, P))
+        nxl, nyl, nzh = N // P, N // P, N // 2 + 1
+        send4, slot, counts = B.route(pos, mass, P)
+        rc = C.allgather_ints(list(counts), B.device)
+        recv_counts = [rc[q][r] for q in range(P)]
+        part4 = C.alltoall_rows(send4, counts, recv_counts)
+        slab = B.slab_paint(part4, r, P)                       # [(nxl + 1), N, N]; last plane = ghost
+        slab[0] += C.shift(slab[nxl], +1)                      # my ghost belongs to the next rank's first plane
+        packed = B.fft_fwd(slab, P)                            # [P, nxl, nyl, nzh] complex
+        rho = C.alltoall_equal(packed).view(N, nyl, nzh)       # block p holds planes p*nxl ..: x is the slowest index
+        B.fft_x(rho, P, False)
+        out4 = B.transfer(rho, r, P)                           # [4, N, nyl, nzh]: phi_k, Fx_k, Fy_k, Fz_k
+        slabs = []
+        for f in range(4):
+            B.fft_x(out4[f], P, True)
+            recv = C.alltoall_equal(out4[f].view(P, nxl, nyl, nzh))
+            s = slab if f == 0 else B.new_slab(P, f)
+            B.fft_inv(recv, P, s)
+            slabs.append(s)
+        for s in slabs:                                        # ghost plane = the next rank's first plane
+            s[nxl] = C.shift(s[0], -1)
+        res = B.readout(part4, r, P, slabs)
+        back = C.alltoall_rows(res, recv_counts, counts)
+        return B.unroute(back, slot)
+
+
+class CudaBackend:
+    """Local compute of DistGravity on one B200 through the C ABI (device pointers of torch tensors).
+    Two library contexts: `loc` sorts and routes this rank's own particles, `glob` holds the all-gathered set, the tree
+    and the walk.  Both run on torch's current stream, so the exchanges and the kernels are ordered without host syncs."""
+
+    def __init__(self, params, device):
+        from . import api
+        self.api = api
+        self.device = torch.device("cuda", device) if isinstance(device, int) else device
+        torch.cuda.set_device(self.device)
+        self.loc = api.Context(self.device.index)
+        self.glob = api.Context(self.device.index)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        self.loc.set_stream(stream); self.glob.set_stream(stream)
+        self.set_params(params)
+        self._slabs = {}
+
+    def set_params(self, params):
+        self.params = params
+        self.nmesh = params.Nmesh
+        self.loc.set_params(params)
+        self.glob.set_params(params)
+
+    def close(self):
+        self.loc.close(); self.glob.close()
+
+    def _wrap(self, ptr, shape, dtype):
+        """torch view of library-owned device memory (valid until the library reallocates it)"""
+        n = 1
+        for s in shape:
+            n *= s
+        esz = torch.empty(0, dtype=dtype).element_size()
+
+        class _Mem:      # __cuda_array_interface__ holder
+            pass
+        m = _Mem()
+        typestr = {torch.float64: "<f8", torch.float32: "<f4", torch.int64: "<i8", torch.int32: "<i4"}[dtype]
+        m.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 2, "strides": None}
+        return torch.as_tensor(m, device=self.device) if n else torch.empty(shape, dtype=dtype, device=self.device)
+
+    # ---- tree side
+    def sort_local(self, pos, mass):
+        """this rank's particles (host or device tensors) -> PH-sorted device tensors (views of library memory)"""
+        n = pos.shape[0]
+        if pos.is_cuda:
+            self.loc.upload_particles_device(pos.contiguous().data_ptr(), mass.contiguous().data_ptr(), n)
+        else:
+            self.loc.upload_particles(pos.numpy(), mass.numpy())
+        self.loc.ph_sort()
+        A = self.api
+        keys = self._wrap(self.loc.device_ptr(A.PTR_SORTED_KEYS)[0], (n,), torch.int64)
+        spos = self._wrap(self.loc.device_ptr(A.PTR_SORTED_POS)[0], (n, 3), torch.float64)
+        smass = self._wrap(self.loc.device_ptr(A.PTR_SORTED_MASS)[0], (n,), torch.float32)
+        perm = self._wrap(self.loc.device_ptr(A.PTR_SORTED_PERM)[0], (n,), torch.int32).to(torch.int64)
+        # "geometric path differs from the key digits" (particles exactly on cell faces): carried to the global tree
+        return {"keys": keys, "pos": spos, "mass": smass, "perm": perm, "geo": self.loc.geo_mismatch()}
+
+    def install_global(self, keys, pos, mass, geo):
+        self.glob.set_sorted_device(keys.data_ptr(), pos.data_ptr(), mass.data_ptr(), keys.shape[0], geo)
+
+    def tree_build(self):
+        return self.glob.tree_build()
+
+    def set_oldacc_range(self, first, oldacc_sorted):
+        self.glob.set_oldacc_range_device(first, oldacc_sorted.shape[0], oldacc_sorted.data_ptr())
+
+    def walk_range(self, first, count):
+        st = self.glob.tree_walk_range(first, count)
+        A = self.api
+        n = self.glob.n
+        acc = self._wrap(self.glob.device_ptr(A.PTR_WALK_ACCEL)[0], (n, 3), torch.float64)[first:first + count]
+        try:
+            pot = self._wrap(self.glob.device_ptr(A.PTR_WALK_POT)[0], (n,), torch.float64)[first:first + count]
+        except A.ShenqiError:
+            pot = None
+        return acc, pot, st
+
+    # ---- PM side
+    def route(self, pos, mass, P):
+        n = pos.shape[0]
+        send4 = torch.empty((n, 4), dtype=torch.float64, device=self.device)
+        slot = torch.empty(n, dtype=torch.int32, device=self.device)
+        counts = self.loc.pm_slab_route(pos.data_ptr(), mass.data_ptr(), n, P, send4.data_ptr(), slot.data_ptr())
+        return send4, slot, counts
+
+    def unroute(self, back4, slot):
+        out = torch.empty_like(back4)
+        self.loc.pm_slab_unroute(back4.data_ptr(), slot.data_ptr(), slot.shape[0], out.data_ptr())
+        return out
+
+    def new_slab(self, P, f):
+        N = self.nmesh
+        return self._buf("slab%d" % f, (N // P + 1, N, N), torch.float64)
+
+    def _buf(self, name, shape, dtype):
+        t = self._slabs.get(name)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            self._slabs[name] = t
+        return t
+
+    def slab_paint(self, part4, rank, P):
+        N = self.nmesh
+        slab = self._buf("slab0", (N // P + 1, N, N), torch.float64)
+        self.loc.pm_slab_paint(part4.data_ptr(), part4.shape[0], rank, P, slab.data_ptr())
+        return slab
+
+    def fft_fwd(self, slab, P):
+        N = self.nmesh
+        nxl, nzh = N // P, N // 2 + 1
+        work = self._buf("work", (nxl, N, nzh), torch.complex128)
+        packed = self._buf("packed", (P, nxl, N // P, nzh), torch.complex128)
+        self.loc.pm_slab_fft_fwd(slab.data_ptr(), P, work.data_ptr(), packed.data_ptr())
+        return packed
+
+    def fft_x(self, data, P, inverse):
+        assert data.is_contiguous()
+        self.loc.pm_slab_fft_x(data.data_ptr(), P, inverse)
+
+    def transfer(self, rho, rank, P):
+        N = self.nmesh
+        out4 = self._buf("out4", (4, N, N // P, N // 2 + 1), torch.complex128)
+        self.loc.pm_slab_transfer(rho.data_ptr(), rank, P, out4.data_ptr())
+        return out4
+
+    def fft_inv(self, recv, P, slab):
+        N = self.nmesh
+        work = self._buf("work", (N // P, N, N // 2 + 1), torch.complex128)
+        self.loc.pm_slab_fft_inv(recv.data_ptr(), P, work.data_ptr(), slab.data_ptr())
+
+    def readout(self, part4, rank, P, slabs):
+        out = torch.empty_like(part4)
+        self.loc.pm_slab_readout(part4.data_ptr(), part4.shape[0], rank, P, [s.data_ptr() for s in slabs], out.data_ptr())
+        return out

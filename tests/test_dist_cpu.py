@@ -1,0 +1,106 @@
+"""world_size-2 gloo tests of the multi-GPU host logic (shenqi_b200/dist.py) on CPU: the exchanges are the product's,
+the local compute is the oracle (tests/dist_backend.py).  The distributed result must equal the single-rank oracle."""
+import os
+import socket
+import sys
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _problem():
+    from helpers import random_clustered, default_params, o_keys, o_sort
+    box, n, nmesh = 8.0, 6000, 16
+    pos = random_clustered(n, box, 11); mass = (1.0 + 0.1 * np.arange(n) % 3).astype(np.float32)
+    par = default_params(box, nmesh, n, TreeUseBH=1, TreeRcut=6.0, update_potential=1)
+    keys = o_keys(pos, box); order = o_sort(keys)
+    return box, n, nmesh, pos, mass, par, order
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from helpers import o_tree, o_walk, o_pm_force
+        from dist_backend import OracleBackend
+        from shenqi_b200.dist import DistGravity, Comm
+        box, n, nmesh, pos, mass, par, order = _problem()
+        # domain decomposition stand-in: consecutive key ranges, unequal sizes, arbitrary order inside a rank
+        cut = [0, int(0.45 * n), n] if world == 2 else np.linspace(0, n, world + 1).astype(int)
+        mine = order[cut[rank]:cut[rank + 1]].copy()
+        np.random.default_rng(rank).shuffle(mine)
+        lp, lm = torch.from_numpy(np.ascontiguousarray(pos[mine])), torch.from_numpy(np.ascontiguousarray(mass[mine]))
+        D = DistGravity(OracleBackend(par), Comm())
+        acc, pot, tot = D.tree_force(lp, lm)
+        out4 = D.pm_force(lp, lm)
+        # single-rank oracle on the whole set
+        spos = np.ascontiguousarray(pos[order]); smass = np.ascontiguousarray(mass[order])
+        nodes, first = o_tree(spos, smass, box)
+        oacc, opot, _, otot = o_walk(nodes, first, spos, smass, np.zeros(n), par, want_pot=True)
+        inv = np.empty(n, np.int64); inv[order] = np.arange(n)
+        ppot, pacc = o_pm_force(pos, mass, box, nmesh, par["Asmth"], par["G"])
+        tots = [None] * world
+        dist.all_gather_object(tots, tot)
+        res = {
+            "tree_acc": float(np.abs(acc.numpy() - oacc[inv[mine]]).max()),
+            "tree_pot": float(np.abs(pot.numpy() - opot[inv[mine]]).max()),
+            "count_ok": sum(tots) == otot,
+            "pm_pot": float(np.abs(out4.numpy()[:, 0] - ppot[mine]).max() / np.abs(ppot).max()),
+            "pm_acc": float(np.abs(out4.numpy()[:, 1:] - pacc[mine]).max() / np.abs(pacc).max()),
+            "bytes": D.comm.bytes_sent,
+        }
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2])
+def test_dist_step_equals_single_rank(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = {}
+    for _ in range(world):
+        r, res = q.get(timeout=600)
+        out[r] = res
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    for r in range(world):
+        res = out[r]
+        assert res["count_ok"]
+        assert res["tree_acc"] == 0.0 and res["tree_pot"] == 0.0, res      # same tree, same walk: bit-identical
+        assert res["pm_pot"] < 1e-12 and res["pm_acc"] < 1e-12, res
+        assert res["bytes"] > 0
+
+
+def test_wrong_domain_order_is_refused():
+    """ranks must own consecutive key ranges: a single process with world 1 passes anything, so check the rule directly"""
+    from shenqi_b200.dist import DistGravity
+
+    class FakeComm:
+        rank, world, bytes_sent = 0, 2, 0
+        def allgather_ints(self, vals, device):
+            return [[5, 100, 200, 0], [5, 150, 300, 0]]       # rank 1 starts below rank 0's last key
+
+    class FakeBackend:
+        device = torch.device("cpu")
+        def sort_local(self, pos, mass):
+            return {"keys": torch.tensor([100, 200]), "pos": pos, "mass": mass, "perm": torch.arange(2), "geo": 0}
+
+    D = DistGravity(FakeBackend(), FakeComm())
+    with pytest.raises(ValueError):
+        D.tree_force(torch.zeros(2, 3, dtype=torch.float64), torch.ones(2))
