@@ -23,7 +23,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 import numpy as np
 
-FLOP_PER_INTERACTION = 23     # force only; 28 with potential
+# 23 flop per interaction, 28 when the potential is accumulated as well.  The step benchmarked is a
+# PM step on a full-particle tree, where the reference also updates the potential (gravshort-tree2.cpp:148).
+FLOP_PER_INTERACTION = 28
+DIST_NGRID = {2: 320, 4: 400, 8: 512}   # ~256^3 particles per GPU (weak scaling), Nmesh = 2 Ngrid divisible by the ranks
 
 
 def read_peaks():
@@ -167,6 +170,146 @@ def run_reference_arm(args):
     print(json.dumps(line))
 
 
+# ---------------------------------------------------------------------------------------------- multi-GPU
+def run_dist(args, rank, local_rank, world):
+    """N > 1: ONE domain-decomposed problem (not replicas): ~256^3 particles per GPU of a global Zel'dovich box, every
+    rank owning a consecutive range of the global Peano-Hilbert order (what the reference's domain decomposition hands
+    the path).  Step = shenqi_b200.dist.DistGravity: local sort, all-gather of the sorted ranges, global tree, walk of
+    the rank's own targets; PM on x-slabs with all-to-all routing/transposes.  NCCL over NVLink."""
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev)
+    import shenqi_b200 as sq
+    from shenqi_b200.ics import zeldovich_torch, rho0, G_INTERNAL
+    from shenqi_b200.dist import DistGravity, CudaBackend, Comm
+
+    ngrid = args.ngrid if args.ngrid != 256 else DIST_NGRID.get(world, int(round(256 * world ** (1 / 3.) / 8)) * 8)
+    nmesh = args.nmesh or 2 * ngrid
+    W = max(args.warmup, 3)
+    box = 1000.0 * ngrid
+    P = sq.Params.defaults(box, nmesh, (box / ngrid) / 30., G=G_INTERNAL, rho0=rho0(), TreeRcut=6.0, TreeUseBH=1)
+    B = CudaBackend(P, local_rank)
+    B.glob.set_group_width(args.group_width)
+    D = DistGravity(B, Comm())
+    fp32_peak = B.glob.measure_fp32_peak()
+    hbm_peak, peak_src = read_peaks()
+
+    # ---- set-up (untimed): global ICs on every GPU, domain = equal-count range of the global PH order, shuffled
+    pos_all, mass_all = zeldovich_torch(ngrid, box, dev)
+    ntot = pos_all.shape[0]
+    srt = B.sort_local(pos_all, mass_all)
+    lo, hi = rank * ntot // world, (rank + 1) * ntot // world
+    g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
+    mine = srt["perm"][lo:hi][torch.randperm(hi - lo, device=dev, generator=g)]
+    pos = pos_all[mine].contiguous(); mass = mass_all[mine].contiguous()
+    del pos_all, mass_all, srt, mine
+    n = pos.shape[0]
+    torch.cuda.empty_cache()
+
+    # bootstrap |a_old| with a Barnes-Hut pass + PM, as the reference starts (gravshort-tree2.cpp:170-171)
+    a0, _, _ = D.tree_force(pos, mass)
+    o4 = D.pm_force(pos, mass)
+    oldacc = ((a0 + o4[:, 1:4]).norm(dim=1) / G_INTERNAL).contiguous()
+    del a0, o4
+    P.TreeUseBH = 0
+    B.set_params(P)
+
+    def step():
+        a, p, st = D.tree_force(pos, mass, oldacc)
+        o = D.pm_force(pos, mass)
+        return a, p, o, st
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    for _ in range(W):
+        step()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    B.loc.reset_timings(); B.glob.reset_timings()
+    D.comm.bytes_sent = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    walk_ms, inter, entries, tb_ms = [], [], [], []
+    for _ in range(args.steps):
+        _, _, _, st = step()
+        walk_ms.append(st.kernel_ms); inter.append(st.interactions); entries.append(st.list_entries)
+        tg = B.glob.timings()
+        tb_ms.append(tg.tree_build_ms + tg.tree_moments_ms)
+    e1.record()
+    barrier()
+    dt = allmax(e0.elapsed_time(e1) * 1e-3)
+    launches = B.loc.timings().kernel_launches + B.glob.timings().kernel_launches
+    clocks = sampler.stop()
+    sent = D.comm.bytes_sent / args.steps
+    ms_per_step = 1e3 * dt / args.steps
+    total_inter = allsum(float(np.mean(inter)))
+    wms_max = allmax(float(np.mean(walk_ms)))
+    wms_mine = float(np.mean(walk_ms))
+    achieved_tf = float(np.mean(inter)) * FLOP_PER_INTERACTION / (wms_mine * 1e-3) / 1e12     # rank 0's kernel against its own SMs
+    numnodes = int(D.tree_info.numnodes)
+
+    # end to end: host buffers in, host buffers out, copies inside the timed region
+    hpos, hmass, hold = pos.cpu().pin_memory(), mass.cpu().pin_memory(), oldacc.cpu().pin_memory()
+    hacc = torch.empty((n, 3), dtype=torch.float64).pin_memory(); hpot = torch.empty(n, dtype=torch.float64).pin_memory()
+    hpm = torch.empty((n, 4), dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        dp, dm, do = hpos.to(dev, non_blocking=True), hmass.to(dev, non_blocking=True), hold.to(dev, non_blocking=True)
+        a, p, st = D.tree_force(dp, dm, do)
+        o = D.pm_force(dp, dm)
+        hacc.copy_(a, non_blocking=True); hpot.copy_(p, non_blocking=True); hpm.copy_(o, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    de = allmax(time.perf_counter() - t0)
+    ntot_all = int(allsum(float(n)))
+
+    line = {"metric": "short-range gravity particles/s", "value": ntot_all / (dt / args.steps), "unit": "particles/s", "n_gpus": world,
+            "steps": args.steps, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 pair math, f64 accumulation/tests", "data": "synthetic",
+            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9 domain-decomposed over %d GPUs (%.3f x 256^3 particles per GPU)" % (ngrid, nmesh, world, n / 256. ** 3),
+                       "particles": ntot_all, "particles_per_gpu": n, "Nmesh": nmesh, "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5,
+                       "group_width": args.group_width, "parallelism": "PH-range domains, replicated global tree, x-slab PM",
+                       "l2": "inputs_exceed_l2 (particle arrays %.0f MB per GPU)" % (ntot_all * 36 / 1e6)},
+            "interactions_per_s": total_inter / (wms_max * 1e-3), "interactions_per_particle": total_inter / ntot_all,
+            "walk_particles_per_s": ntot_all / (wms_max * 1e-3),
+            "stage_ms": {"walk_ms_max_over_ranks": wms_max, "walk_ms_rank0": wms_mine, "global_tree_build_ms_rank0": float(np.mean(tb_ms)),
+                         "other_ms (local sort, exchanges, PM)": ms_per_step - wms_max - float(np.mean(tb_ms))},
+            "exchange_bytes_sent_per_step_rank0": int(sent), "tree_nodes": numnodes,
+            "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None, "flop_per_interaction": FLOP_PER_INTERACTION,
+                         "peak_source": "FFMA microbenchmark in this run (sq_measure_fp32_peak), rank 0",
+                         "lane_efficiency": float(np.mean(inter)) / float(max(1, np.mean(entries) * 32))},
+            "e2e": {"value": ntot_all / (de / e2e_steps), "unit": "particles/s", "h2d_bytes_per_step": int(n * (24 + 4 + 8)) * world,
+                    "d2h_bytes_per_step": int(n * (24 + 8 + 32)) * world, "ms_per_step": 1e3 * de / e2e_steps},
+            "gpu_launches": int(launches), "clocks": clocks}
+    if rank == 0:
+        print(json.dumps(line))
+    B.close()
+    dist.destroy_process_group()
+
+
 # ---------------------------------------------------------------------------------------------- GPU side
 def main():
     ap = argparse.ArgumentParser()
@@ -187,6 +330,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        return run_dist(args, rank, local_rank, world)
     import torch
     dist = None
     if world > 1:
@@ -302,7 +447,7 @@ def main():
     line = {"metric": "short-range gravity particles/s", "value": value, "unit": "particles/s", "n_gpus": world, "steps": args.steps,
             "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 pair math, f64 accumulation/tests", "data": "synthetic",
-            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9%s" % (args.ngrid, nmesh, "" if world == 1 else " x %d independent replicas (domain-decomposed exchange not built yet)" % world),
+            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9" % (args.ngrid, nmesh),
                        "particles": n, "Nmesh": nmesh, "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5, "group_width": args.group_width,
                        "l2": "inputs_exceed_l2 (particle arrays %.0f MB, mesh %.0f MB)" % (n * 36 / 1e6, nm3 * 8 / 1e6)},
             "interactions_per_s": world * interactions / (wms * 1e-3), "interactions_per_particle": interactions / n,

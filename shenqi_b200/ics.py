@@ -44,5 +44,40 @@ def zeldovich(ngrid, box, rms_disp=0.2, seed=181170, index=-1.0):
     return pos, mass, ids
 
 
+def zeldovich_torch(ngrid, box, device, rms_disp=0.2, seed=181170, index=-1.0):
+    """The same construction on a CUDA device with torch (input generation for the multi-GPU benchmark, where
+    512^3 particles per rank in numpy would take minutes; torch's generator, so not the same realisation as
+    zeldovich()).  Returns pos[N,3] float64 and mass[N] float32 device tensors."""
+    import torch
+    n = ngrid
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    dk = torch.fft.rfftn(torch.randn((n, n, n), dtype=torch.float64, device=device, generator=g))
+    kx = torch.fft.fftfreq(n, 1.0 / n, dtype=torch.float64, device=device)[:, None, None]
+    ky = torch.fft.fftfreq(n, 1.0 / n, dtype=torch.float64, device=device)[None, :, None]
+    kz = torch.fft.rfftfreq(n, 1.0 / n, dtype=torch.float64, device=device)[None, None, :]
+    k2 = kx * kx + ky * ky + kz * kz
+    k2[0, 0, 0] = 1.0
+    amp = k2 ** (index / 4.0) * torch.exp(-k2 / (0.25 * n) ** 2)
+    amp[0, 0, 0] = 0.0
+    dk *= amp
+    del amp
+    pos = torch.empty((n ** 3, 3), dtype=torch.float64, device=device)
+    for a, kk in enumerate((kx, ky, kz)):
+        pos[:, a] = torch.fft.irfftn(1j * kk / k2 * dk, s=(n, n, n)).reshape(-1)
+    del dk, k2
+    pos *= rms_disp * (box / n) / torch.sqrt((pos ** 2).sum(1).mean() / 3.0)
+    idx = torch.arange(n ** 3, device=device)
+    pos[:, 0] += (idx // (n * n)).to(torch.float64) * (box / n)
+    pos[:, 1] += ((idx // n) % n).to(torch.float64) * (box / n)
+    pos[:, 2] += (idx % n).to(torch.float64) * (box / n)
+    del idx
+    pos.remainder_(box)
+    pos[pos >= box] = 0.0
+    rho_crit = 3 * HUBBLE ** 2 / (8 * np.pi * G_INTERNAL)
+    mass = torch.full((n ** 3,), OMEGA0 * rho_crit * box ** 3 / n ** 3, dtype=torch.float32, device=device)
+    return pos, mass
+
+
 def rho0():
     return OMEGA0 * 3 * HUBBLE ** 2 / (8 * np.pi * G_INTERNAL)
