@@ -180,6 +180,7 @@ def run_dist(args, rank, local_rank, world):
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p")     # keep stdout to the one JSON line
     dist.init_process_group("nccl", device_id=dev)
     import shenqi_b200 as sq
     from shenqi_b200.ics import zeldovich_torch, rho0, G_INTERNAL
@@ -192,7 +193,7 @@ def run_dist(args, rank, local_rank, world):
     P = sq.Params.defaults(box, nmesh, (box / ngrid) / 30., G=G_INTERNAL, rho0=rho0(), TreeRcut=6.0, TreeUseBH=1)
     B = CudaBackend(P, local_rank)
     B.glob.set_group_width(args.group_width)
-    D = DistGravity(B, Comm())
+    D = DistGravity(B, Comm(), profile=True)
     fp32_peak = B.glob.measure_fp32_peak()
     hbm_peak, peak_src = read_peaks()
 
@@ -218,7 +219,7 @@ def run_dist(args, rank, local_rank, world):
 
     def step():
         a, p, st = D.tree_force(pos, mass, oldacc)
-        o = D.pm_force(pos, mass)
+        o = D.pm_force(pos, mass, reuse_sorted=True)
         return a, p, o, st
 
     def barrier():
@@ -237,6 +238,11 @@ def run_dist(args, rank, local_rank, world):
 
     for _ in range(W):
         step()
+    # one extra untimed step with CUDA-event marks between the phases (the marks are off in the timed region)
+    D.stage_ms()
+    step()
+    phases = {k: round(v, 3) for k, v in D.stage_ms().items()}
+    D.profile = False
     sampler = ClockSampler(local_rank)
     sampler.start()
     B.loc.reset_timings(); B.glob.reset_timings()
@@ -271,7 +277,7 @@ def run_dist(args, rank, local_rank, world):
     def e2e_step():
         dp, dm, do = hpos.to(dev, non_blocking=True), hmass.to(dev, non_blocking=True), hold.to(dev, non_blocking=True)
         a, p, st = D.tree_force(dp, dm, do)
-        o = D.pm_force(dp, dm)
+        o = D.pm_force(dp, dm, reuse_sorted=True)
         hacc.copy_(a, non_blocking=True); hpot.copy_(p, non_blocking=True); hpm.copy_(o, non_blocking=True)
         torch.cuda.synchronize()
 
@@ -295,7 +301,8 @@ def run_dist(args, rank, local_rank, world):
             "interactions_per_s": total_inter / (wms_max * 1e-3), "interactions_per_particle": total_inter / ntot_all,
             "walk_particles_per_s": ntot_all / (wms_max * 1e-3),
             "stage_ms": {"walk_ms_max_over_ranks": wms_max, "walk_ms_rank0": wms_mine, "global_tree_build_ms_rank0": float(np.mean(tb_ms)),
-                         "other_ms (local sort, exchanges, PM)": ms_per_step - wms_max - float(np.mean(tb_ms))},
+                         "other_ms (local sort, exchanges, PM)": ms_per_step - wms_max - float(np.mean(tb_ms)),
+                         "phases_rank0_ms (one untimed step, CUDA events)": phases},
             "exchange_bytes_sent_per_step_rank0": int(sent), "tree_nodes": numnodes,
             "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None, "flop_per_interaction": FLOP_PER_INTERACTION,

@@ -124,10 +124,29 @@ class Comm:
 class DistGravity:
     """One rank of the distributed force step.  `backend` does the local compute (CudaBackend or the tests' CPU one)."""
 
-    def __init__(self, backend, comm=None):
+    def __init__(self, backend, comm=None, profile=False):
         self.B = backend
         self.comm = comm or Comm()
         self.rank, self.world = self.comm.rank, self.comm.world
+        self.profile = profile and torch.cuda.is_available()
+        self._marks = []
+
+    # ---- optional stage timing (CUDA events on the current stream; read with stage_ms())
+    def _mark(self, name):
+        if self.profile:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self._marks.append((name, e))
+
+    def stage_ms(self):
+        """milliseconds between consecutive marks since the last call, summed by name"""
+        torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self._marks[:-1], self._marks[1:]):
+            if n1 != "begin":
+                out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        self._marks = []
+        return out
 
     # ------------------------------------------------------------------ short-range tree force
     def tree_force(self, pos, mass, oldacc=None):
@@ -136,7 +155,9 @@ class DistGravity:
         Returns (accel [n,3] already x G, potential [n] or None, stats) in the caller's particle order."""
         B, C = self.B, self.comm
         n = pos.shape[0]
+        self._mark("begin")
         srt = B.sort_local(pos, mass)
+        self._mark("tree:local_sort")
         kmin = int(srt["keys"][0].item()) if n else 2 ** 63 - 1
         kmax = int(srt["keys"][-1].item()) if n else -1
         info = C.allgather_ints([n, kmin, kmax, int(srt["geo"])], B.device)
@@ -147,55 +168,87 @@ class DistGravity:
                 raise ValueError("ranks must own consecutive Peano-Hilbert key ranges in rank order (domain decomposition)")
             if r[0]:
                 last = r[2]
+        self._mark("tree:counts_sync")
         gk = C.allgather_rows(srt["keys"], counts)
         gp = C.allgather_rows(srt["pos"], counts)
         gm = C.allgather_rows(srt["mass"], counts)
+        self._mark("tree:allgather")
         B.install_global(gk, gp, gm, max(r[3] for r in info))
         self.tree_info = B.tree_build()
+        self._mark("tree:global_build")
         first = sum(counts[: self.rank])
         perm = srt["perm"]
+        self._sorted = srt          # PH-sorted copies of this rank's particles: pm_force(reuse_sorted=True) paints from them
         if oldacc is not None:
             B.set_oldacc_range(first, oldacc[perm].contiguous())
         acc_s, pot_s, st = B.walk_range(first, n)
+        self._mark("tree:walk")
         accel = torch.empty_like(acc_s)
         accel[perm] = acc_s
         pot = None
         if pot_s is not None:
             pot = torch.empty_like(pot_s)
             pot[perm] = pot_s
+        self._mark("tree:unpermute")
         return accel, pot, st
 
     # ------------------------------------------------------------------ particle-mesh force
-    def pm_force(self, pos, mass):
-        """Returns out4 [n,4] = (PM potential, fx, fy, fz) for this rank's particles, in their order."""
+    def pm_force(self, pos, mass, reuse_sorted=False):
+        """Returns out4 [n,4] = (PM potential, fx, fy, fz) for this rank's particles, in their order.
+        reuse_sorted: pos/mass are the arrays the last tree_force() was called with; the PH-sorted copies it left are
+        routed instead (PH-adjacent particles share mesh cells, so paint and readout stay cache-coherent, as on the
+        single-GPU path and as after the reference's slots_gc_sorted) and the result is put back in the caller's order."""
         B, C = self.B, self.comm
+        perm = None
+        if reuse_sorted and getattr(self, "_sorted", None) is not None and self._sorted["pos"].shape[0] == pos.shape[0]:
+            pos, mass, perm = self._sorted["pos"], self._sorted["mass"], self._sorted["perm"]
         P, r = self.world, self.rank
         N = B.nmesh
         if N % P or N % 2:
             raise ValueError("Nmesh %d must be even and divisible by the number of ranks %d" % (N, P))
         nxl, nyl, nzh = N // P, N // P, N // 2 + 1
+        self._mark("begin")
         send4, slot, counts = B.route(pos, mass, P)
         rc = C.allgather_ints(list(counts), B.device)
         recv_counts = [rc[q][r] for q in range(P)]
+        self._mark("pm:route")
         part4 = C.alltoall_rows(send4, counts, recv_counts)
+        self._mark("pm:particles_a2a")
         slab = B.slab_paint(part4, r, P)                       # [(nxl + 1), N, N]; last plane = ghost
         slab[0] += C.shift(slab[nxl], +1)                      # my ghost belongs to the next rank's first plane
+        self._mark("pm:paint+ghost")
         packed = B.fft_fwd(slab, P)                            # [P, nxl, nyl, nzh] complex
+        self._mark("pm:fft")
         rho = C.alltoall_equal(packed).view(N, nyl, nzh)       # block p holds planes p*nxl ..: x is the slowest index
+        self._mark("pm:transpose_a2a")
         B.fft_x(rho, P, False)
+        self._mark("pm:fft")
         out4 = B.transfer(rho, r, P)                           # [4, N, nyl, nzh]: phi_k, Fx_k, Fy_k, Fz_k
+        self._mark("pm:transfer")
         slabs = []
         for f in range(4):
             B.fft_x(out4[f], P, True)
+            self._mark("pm:fft")
             recv = C.alltoall_equal(out4[f].view(P, nxl, nyl, nzh))
+            self._mark("pm:transpose_a2a")
             s = slab if f == 0 else B.new_slab(P, f)
             B.fft_inv(recv, P, s)
             slabs.append(s)
+            self._mark("pm:fft")
         for s in slabs:                                        # ghost plane = the next rank's first plane
             s[nxl] = C.shift(s[0], -1)
+        self._mark("pm:paint+ghost")
         res = B.readout(part4, r, P, slabs)
+        self._mark("pm:readout")
         back = C.alltoall_rows(res, recv_counts, counts)
-        return B.unroute(back, slot)
+        self._mark("pm:particles_a2a")
+        out = B.unroute(back, slot)
+        if perm is not None:
+            res = torch.empty_like(out)
+            res[perm] = out
+            out = res
+        self._mark("pm:route")
+        return out
 
 
 class CudaBackend:

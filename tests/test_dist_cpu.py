@@ -51,6 +51,9 @@ def _worker(rank, world, port, q):
         ppot, pacc = o_pm_force(pos, mass, box, nmesh, par["Asmth"], par["G"])
         tots = [None] * world
         dist.all_gather_object(tots, tot)
+        # the PM step from the PH-sorted copies tree_force left: same particles, other routing order
+        out4s = D.pm_force(lp, lm, reuse_sorted=True).numpy()
+        assert np.abs(out4s - out4.numpy()).max() <= 1e-12 * np.abs(out4.numpy()).max()
         res = {
             "tree_acc": float(np.abs(acc.numpy() - oacc[inv[mine]]).max()),
             "tree_pot": float(np.abs(pot.numpy() - opot[inv[mine]]).max()),
