@@ -15,6 +15,9 @@
 //     quantised once per walk by sq_walk_prep_*; a group-relative coordinate is one integer subtraction (which
 //     is also the periodic NEAREST()), one I2F and one multiply - no FP64 on the walk's hot path.  Node records
 //     are two 128-bit loads + the link record; a source particle is one 128-bit load.
+//   * The stack holds OPENED internal nodes (first child, child count, mask of the targets that opened it).  Per step the
+//     warp pops as many entries as have <= 32 children in total and tests one child per lane, so the tests run at
+//     close to full lane occupancy.
 //   * Every (target, node) decision is the reference's own (discard: the Rcut + len/2 box; open: relative
 //     criterion M l^2 > r^4 alpha |a_old|, Barnes-Hut angle, inside-0.6-len box), reached in tiers so that FP64 is
 //     the exception:
@@ -63,6 +66,9 @@ struct sq_walk_par {
     // FP32 tiers (table units)
     float qs;                     // table units per fixed-point unit
     float f_rcut, f_rc2_lo, f_rc2_hi, f_invbh2, f_h2, f_hs, f_boxs, f_invboxs, f_halfs, f_range;
+    // exact keep test per tree level: |centre - x| <= e_in certainly inside the keep box, > e_out certainly outside
+    // (fixed-point quanta); e_in < 0: -1 = every target is inside (Rcut + len/2 >= Box/2), -2 = use the FP32/FP64 tiers
+    int e_in[SQ_MAXLEVEL + 3], e_out[SQ_MAXLEVEL + 3];
 };
 
 struct sq_walk_warp_smem {
@@ -75,9 +81,14 @@ struct sq_walk_warp_smem {
     unsigned mw[LIST_CAP + LIST_PAD];  // mask words, one per evaluation step: bit (s*G + t) = entry of slice s reaches target t
     unsigned nm[NEAR_CAP];
     float4 nrec[32][3];                // tier 2 work list: (cm.xyz, dr2) (centre.xyz, de) (len, M l^2, need mask, -)
-    int s_end[32], s_first[32];
+    int s_end[32], s_first[32];        // pop: children of the popped entries; later in the step: particles of opened leaves
     unsigned s_mask[32];
+    int sx[3][32];                     // target coordinates per axis, sorted (fixed point, relative to the first target)
+    unsigned pmk[3][36];               // pmk[a][k] = targets among the k smallest coordinates of axis a
+    unsigned char scnt[STACK_CAP];     // child count of stack entry i
 };
+
+static_assert(TAB_BYTES + WALK_WARPS * sizeof(sq_walk_warp_smem) <= 232448, "walk kernel shared memory exceeds the 227 KB of an sm_100 CTA");
 
 // FP64 position -> 32-bit fixed point, periodic (two's complement wrap = the box)
 __host__ __device__ __forceinline__ unsigned sq_quant(double x, double qinv)
@@ -143,6 +154,39 @@ __device__ __noinline__ int sq_exact_class(const double4 M, const double4 C, dou
     return 1;
 }
 
+
+__device__ __forceinline__ int sq_add_sat(int a, int b)
+{
+    int r;
+    asm("add.sat.s32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ int sq_sub_sat(int a, int b)
+{
+    int r;
+    asm("sub.sat.s32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+// number of the 32 sorted values that are <= v
+__device__ __forceinline__ int sq_count_le(const int * s, int v)
+{
+    int pos = 0;
+    #pragma unroll
+    for(int step = 16; step >= 1; step >>= 1)
+        if(s[pos + step - 1] <= v) pos += step;
+    if(s[pos] <= v) pos++;
+    return pos;
+}
+// targets with |c - x_t| <= e_in on this axis; amb is set when some target sits within (e_in, e_out] of c
+__device__ __forceinline__ unsigned sq_axis_keep(const int * s, const unsigned * pm, int c, int e_in, int e_out, bool & amb)
+{
+    const int hi = sq_add_sat(c, e_in), lo = sq_sub_sat(c, e_in);
+    const int p = sq_count_le(s, hi);                              // values <= c + e_in
+    const int q = lo == (int) 0x80000000 ? 0 : sq_count_le(s, lo - 1);   // values < c - e_in
+    if(p < 32 && s[p] != 0x7fffffff && s[p] <= sq_add_sat(c, e_out)) amb = true;
+    if(q > 0 && s[q - 1] >= sq_sub_sat(c, e_out)) amb = true;
+    return pm[p] & ~pm[q];
+}
 
 template <int S>
 __device__ __forceinline__ int sq_list_slot(int p)
@@ -358,7 +402,41 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         float ax = 0.f, ay = 0.f, az = 0.f, ap = 0.f;
         double dax = 0.0, day = 0.0, daz = 0.0, dap = 0.0;
         int top = 1, nlist = 0, nn = 0;
-        if(lane == 0) W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
+        // ---- exact keep test: sort the targets' coordinates on every axis, prefix masks over the sorted order
+        // (a group wider than a quarter of the box keeps the FP32 / FP64 tiers only)
+        const bool intkeep = max(exx, max(exy, exz)) < 0x40000000u;
+        if(intkeep) {
+            unsigned * oh = reinterpret_cast<unsigned *>(W.nrec);
+            #pragma unroll
+            for(int a = 0; a < 3; a++) {
+                const int v = valid ? (a == 0 ? rx : (a == 1 ? ry : rz)) : 0x7fffffff;
+                int rk = 0;
+                #pragma unroll 8
+                for(int u = 0; u < 32; u++) {
+                    const int vu = __shfl_sync(SQ_FULL, v, u);
+                    rk += (vu < v || (vu == v && u < (int) lane)) ? 1 : 0;
+                }
+                W.sx[a][rk] = v;
+                oh[a * 32 + rk] = valid ? lanebit : 0u;
+            }
+            __syncwarp();
+            #pragma unroll
+            for(int a = 0; a < 3; a++) {
+                unsigned m = oh[a * 32 + lane];
+                #pragma unroll
+                for(int o = 1; o < 32; o <<= 1) {
+                    const unsigned y = __shfl_up_sync(SQ_FULL, m, o);
+                    if((int) lane >= o) m |= y;
+                }
+                W.pmk[a][lane + 1] = m;
+                if(lane == 0) W.pmk[a][0] = 0u;
+            }
+        }
+        if(lane == 0) {
+            // the root is "the only child" of a virtual entry reached by every target
+            W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
+            W.scnt[0] = 1;
+        }
         __syncwarp();
 
         for(;;) {
@@ -371,17 +449,32 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             unsigned t2_need = 0, risky_exact = 0;
             float4 t2_cm = nodeE, t2_cl = nodeE, t2_lm = nodeE;
             if(!drain) {
-                // wide pops only while a depth-first descent (<= 7 entries per level) still fits above them
-                int k = (STACK_CAP - STACK_RESERVE - top) / 7;
-                k = k < 1 ? 1 : k;
-                k = k > 32 ? 32 : k;
-                k = k > top ? top : k;
-                top -= k;
-                const bool have = (int) lane < k;
+                // pop the entries whose children fit the 32 lanes (always at least one: <= 8 children); every child can
+                // push one entry, so wide pops only while a depth-first descent (<= 7 entries per level) still fits
+                const int cnt = (int) lane < top ? (int) W.scnt[top - 1 - lane] : 64;
+                int tot_all;
+                const int exc = sq_warp_excl_scan(cnt, tot_all);
+                int npop = __popc(__ballot_sync(SQ_FULL, exc + cnt <= 32));
+                if(top - npop + 32 > STACK_CAP - STACK_RESERVE) npop = 1;
+                const int nchild = __shfl_sync(SQ_FULL, exc + cnt, npop - 1);
+                if((int) lane < npop) {
+                    const int2 e = W.stack[top - 1 - lane];
+                    W.s_end[lane] = exc + cnt;
+                    W.s_first[lane] = e.x - exc;
+                    W.s_mask[lane] = (unsigned) e.y;
+                }
+                top -= npop;
+                __syncwarp();
+                const bool have = (int) lane < nchild;
                 unsigned mask = 0;
                 if(have) {
-                    const int2 e = W.stack[top + lane];
-                    node = e.x; mask = (unsigned) e.y;
+                    int lo = 0, hi = npop - 1;
+                    while(lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if(W.s_end[mid] > (int) lane) hi = mid; else lo = mid + 1;
+                    }
+                    node = W.s_first[lo] + (int) lane;
+                    mask = W.s_mask[lo];
                 }
                 __syncwarp();
                 if(have) {
@@ -414,24 +507,45 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                     unsigned need = 0;
                     if(risky) risky_exact = mask;
                     else {
-                        // ---- tier 1: the whole group at once (bounding box, min/max |a_old|).  With the centre of
-                        // mass inside the cell "r2 <= Rcut^2" implies the box test, so the box decides keep/discard.
+                        // With the centre of mass inside the cell "r2 <= Rcut^2" implies the box test, so the box
+                        // decides keep/discard.
                         const float en = fmaxf(fmaxf(acx - ghx, acy - ghy), acz - ghz);
                         const float ef = fmaxf(fmaxf(acx + ghx, acy + ghy), acz + ghz);
                         const float hl = fmaf(0.5f * (1.f + 1e-5f), len, de);
                         const bool cmin = fabsf(cmx - cx) <= hl && fabsf(cmy - cy) <= hl && fabsf(cmz - cz) <= hl;
+                        const int lvl = SQ_INFO_LEVEL(L.w);
+                        const int e_in = P.e_in[lvl], e_out = P.e_out[lvl];
                         if(!cmin) need = mask;
                         else if(en > efA) { }                       // outside every target's box: discarded
                         else {
-                            const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
-                            const float wx = amx + ghx, wy = amy + ghy, wz = amz + ghz;
-                            const float r2n = fmaf(qz, qz, fmaf(qy, qy, qx * qx)), r2f = fmaf(wz, wz, fmaf(wy, wy, wx * wx));
-                            const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
-                            const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
-                            const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
-                            if(!(ef > efB) && go_lo == go_hi) {     // inside every target's box, same opening for all
-                                if(go_hi) open_mask = mask; else acc_mask = mask;
-                            } else need = mask;
+                            // ---- tier 0: the targets that keep the node, exact
+                            unsigned keep = mask;
+                            bool known = !(ef > efB);               // inside every target's box
+                            if(!known && intkeep && e_in != -2) {
+                                known = true;
+                                if(e_in >= 0) {
+                                    bool amb = false;
+                                    keep &= sq_axis_keep(W.sx[0], W.pmk[0], (int) (B.x - ix0), e_in, e_out, amb);
+                                    keep &= sq_axis_keep(W.sx[1], W.pmk[1], (int) (B.y - iy0), e_in, e_out, amb);
+                                    keep &= sq_axis_keep(W.sx[2], W.pmk[2], (int) (B.z - iz0), e_in, e_out, amb);
+                                    if(amb) { risky_exact = mask; keep = 0u; }
+                                }
+                            }
+                            if(!known) need = mask;
+                            else if(keep == 0u) { }
+                            else if(SQ_INFO_TYPE(L.w) == 0 && L.y == 1) acc_mask = keep;   // one particle: monopole = the particle
+                            else {
+                                // ---- tier 1: one opening decision for all kept targets (group box clipped to the keep box)
+                                const float qx = fmaxf(amx - ghx, 0.f), qy = fmaxf(amy - ghy, 0.f), qz = fmaxf(amz - ghz, 0.f);
+                                const float wx = fminf(amx + ghx, fabsf(cmx - cx) + efA), wy = fminf(amy + ghy, fabsf(cmy - cy) + efA), wz = fminf(amz + ghz, fabsf(cmz - cz) + efA);
+                                const float r2n = fmaf(qz, qz, fmaf(qy, qy, qx * qx)), r2f = fmaf(wz, wz, fmaf(wy, wy, wx * wx));
+                                const float r2nl = fmaxf(r2n - dr2, 0.f), r2fh = r2f + dr2;
+                                const bool go_lo = (mlA > r2nl * r2nl * ta_lo) || (r2n < bhA) || (en < inA);
+                                const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
+                                if(go_lo == go_hi) {
+                                    if(go_hi) open_mask = keep; else acc_mask = keep;
+                                } else need = keep;
+                            }
                         }
                         if(need) {
                             // ---- tier 2 runs transposed below: hand the node over
@@ -515,12 +629,14 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             const int type = SQ_INFO_TYPE(L.w);
             // ---- opened internal nodes -> push children with the open mask (pseudo nodes are skipped: gravshort2.hpp:305-314)
             {
-                const int nch = (open_mask && type == 1) ? L.y : 0;
-                int tot;
-                const int off = sq_warp_excl_scan(nch, tot);
-                for(int j = 0; j < nch; j++)
-                    W.stack[top + off + j] = make_int2(L.x + j, (int) open_mask);
-                top += tot;
+                const bool pushes = open_mask && type == 1;
+                const unsigned bp = __ballot_sync(SQ_FULL, pushes);
+                if(pushes) {
+                    const int p = top + __popc(bp & sq_lanemask_lt());
+                    W.stack[p] = make_int2(L.x, (int) open_mask);
+                    W.scnt[p] = (unsigned char) L.y;
+                }
+                top += __popc(bp);
             }
             // ---- opened leaves -> their particles are sources (gravshort2.hpp:291-303)
             int tot_leaf;
@@ -787,6 +903,14 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     P.f_invboxs = (float) (1.0 / (P.box * P.s));
     P.f_halfs = (float) (P.half * P.s);
     P.f_range = (float) (SQ_NTAB - 1);
+    // keep box per level in fixed-point quanta: eff = Rcut + len/2 (gravshort2.hpp:160), len = 1.001 Box / 2^level
+    for(int L = 0; L < SQ_MAXLEVEL + 3; L++) {
+        const double len = ldexp(1.001 * par.BoxSize, -L);
+        const double effq = (P.rcut + 0.5 * len) * P.qinv;
+        if(effq >= 2147483648.0 + 8.0) { P.e_in[L] = -1; P.e_out[L] = -1; }              // >= Box/2: |NEAREST()| never exceeds it
+        else if(effq > 2147483648.0 - 8.0 || effq < 8.0) { P.e_in[L] = -2; P.e_out[L] = -2; }
+        else { P.e_in[L] = (int) floor(effq) - 2; P.e_out[L] = (int) ceil(effq) + 2; }
+    }
 
     const int64_t n = c->n;
     const uint32_t * targets = nullptr;

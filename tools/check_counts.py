@@ -10,6 +10,7 @@ import shenqi_b200 as sq
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--ngrid", type=int, default=64)
+ap.add_argument("--with-pm", action="store_true", help="|a_old| from tree + PM (as bench.py / prof_step.py) instead of the tree alone")
 a = ap.parse_args()
 pos, mass, par = bench.workload(a.ngrid, 2 * a.ngrid)
 n = len(pos); box = par["BoxSize"]
@@ -17,7 +18,8 @@ ctx = sq.Context(0)
 P = sq.Params.defaults(box, 2 * a.ngrid, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
 ctx.set_params(P); ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
 a0, _, st0 = ctx.grav_short_tree()
-P.TreeUseBH = 0; ctx.set_params(P); ctx.set_old_accel(a0, None)
+g0 = ctx.gravpm_force()[0] if a.with_pm else None
+P.TreeUseBH = 0; ctx.set_params(P); ctx.set_old_accel(a0, g0)
 a1, _, st1 = ctx.grav_short_tree()
 meansep = box / a.ngrid
 opar = H.default_params(box, 2 * a.ngrid, n, G=par["G"], TreeUseBH=1, TreeRcut=par["TreeRcut"], GravitySoftening=par["GravitySoftening"], rho0=par["rho0"])
@@ -30,9 +32,12 @@ with H.quiet_stdout():
     full = np.zeros((n, 3)); full[:] = a0[inv]
     opar["TreeUseBH"] = 0
     # counts first: the walk itself overwrites FullTreeGravAccel (the |a_old| input) on a full tree
-    H.ref().ref_set_accels(H.ptr(full), H.ptr(np.zeros((n, 3))))
+    gpm = np.zeros((n, 3))
+    if g0 is not None:
+        gpm[:] = g0[inv]
+    H.ref().ref_set_accels(H.ptr(full), H.ptr(gpm))
     _, t1 = H.r_counts(opar, meansep)
-    r1, _ = H.r_walk(opar, meansep, fulltree=full, gravpm=np.zeros((n, 3)))
+    r1, _ = H.r_walk(opar, meansep, fulltree=full, gravpm=gpm)
 e0 = H.rel_err(a0[inv], r0); e1 = H.rel_err(a1[inv], r1)
 print(json.dumps({"n": n, "bh": {"gpu": st0.interactions, "ref": int(t0), "median": float(np.median(e0)), "p999": float(np.percentile(e0, 99.9))},
                   "rel": {"gpu": st1.interactions, "ref": int(t1), "median": float(np.median(e1)), "p999": float(np.percentile(e1, 99.9)),
