@@ -102,6 +102,12 @@ __device__ __forceinline__ float2 sq_lds_f2(unsigned addr)
     asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ float4 sq_lds_f4(unsigned addr)
+{
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
 // one MUFU.RSQ (the caller keeps the argument away from 0 and denormals)
 __device__ __forceinline__ float sq_rsqrt(float x)
 {
@@ -201,8 +207,10 @@ __device__ __forceinline__ int sq_list_slot(int p)
 // Every genuine entry is farther than the softening length from every target of the group (the others are in the
 // near list), padding entries are SQ_FAR away, so r2 > 0 and no softening or wrap test is needed.
 // Table (gravity.h:50-60): i = floor(r), linear interpolation, zero from row 511 on.
-//   !POT: row i = (value at the middle of [i, i+1], slope); row 511 = (0, 0)
-//    POT: row i = (force[i], potential[i]); rows i and i+1 are read; the r < 511 test zeroes the tail
+//   !POT: row i = (force value at the middle of [i, i+1], slope), 16 copies of 8 bytes per 128-byte row
+//    POT: row i = (force middle, force slope, potential middle, potential slope), 8 copies of 16 bytes per row: a
+//         128-bit LDS is served 8 lanes at a time, each lane of a quarter warp has its own copy (conflict-free)
+//   rows 511.. = 0: the clamp of r - 1/2 to 511 lands there, which is the reference's "outside the table"
 struct sq_acc2 { float2 x, y, z, p; };
 
 template <bool POT>
@@ -221,17 +229,16 @@ __device__ __forceinline__ void sq_eval_pair(float x0, float x1, float y0, float
     const unsigned a0 = ((unsigned) __float_as_int(tt.x) << 7) + tabaddr, a1 = ((unsigned) __float_as_int(tt.y) << 7) + tabaddr;
     const float2 rinv2 = __fmul2_rn(rinv, rinv);
     if(POT) {
-        const float2 e00 = sq_lds_f2(a0), e01 = sq_lds_f2(a0 + 128), e10 = sq_lds_f2(a1), e11 = sq_lds_f2(a1 + 128);
-        const float2 fr = __fadd2_rn(d, make_float2(0.5f, 0.5f));
-        const float2 w0 = __ffma2_rn(make_float2(fr.x, fr.x), __ffma2_rn(e00, make_float2(-1.f, -1.f), e01), e00);   // (force, potential) window of entry 0
-        const float2 w1 = __ffma2_rn(make_float2(fr.y, fr.y), __ffma2_rn(e10, make_float2(-1.f, -1.f), e11), e10);
-        const float2 mm = make_float2((on0 && r2.x < 261121.f) ? m0 : 0.f, (on1 && r2.y < 261121.f) ? m1 : 0.f);
+        const float4 e0 = sq_lds_f4(a0), e1 = sq_lds_f4(a1);
+        const float2 wf = __ffma2_rn(d, make_float2(e0.y, e1.y), make_float2(e0.x, e1.x));
+        const float2 wp = __ffma2_rn(d, make_float2(e0.w, e1.w), make_float2(e0.z, e1.z));
+        const float2 mm = make_float2(on0 ? m0 : 0.f, on1 ? m1 : 0.f);
         const float2 mr = __fmul2_rn(mm, rinv);
-        const float2 fac = __fmul2_rn(__fmul2_rn(mr, rinv2), make_float2(w0.x, w1.x));
+        const float2 fac = __fmul2_rn(__fmul2_rn(mr, rinv2), wf);
         A.x = __ffma2_rn(dx, fac, A.x);
         A.y = __ffma2_rn(dy, fac, A.y);
         A.z = __ffma2_rn(dz, fac, A.z);
-        A.p = __ffma2_rn(mr, make_float2(w0.y, w1.y), A.p);       // sign applied at the flush
+        A.p = __ffma2_rn(mr, wp, A.p);       // sign applied at the flush
     } else {
         const float2 w0 = sq_lds_f2(a0), w1 = sq_lds_f2(a1);
         const float2 wf = make_float2(fmaf(d.x, w0.y, w0.x), fmaf(d.y, w1.y, w1.x));
@@ -267,48 +274,75 @@ __device__ __forceinline__ void sq_eval_list(const sq_walk_warp_smem & W, int ns
 
 // ---- careful evaluation of the near list (slice s takes entries s, s+S, ...): softened pairs (r < 2.8 eps),
 // the target meeting itself in its own leaf (r = 0, as in the reference), per-pair periodic wrap.
+template <bool POT>
+__device__ __forceinline__ void sq_near_pair(const float4 src, unsigned tabrow0, const sq_walk_par & P, bool pairwrap, bool soft_only,
+                                             float tx, float ty, float tz, float & ax, float & ay, float & az, float & ap, bool & deferred)
+{
+    float dx = src.x - tx, dy = src.y - ty, dz = src.z - tz;
+    if(pairwrap) {
+        dx -= P.f_boxs * rintf(dx * P.f_invboxs);
+        dy -= P.f_boxs * rintf(dy * P.f_invboxs);
+        dz -= P.f_boxs * rintf(dz * P.f_invboxs);
+    }
+    const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+    float r, fac, facpot;
+    if(r2 >= P.f_h2) {
+        const float rinv = sq_rsqrt(r2);
+        r = r2 * rinv; fac = rinv * rinv * rinv; facpot = -rinv;
+    } else {
+        if(!soft_only) { deferred = true; return; }
+        r = sqrtf(r2);
+        const float2 sf = sq_soft_kernel(r, P.f_hs);
+        fac = sf.x; facpot = sf.y;
+    }
+    // i = floor(r) clamped to the zero rows from 511 on
+    const float fl = fminf(floorf(r), 511.f);
+    const float d = (r - fl) - 0.5f;
+    const unsigned addr = tabrow0 + ((unsigned) (int) fl << 7);
+    float wf, wp = 0.f;
+    if(POT) {
+        const float4 e = sq_lds_f4(addr);
+        wf = fmaf(d, e.y, e.x); wp = fmaf(d, e.w, e.z);
+    } else {
+        const float2 w = sq_lds_f2(addr);
+        wf = fmaf(d, w.y, w.x);
+    }
+    const float f = src.w * fac * wf;
+    ax = fmaf(dx, f, ax);
+    ay = fmaf(dy, f, ay);
+    az = fmaf(dz, f, az);
+    if(POT) ap = fmaf(src.w * facpot, wp, ap);
+}
+
+// ---- careful evaluation of the near list (slice s takes entries s, s+S, ...): softened pairs (r < 2.8 eps),
+// the target meeting itself in its own leaf (r = 0, as in the reference), per-pair periodic wrap.
+// Softened pairs are rare per lane (typically the self pair only) but nearly every entry has one in SOME lane, so a
+// lane queues its softened entries (two slots) and the FP64 spline runs once or twice per flush instead of per entry.
 template <bool POT, int S>
 __device__ __forceinline__ void sq_eval_near(const sq_walk_warp_smem & W, int nn, unsigned tabrow0, const sq_walk_par & P, bool pairwrap,
                                              float tx, float ty, float tz, int s, int t, float & ax, float & ay, float & az, float & ap)
 {
+    int nq = 0, q0 = 0, q1 = 0;
     for(int k = s; k < nn; k += S) {
         const float4 src = W.nl[k];
         const unsigned m = W.nm[k];
         if((m >> t) & 1u) {
-            float dx = src.x - tx, dy = src.y - ty, dz = src.z - tz;
-            if(pairwrap) {
-                dx -= P.f_boxs * rintf(dx * P.f_invboxs);
-                dy -= P.f_boxs * rintf(dy * P.f_invboxs);
-                dz -= P.f_boxs * rintf(dz * P.f_invboxs);
+            bool deferred = false;
+            sq_near_pair<POT>(src, tabrow0, P, pairwrap, false, tx, ty, tz, ax, ay, az, ap, deferred);
+            if(deferred) {
+                if(nq == 0) q0 = k;
+                else if(nq == 1) q1 = k;
+                else sq_near_pair<POT>(src, tabrow0, P, pairwrap, true, tx, ty, tz, ax, ay, az, ap, deferred);
+                nq++;
             }
-            const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-            float r, fac, facpot;
-            if(r2 >= P.f_h2) {
-                const float rinv = sq_rsqrt(r2);
-                r = r2 * rinv; fac = rinv * rinv * rinv; facpot = -rinv;
-            } else {
-                r = sqrtf(r2);
-                const float2 sf = sq_soft_kernel(r, P.f_hs);
-                fac = sf.x; facpot = sf.y;
-            }
-            if(r < 511.f) {
-                const float fl = floorf(r);
-                const float fr = r - fl;
-                const unsigned addr = tabrow0 + ((unsigned) (int) fl << 7);
-                float wf, wp = 0.f;
-                if(POT) {
-                    const float2 e0 = sq_lds_f2(addr), e1 = sq_lds_f2(addr + 128);
-                    wf = fmaf(fr, e1.x - e0.x, e0.x); wp = fmaf(fr, e1.y - e0.y, e0.y);
-                } else {
-                    const float2 w = sq_lds_f2(addr);
-                    wf = fmaf(fr - 0.5f, w.y, w.x);
-                }
-                const float f = src.w * fac * wf;
-                ax = fmaf(dx, f, ax);
-                ay = fmaf(dy, f, ay);
-                az = fmaf(dz, f, az);
-                if(POT) ap = fmaf(src.w * facpot, wp, ap);
-            }
+        }
+    }
+    #pragma unroll 1
+    for(int j = 0; j < 2; j++) {
+        if(!__any_sync(SQ_FULL, nq > j)) break;
+        if(nq > j) {
+            bool deferred = false;
+            sq_near_pair<POT>(W.nl[j == 0 ? q0 : q1], tabrow0, P, pairwrap, true, tx, ty, tz, ax, ay, az, ap, deferred);
         }
     }
 }
@@ -335,13 +369,20 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 * tab = reinterpret_cast<float2 *>(smem_raw);
     sq_walk_warp_smem * Wall = reinterpret_cast<sq_walk_warp_smem *>(smem_raw + TAB_BYTES);
-    // 16 copies of every table row side by side: copy c of row i at byte i*128 + c*8
-    for(int i = threadIdx.x; i < TAB_ROWS * TAB_COPIES; i += blockDim.x)
-        tab[i] = gtab[i / TAB_COPIES];
+    // copies of every table row side by side in a 128-byte row: 16 x float2 (force only) or 8 x float4 (force + potential)
+    if(POT) {
+        const float4 * g4 = reinterpret_cast<const float4 *>(gtab);
+        float4 * tab4 = reinterpret_cast<float4 *>(smem_raw);
+        for(int i = threadIdx.x; i < TAB_ROWS * (TAB_COPIES / 2); i += blockDim.x)
+            tab4[i] = g4[i / (TAB_COPIES / 2)];
+    } else {
+        for(int i = threadIdx.x; i < TAB_ROWS * TAB_COPIES; i += blockDim.x)
+            tab[i] = gtab[i / TAB_COPIES];
+    }
     const unsigned lane = sq_lane();
     sq_walk_warp_smem & W = Wall[threadIdx.x >> 5];
     __syncthreads();
-    const unsigned tabrow0 = (unsigned) __cvta_generic_to_shared(tab) + (lane & 15u) * 8u;
+    const unsigned tabrow0 = (unsigned) __cvta_generic_to_shared(tab) + (POT ? (lane & 7u) * 16u : (lane & 15u) * 8u);
     // biased so that the mantissa bits of (x + 1.5*2^23) index the rows directly
     const unsigned tabaddr = tabrow0 - (0x4B400000u << 7);
     const int t = (int) (lane & (G - 1)), s = (int) (lane / G);
@@ -447,6 +488,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             float4 nodeE = make_float4(0.f, 0.f, 0.f, 0.f);
             int node = 0;
             unsigned t2_need = 0, risky_exact = 0;
+            bool relonly = false;
             float4 t2_cm = nodeE, t2_cl = nodeE, t2_lm = nodeE;
             if(!drain) {
                 // pop the entries whose children fit the 32 lanes (always at least one: <= 8 children); every child can
@@ -521,13 +563,39 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                             // ---- tier 0: the targets that keep the node, exact
                             unsigned keep = mask;
                             bool known = !(ef > efB);               // inside every target's box
+                            const bool known_exact = known || (intkeep && e_in != -2);
                             if(!known && intkeep && e_in != -2) {
                                 known = true;
                                 if(e_in >= 0) {
+                                    // only the faces of the keep box that cut through the group's extent need a search
+                                    const int c0 = (int) (B.x - ix0), c1 = (int) (B.y - iy0), c2 = (int) (B.z - iz0);
+                                    unsigned tasks = 0;
+                                    if(sq_add_sat(c0, e_in) < mxx) tasks |= 1u;
+                                    if(sq_sub_sat(c0, e_in) > mnx) tasks |= 2u;
+                                    if(sq_add_sat(c1, e_in) < mxy) tasks |= 4u;
+                                    if(sq_sub_sat(c1, e_in) > mny) tasks |= 8u;
+                                    if(sq_add_sat(c2, e_in) < mxz) tasks |= 16u;
+                                    if(sq_sub_sat(c2, e_in) > mnz) tasks |= 32u;
                                     bool amb = false;
-                                    keep &= sq_axis_keep(W.sx[0], W.pmk[0], (int) (B.x - ix0), e_in, e_out, amb);
-                                    keep &= sq_axis_keep(W.sx[1], W.pmk[1], (int) (B.y - iy0), e_in, e_out, amb);
-                                    keep &= sq_axis_keep(W.sx[2], W.pmk[2], (int) (B.z - iz0), e_in, e_out, amb);
+                                    while(tasks) {
+                                        const int j = __ffs((int) tasks) - 1;
+                                        tasks &= tasks - 1u;
+                                        const int a = j >> 1;
+                                        const bool lower = (j & 1) != 0;
+                                        const int c = a == 0 ? c0 : (a == 1 ? c1 : c2);
+                                        const int * sa = W.sx[a];
+                                        // upper face: targets with x <= c + e_in pass; lower face: targets with x < c - e_in fail
+                                        const int v = lower ? sq_sub_sat(c, e_in) - 1 : sq_add_sat(c, e_in);     // the task bit implies no saturation at INT_MIN
+                                        const int k = sq_count_le(sa, v);
+                                        const unsigned pm = W.pmk[a][k];
+                                        if(lower) {
+                                            if(k > 0 && sa[k - 1] >= sq_sub_sat(c, e_out)) amb = true;
+                                            keep &= ~pm;
+                                        } else {
+                                            if(k < 32 && sa[k] != 0x7fffffff && sa[k] <= sq_add_sat(c, e_out)) amb = true;
+                                            keep &= pm;
+                                        }
+                                    }
                                     if(amb) { risky_exact = mask; keep = 0u; }
                                 }
                             }
@@ -544,7 +612,12 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                                 const bool go_hi = (mlB > r2fh * r2fh * ta_hi) || (r2f < bhB) || (ef < inB);
                                 if(go_lo == go_hi) {
                                     if(go_hi) open_mask = keep; else acc_mask = keep;
-                                } else need = keep;
+                                } else {
+                                    need = keep;
+                                    // kept for certain, and neither the angle nor the inside test can fire for any target:
+                                    // only the relative criterion is left to tier 2
+                                    relonly = known_exact && !(r2n < bhA) && !(en < inA);
+                                }
                             }
                         }
                         if(need) {
@@ -552,7 +625,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                             t2_need = need;
                             t2_cm = make_float4(cmx, cmy, cmz, dr2);
                             t2_cl = make_float4(cx, cy, cz, de);
-                            t2_lm = make_float4(len, ml2, 0.f, 0.f);
+                            t2_lm = make_float4(len, ml2, 0.f, relonly ? 1.f : 0.f);
                         }
                     }
                 }
@@ -577,20 +650,24 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                         const float4 a = W.nrec[ii][0], c4 = W.nrec[ii][1], lm = W.nrec[ii][2];
                         const float dr2 = a.w, de = c4.w, len = lm.x, ml2 = lm.y;
                         const bool mine = act && ((__float_as_uint(lm.z) >> t) & 1u);
-                        const float eff = fmaf(0.5f, len, P.f_rcut), ins = 0.6f * len, bhq = len * len * P.f_invbh2;
-                        const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
-                        const float efA = fmaf(eff, 1.f + SQ_EPS, de), efB = fmaf(eff, 1.f - SQ_EPS, -de);
-                        const float inA = fmaf(ins, 1.f + SQ_EPS, de), inB = fmaf(ins, 1.f - SQ_EPS, -de);
-                        const float bhA = fmaf(bhq, 1.f + SQ_EPS, dr2), bhB = fmaf(bhq, 1.f - SQ_EPS, -dr2);
                         const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
                         const float dx = a.x - tx, dy = a.y - ty, dz = a.z - tz;
                         const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                        const float em = fmaxf(fmaxf(fabsf(c4.x - tx), fabsf(c4.y - ty)), fabsf(c4.z - tz));
-                        const bool k_lo = (r2 <= rcA) || !(em > efA);
-                        const bool k_hi = (r2 <= rcB) || !(em > efB);
                         const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
-                        const bool o_lo = (mlA > r2l * r2l * ta) || (r2 < bhA) || (em < inA);
-                        const bool o_hi = (mlB > r2h * r2h * ta) || (r2 < bhB) || (em < inB);
+                        bool k_lo = true, k_hi = true;
+                        bool o_lo = mlA > r2l * r2l * ta, o_hi = mlB > r2h * r2h * ta;
+                        if(lm.w == 0.f) {
+                            const float eff = fmaf(0.5f, len, P.f_rcut), ins = 0.6f * len, bhq = len * len * P.f_invbh2;
+                            const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
+                            const float efA = fmaf(eff, 1.f + SQ_EPS, de), efB = fmaf(eff, 1.f - SQ_EPS, -de);
+                            const float inA = fmaf(ins, 1.f + SQ_EPS, de), inB = fmaf(ins, 1.f - SQ_EPS, -de);
+                            const float bhA = fmaf(bhq, 1.f + SQ_EPS, dr2), bhB = fmaf(bhq, 1.f - SQ_EPS, -dr2);
+                            const float em = fmaxf(fmaxf(fabsf(c4.x - tx), fabsf(c4.y - ty)), fabsf(c4.z - tz));
+                            k_lo = (r2 <= rcA) || !(em > efA);
+                            k_hi = (r2 <= rcB) || !(em > efB);
+                            o_lo = o_lo || (r2 < bhA) || (em < inA);
+                            o_hi = o_hi || (r2 < bhB) || (em < inB);
+                        }
                         const bool ex = k_lo != k_hi || (k_lo && o_lo != o_hi);
                         const unsigned bx = __ballot_sync(SQ_FULL, mine && ex);
                         const unsigned bo = __ballot_sync(SQ_FULL, mine && !ex && k_lo && o_lo);
@@ -812,18 +889,17 @@ static int sq_walk_table(sq_ctx * c)
             pt[i] = (float) erfc(u);
         }
     }
-    float2 h[2][TAB_ROWS];
-    for(int i = 0; i < TAB_ROWS; i++) {
-        h[0][i] = make_float2(0.f, 0.f);
-        h[1][i] = make_float2(0.f, 0.f);
-        if(i + 1 < SQ_NTAB) {
-            const double sf = (double) ft[i + 1] - (double) ft[i];
-            h[0][i] = make_float2((float) ((double) ft[i] + 0.5 * sf), (float) sf);
-        }
-        if(i < SQ_NTAB) h[1][i] = make_float2(ft[i], pt[i]);
+    // device image: TAB_ROWS float2 rows (force only) followed by TAB_ROWS float4 rows (force + potential)
+    static_assert(TAB_ROWS % 2 == 1, "float4 part starts 8 bytes after a 16-byte boundary otherwise");
+    struct { float2 f[TAB_ROWS + 1]; float4 fp[TAB_ROWS]; } h;
+    memset(&h, 0, sizeof(h));
+    for(int i = 0; i + 1 < SQ_NTAB; i++) {
+        const double sf = (double) ft[i + 1] - (double) ft[i], sp = (double) pt[i + 1] - (double) pt[i];
+        h.f[i] = make_float2((float) ((double) ft[i] + 0.5 * sf), (float) sf);
+        h.fp[i] = make_float4((float) ((double) ft[i] + 0.5 * sf), (float) sf, (float) ((double) pt[i] + 0.5 * sp), (float) sp);
     }
     SQ_TRY(c->w_table.reserve(sizeof(h)));
-    SQ_CUDA(cudaMemcpyAsync(c->w_table.p, h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(c->w_table.p, &h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));
     return SQ_OK;
 }
@@ -843,7 +919,7 @@ static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets
     if(grid < 1) grid = 1;
     sq_walk_kernel<POT, G><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->w_icm.as<uint4>(), c->w_icl.as<uint4>(), c->t_lk.as<int4>(),
             c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->w_ipart.as<uint4>(), c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(),
-            targets, (long long) ntargets, c->w_table.as<float2>() + (POT ? TAB_ROWS : 0), c->w_accel.as<double>(), c->w_pot.as<double>(),
+            targets, (long long) ntargets, c->w_table.as<float2>() + (POT ? TAB_ROWS + 1 : 0), c->w_accel.as<double>(), c->w_pot.as<double>(),
             c->w_stats.as<unsigned long long>(), c->w_counter.as<int>(), P);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
