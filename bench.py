@@ -180,7 +180,8 @@ def run_dist(args, rank, local_rank, world):
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p")     # keep stdout to the one JSON line
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":              # NCCL prints its banner on stdout: keep it to the one JSON line
+        del os.environ["NCCL_DEBUG"]
     dist.init_process_group("nccl", device_id=dev)
     import shenqi_b200 as sq
     from shenqi_b200.ics import zeldovich_torch, rho0, G_INTERNAL
