@@ -26,6 +26,9 @@ import numpy as np
 # 23 flop per interaction, 28 when the potential is accumulated as well.  The step benchmarked is a
 # PM step on a full-particle tree, where the reference also updates the potential (gravshort-tree2.cpp:148).
 FLOP_PER_INTERACTION = 28
+# dram__bytes_read.sum + dram__bytes_write.sum of one sq_walk_kernel launch on the N=1 workload (256^3), from the
+# `ncu --set full` capture summarised in profiles/r1_walk_v5c_sections.txt (1.663 GB + 0.526 GB); None for other sizes
+WALK_DRAM_TRAFFIC_256 = 2.189e9
 DIST_NGRID = {2: 320, 4: 400, 8: 512}   # ~256^3 particles per GPU (weak scaling), Nmesh = 2 Ngrid divisible by the ranks
 
 
@@ -462,7 +465,7 @@ def main():
             "walk_particles_per_s": world * n / (wms * 1e-3),
             "stage_ms": stage_ms, "tree_nodes": int(numnodes),
             "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None,
+                         "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": WALK_DRAM_TRAFFIC_256 if args.ngrid == 256 else None, "traffic_unit": "bytes per launch (ncu dram read + write)",
                          "flop_per_interaction": FLOP_PER_INTERACTION, "peak_source": "FFMA microbenchmark in this run (sq_measure_fp32_peak)",
                          "lane_efficiency": interactions / float(max(1, np.mean([s.list_entries for s in stats]) * 32))},
             "roofline_hbm": {"peak_gbs": hbm_peak, "peak_source": peak_src, "stages": hbm},
