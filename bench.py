@@ -452,7 +452,7 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         de = float(tt.item())
     e2e_value = world * n / (de / e2e_steps)
-    h2d = n * (24 + 4 + 48) + n * 24 + n * 8       # pos, mass, old accelerations; accel/potential buffers round-trip (inactive entries are preserved)
+    h2d = n * (24 + 4 + 48)                        # pos, mass, FullTreeGravAccel + GravPM (the |a_old| inputs)
     d2h = n * (24 + 8 + 24 + 8)
 
     line = {"metric": "short-range gravity particles/s", "value": value, "unit": "particles/s", "n_gpus": world, "steps": args.steps,

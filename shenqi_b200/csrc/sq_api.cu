@@ -111,7 +111,7 @@ void sq_ctx_destroy(sq_ctx * c)
                        &c->t_lk, &c->t_parent, &c->t_rot, &c->t_lvl, &c->t_counters, &c->tree_keys, &c->tree_order, &c->tree_pos, &c->tree_mass,
                        &c->active_sorted, &c->w_accel, &c->w_pot, &c->w_stats, &c->w_targets, &c->w_table, &c->w_out_accel, &c->w_out_pot,
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
-                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp};
+                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
     if(c->stream && c->own_stream) cudaStreamDestroy(c->stream);
@@ -226,19 +226,15 @@ int sq_set_old_accel(sq_ctx * c, const double * fulltree, const double * gravpm)
     if(!c) return SQ_ERR_ARG;
     if(!c->have_params) { sq_set_error("sq_set_old_accel: call sq_set_params first"); return SQ_ERR_ARG; }
     const int64_t n = c->n;
-    sq_buf a, b;
-    int rc = SQ_OK;
-    do {
-        if(fulltree) { if((rc = a.reserve(sizeof(double) * 3 * (size_t) (n + 1)))) break; cudaMemcpyAsync(a.p, fulltree, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream); }
-        if(gravpm) { if((rc = b.reserve(sizeof(double) * 3 * (size_t) (n + 1)))) break; cudaMemcpyAsync(b.p, gravpm, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream); }
-        if(n > 0) {
-            sq_oldacc_kernel<<<api_grid(c, n), 256, 0, c->stream>>>(a.as<double>(), b.as<double>(), n, c->par.G, c->oldacc_in.as<double>());
-            c->kernel_launches++;
-        }
-        if(cudaStreamSynchronize(c->stream) != cudaSuccess) { sq_set_error("sq_set_old_accel: %s", cudaGetErrorString(cudaGetLastError())); rc = SQ_ERR_CUDA; }
-    } while(0);
-    a.release(); b.release();
-    if(rc != SQ_OK) return rc;
+    // staging in two scratch buffers the context already owns (not in use before the next walk / download)
+    sq_buf & a = c->w_out_accel, & b = c->oldacc_tmp;
+    if(fulltree) { SQ_TRY(a.reserve(sizeof(double) * 3 * (size_t) (n + 1))); SQ_CUDA(cudaMemcpyAsync(a.p, fulltree, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream)); }
+    if(gravpm) { SQ_TRY(b.reserve(sizeof(double) * 3 * (size_t) (n + 1))); SQ_CUDA(cudaMemcpyAsync(b.p, gravpm, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream)); }
+    if(n > 0) {
+        sq_oldacc_kernel<<<api_grid(c, n), 256, 0, c->stream>>>(fulltree ? a.as<double>() : nullptr, gravpm ? b.as<double>() : nullptr, n, c->par.G, c->oldacc_in.as<double>());
+        c->kernel_launches++;
+        SQ_CUDA(cudaGetLastError());
+    }
     if(c->sorted) SQ_TRY(sq_gather_run(c));
     return sq_sync(c);
 }
@@ -317,7 +313,8 @@ int sq_download_accel(sq_ctx * c, double * accel, double * potential)
     const long long m = c->walk_ntargets;
     if(accel) {
         SQ_TRY(c->w_out_accel.reserve(sizeof(double) * 3 * (size_t) (n + 1)));
-        SQ_CUDA(cudaMemcpyAsync(c->w_out_accel.p, accel, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream));
+        // a partial walk leaves the other particles' entries as the caller passed them: bring those in first
+        if(!all) SQ_CUDA(cudaMemcpyAsync(c->w_out_accel.p, accel, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream));
         if(m > 0) {
             sq_unpermute_kernel<3><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_accel.as<double>(), 3, 0, c->perm.as<uint32_t>(), targets, m, c->w_out_accel.as<double>());
             c->kernel_launches++;
@@ -326,7 +323,7 @@ int sq_download_accel(sq_ctx * c, double * accel, double * potential)
     }
     if(potential && c->tree_full) {
         SQ_TRY(c->w_out_pot.reserve(sizeof(double) * (size_t) (n + 1)));
-        SQ_CUDA(cudaMemcpyAsync(c->w_out_pot.p, potential, sizeof(double) * (size_t) n, cudaMemcpyHostToDevice, c->stream));
+        if(!all) SQ_CUDA(cudaMemcpyAsync(c->w_out_pot.p, potential, sizeof(double) * (size_t) n, cudaMemcpyHostToDevice, c->stream));
         if(m > 0) {
             sq_unpermute_kernel<1><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_pot.as<double>(), 1, 0, c->perm.as<uint32_t>(), targets, m, c->w_out_pot.as<double>());
             c->kernel_launches++;

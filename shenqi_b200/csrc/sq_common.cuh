@@ -93,7 +93,7 @@ struct sq_ctx {
 
     // ---- particles, upload order
     int64_t n = 0;
-    sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in;
+    sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in, oldacc_tmp;
     bool have_types = false;
     // ---- particles, PH-sorted order
     sq_buf pos, mass, oldacc, keys, perm, rank;   // perm[sorted] = upload idx; rank[upload] = sorted pos

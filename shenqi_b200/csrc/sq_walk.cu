@@ -81,11 +81,12 @@ struct sq_walk_warp_smem {
     unsigned mw[LIST_CAP + LIST_PAD];  // mask words, one per evaluation step: bit (s*G + t) = entry of slice s reaches target t
     unsigned nm[NEAR_CAP];
     float4 nrec[32][3];                // tier 2 work list: (cm.xyz, dr2) (centre.xyz, de) (len, M l^2, need mask, -)
-    int s_end[32], s_first[32];        // pop: children of the popped entries; later in the step: particles of opened leaves
+    int s_first[32];                     // pop: children of the popped entries; later in the step: particles of opened leaves
     unsigned s_mask[32];
     int sx[3][32];                     // target coordinates per axis, sorted (fixed point, relative to the first target)
     unsigned pmk[3][36];               // pmk[a][k] = targets among the k smallest coordinates of axis a
     unsigned char scnt[STACK_CAP];     // child count of stack entry i
+    unsigned char src[256];            // slot j of an expansion (children of popped entries / particles of opened leaves) -> lane that owns it
 };
 
 static_assert(TAB_BYTES + WALK_WARPS * sizeof(sq_walk_warp_smem) <= 232448, "walk kernel shared memory exceeds the 227 KB of an sm_100 CTA");
@@ -501,22 +502,18 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 const int nchild = __shfl_sync(SQ_FULL, exc + cnt, npop - 1);
                 if((int) lane < npop) {
                     const int2 e = W.stack[top - 1 - lane];
-                    W.s_end[lane] = exc + cnt;
                     W.s_first[lane] = e.x - exc;
                     W.s_mask[lane] = (unsigned) e.y;
+                    for(int k = 0; k < cnt; k++) W.src[exc + k] = (unsigned char) lane;
                 }
                 top -= npop;
                 __syncwarp();
                 const bool have = (int) lane < nchild;
                 unsigned mask = 0;
                 if(have) {
-                    int lo = 0, hi = npop - 1;
-                    while(lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        if(W.s_end[mid] > (int) lane) hi = mid; else lo = mid + 1;
-                    }
-                    node = W.s_first[lo] + (int) lane;
-                    mask = W.s_mask[lo];
+                    const int o = W.src[lane];
+                    node = W.s_first[o] + (int) lane;
+                    mask = W.s_mask[o];
                 }
                 __syncwarp();
                 if(have) {
@@ -722,9 +719,9 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 const int off = sq_warp_excl_scan(np, tot_leaf);
                 if(tot_leaf) {
                     st_int += (unsigned long long) np * __popc(open_mask);
-                    W.s_end[lane] = off + np;
                     W.s_first[lane] = L.x - off;        // particle = s_first + j
                     W.s_mask[lane] = open_mask;
+                    for(int k = 0; k < np; k++) W.src[off + k] = (unsigned char) lane;
                 }
             }
             st_int += __popc(acc_mask);
@@ -742,12 +739,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 } else {
                     const int j = ((rd - 1) << 5) + (int) lane;
                     if(j < tot_leaf) {
-                        // first source lane whose end is past j
-                        int lo = 0, hi = 31;
-                        while(lo < hi) {
-                            const int mid = (lo + hi) >> 1;
-                            if(W.s_end[mid] > j) hi = mid; else lo = mid + 1;
-                        }
+                        const int lo = W.src[j];
                         const uint4 q4 = ipart[(long long) W.s_first[lo] + j];
                         e = make_float4((float) (int) (q4.x - gcix) * P.qs, (float) (int) (q4.y - gciy) * P.qs, (float) (int) (q4.z - gciz) * P.qs, __uint_as_float(q4.w));
                         m = W.s_mask[lo];
