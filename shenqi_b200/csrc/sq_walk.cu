@@ -231,8 +231,9 @@ __device__ __forceinline__ void sq_eval_pair(float x0, float x1, float y0, float
     const float2 rinv2 = __fmul2_rn(rinv, rinv);
     if(POT) {
         const float4 e0 = sq_lds_f4(a0), e1 = sq_lds_f4(a1);
-        const float2 wf = __ffma2_rn(d, make_float2(e0.y, e1.y), make_float2(e0.x, e1.x));
-        const float2 wp = __ffma2_rn(d, make_float2(e0.w, e1.w), make_float2(e0.z, e1.z));
+        // scalar FMAs here: pairing (e0.y, e1.y) etc. for the packed form costs more register moves than it saves
+        const float2 wf = make_float2(fmaf(d.x, e0.y, e0.x), fmaf(d.y, e1.y, e1.x));
+        const float2 wp = make_float2(fmaf(d.x, e0.w, e0.z), fmaf(d.y, e1.w, e1.z));
         const float2 mm = make_float2(on0 ? m0 : 0.f, on1 ? m1 : 0.f);
         const float2 mr = __fmul2_rn(mm, rinv);
         const float2 fac = __fmul2_rn(__fmul2_rn(mr, rinv2), wf);
