@@ -195,6 +195,10 @@ int sq_pm_slab_paint(sq_ctx * ctx, const double * part4, int64_t m, int rank, in
 int sq_pm_slab_fft_fwd(sq_ctx * ctx, double * slab, int nranks, double * work, double * packed);
 int sq_pm_slab_fft_x(sq_ctx * ctx, double * data, int nranks, int inverse);
 int sq_pm_slab_transfer(sq_ctx * ctx, const double * rho, int rank, int nranks, double * out4);
+/* phi_k only; the forces are then differenced in real space from the potential slab and two / three planes of each
+ * x-neighbour (4-point stencil = the reference's k-space filter of gravpm.cpp:447-475 in real space). */
+int sq_pm_slab_transfer_phi(sq_ctx * ctx, const double * rho, int rank, int nranks, double * phik);
+int sq_pm_slab_gradient(sq_ctx * ctx, double * phi, const double * lo2, const double * hi3, int nranks, double * ext, double * fx, double * fy, double * fz);
 int sq_pm_slab_fft_inv(sq_ctx * ctx, const double * recv, int nranks, double * work, double * slab);
 int sq_pm_slab_readout(sq_ctx * ctx, const double * part4, int64_t m, int rank, int nranks, const double * s0, const double * s1,
                        const double * s2, const double * s3, double * out4);

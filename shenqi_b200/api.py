@@ -66,7 +66,7 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
            "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
            "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
-           "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer",
+           "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
            "sq_pm_slab_fft_inv", "sq_pm_slab_readout"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
@@ -286,6 +286,13 @@ class Context:
 
     def pm_slab_transfer(self, rho_ptr, rank, nranks, out4_ptr):
         self._check(self.L.sq_pm_slab_transfer(self._ctx, ctypes.c_void_p(rho_ptr), c_int(rank), c_int(nranks), ctypes.c_void_p(out4_ptr)))
+
+    def pm_slab_transfer_phi(self, rho_ptr, rank, nranks, phik_ptr):
+        self._check(self.L.sq_pm_slab_transfer_phi(self._ctx, ctypes.c_void_p(rho_ptr), c_int(rank), c_int(nranks), ctypes.c_void_p(phik_ptr)))
+
+    def pm_slab_gradient(self, phi_ptr, lo2_ptr, hi3_ptr, nranks, ext_ptr, fx_ptr, fy_ptr, fz_ptr):
+        self._check(self.L.sq_pm_slab_gradient(self._ctx, ctypes.c_void_p(phi_ptr), ctypes.c_void_p(lo2_ptr), ctypes.c_void_p(hi3_ptr), c_int(nranks),
+                                               ctypes.c_void_p(ext_ptr), ctypes.c_void_p(fx_ptr), ctypes.c_void_p(fy_ptr), ctypes.c_void_p(fz_ptr)))
 
     def pm_slab_fft_inv(self, recv_ptr, nranks, work_ptr, slab_ptr):
         self._check(self.L.sq_pm_slab_fft_inv(self._ctx, ctypes.c_void_p(recv_ptr), c_int(nranks), ctypes.c_void_p(work_ptr), ctypes.c_void_p(slab_ptr)))

@@ -167,5 +167,6 @@ int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_
 int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
 int sq_pm_run(sq_ctx * c, bool paint_only);
 void sq_pm_destroy(sq_ctx * c);
+int sq_pm_gradient(sq_ctx * c, const double * phi, int nout, int xwrap, double * fx, double * fy, double * fz);
 void sq_dist_destroy(sq_ctx * c);
 int sq_walk_range_targets(sq_ctx * c, sq_buf * out);

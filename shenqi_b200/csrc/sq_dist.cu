@@ -227,10 +227,12 @@ __global__ void __launch_bounds__(256) sqd_slab_transfer_kernel(const double2 * 
             v.x *= fac; v.y *= fac;
         }
         potk[ip] = v;
-        const double fx = dker[ix], fy = dker[iy], fz = dker[iz];
-        fxk[ip] = make_double2(-v.y * fx, v.x * fx);
-        fyk[ip] = make_double2(-v.y * fy, v.x * fy);
-        fzk[ip] = make_double2(-v.y * fz, v.x * fz);
+        if(fxk) {
+            const double fx = dker[ix], fy = dker[iy], fz = dker[iz];
+            fxk[ip] = make_double2(-v.y * fx, v.x * fx);
+            fyk[ip] = make_double2(-v.y * fy, v.x * fy);
+            fzk[ip] = make_double2(-v.y * fz, v.x * fz);
+        }
     }
 }
 
@@ -521,6 +523,39 @@ int sq_pm_slab_transfer(sq_ctx * c, const double * rho, int rank, int nranks, do
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
     return SQ_OK;
+}
+
+// rho_k -> phi_k in place of the four outputs: the forces are differenced in real space (sq_pm_slab_gradient)
+int sq_pm_slab_transfer_phi(sq_ctx * c, const double * rho, int rank, int nranks, double * phik)
+{
+    SQ_TRY(slab_check(c, nranks, "sq_pm_slab_transfer_phi"));
+    SQ_TRY(slab_plans(c, nranks));
+    const int N = c->par.Nmesh, nyl = N / nranks, nzh = N / 2 + 1;
+    const size_t per = (size_t) N * nyl * nzh;
+    const double asmth2 = pow((2 * M_PI) * c->par.Asmth / N, 2);
+    const double pot_factor = -c->par.G / (M_PI * c->par.BoxSize);
+    sqd_slab_transfer_kernel<<<dist_grid(c, (long long) per, 16), 256, 0, c->stream>>>((const double2 *) rho, N, rank * nyl, nyl, asmth2, pot_factor,
+            c->slab_tab.as<double>(), c->slab_tab.as<double>() + N, (double2 *) phik, nullptr, nullptr, nullptr);
+    c->kernel_launches++;
+    SQ_CUDA(cudaGetLastError());
+    return SQ_OK;
+}
+
+// Potential slab (planes 0 .. nxl-1 valid) + the neighbours' planes -> force slabs by the 4-point difference.
+//   lo2: planes -2, -1 (the previous rank's last two), hi3: planes nxl .. nxl+2 (the next rank's first three)
+//   ext: work space (nxl + 5) planes; fx, fy, fz: (nxl + 1) planes each (the last one is the CIC ghost plane);
+//   phi[nxl] is filled with the ghost plane as well.
+int sq_pm_slab_gradient(sq_ctx * c, double * phi, const double * lo2, const double * hi3, int nranks, double * ext, double * fx, double * fy, double * fz)
+{
+    SQ_TRY(slab_check(c, nranks, "sq_pm_slab_gradient"));
+    const int N = c->par.Nmesh, nxl = N / nranks;
+    if(nxl < 3) { sq_set_error("sq_pm_slab_gradient: needs at least 3 planes per rank"); return SQ_ERR_ARG; }
+    const size_t plane = (size_t) N * N;
+    SQ_CUDA(cudaMemcpyAsync(ext, lo2, sizeof(double) * 2 * plane, cudaMemcpyDeviceToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(ext + 2 * plane, phi, sizeof(double) * (size_t) nxl * plane, cudaMemcpyDeviceToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(ext + (size_t) (2 + nxl) * plane, hi3, sizeof(double) * 3 * plane, cudaMemcpyDeviceToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(phi + (size_t) nxl * plane, hi3, sizeof(double) * plane, cudaMemcpyDeviceToDevice, c->stream));
+    return sq_pm_gradient(c, ext + 2 * plane, nxl + 1, 0, fx, fy, fz);
 }
 
 // received blocks [nranks][nxl][nyl][Nzh] -> planes (work) -> 2-D c2r into the slab's nxl planes

@@ -136,11 +136,61 @@ __global__ void __launch_bounds__(256) sq_pm_transfer_kernel(const double2 * rho
             v.x *= fac; v.y *= fac;
         }
         potk[ip] = v;
-        const double fx = dker[ix], fy = dker[iy], fz = dker[iz];
-        fxk[ip] = make_double2(-v.y * fx, v.x * fx);
-        fyk[ip] = make_double2(-v.y * fy, v.x * fy);
-        fzk[ip] = make_double2(-v.y * fz, v.x * fz);
+        if(fxk) {       // k-space differencing (the reference's four c2r transforms); the product path differences phi in real space
+            const double fx = dker[ix], fy = dker[iy], fz = dker[iz];
+            fxk[ip] = make_double2(-v.y * fx, v.x * fx);
+            fyk[ip] = make_double2(-v.y * fy, v.x * fy);
+            fzk[ip] = make_double2(-v.y * fz, v.x * fz);
+        }
     }
+}
+
+// Force meshes from the potential mesh by the 4-point central difference
+//     F = -[ 2/3 (phi(+1) - phi(-1)) - 1/12 (phi(+2) - phi(-2)) ] N / Box
+// which is the real-space form of the reference's k-space filter i K(w), K(w) = (8 sin w - sin 2w) / 6
+// (gravpm.cpp:447-475: "the same as GADGET-2 but in fourier space").  One c2r transform instead of four; equal to the
+// k-space result to rounding (tests: 1e-9 of the restatement, which keeps the four transforms).
+// phi addresses plane 0 of nout output planes; xwrap: plane indices wrap mod nmesh (single GPU), otherwise planes
+// -2 .. nout + 1 exist around it (x-slab with ghost planes).  y and z are periodic in the mesh.
+__global__ void __launch_bounds__(256) sq_pm_gradient_kernel(const double * __restrict__ phi, int nmesh, int nout, int xwrap, double scale,
+                                                             double * __restrict__ fx, double * __restrict__ fy, double * __restrict__ fz)
+{
+    const long long plane = (long long) nmesh * nmesh;
+    const long long total = plane * nout;
+    const double c1 = -scale * (2.0 / 3.0), c2 = scale / 12.0;
+    for(long long ip = (long long) blockIdx.x * blockDim.x + threadIdx.x; ip < total; ip += (long long) gridDim.x * blockDim.x) {
+        const int iz = (int) (ip % nmesh);
+        const long long t = ip / nmesh;
+        const int iy = (int) (t % nmesh);
+        const int ix = (int) (t / nmesh);
+        int xm2 = ix - 2, xm1 = ix - 1, xp1 = ix + 1, xp2 = ix + 2;
+        if(xwrap) {
+            xm2 += xm2 < 0 ? nmesh : 0; xm1 += xm1 < 0 ? nmesh : 0;
+            xp1 -= xp1 >= nmesh ? nmesh : 0; xp2 -= xp2 >= nmesh ? nmesh : 0;
+        }
+        const int ym2 = iy - 2 + (iy < 2 ? nmesh : 0), ym1 = iy - 1 + (iy < 1 ? nmesh : 0);
+        const int yp1 = iy + 1 - (iy + 1 >= nmesh ? nmesh : 0), yp2 = iy + 2 - (iy + 2 >= nmesh ? nmesh : 0);
+        const int zm2 = iz - 2 + (iz < 2 ? nmesh : 0), zm1 = iz - 1 + (iz < 1 ? nmesh : 0);
+        const int zp1 = iz + 1 - (iz + 1 >= nmesh ? nmesh : 0), zp2 = iz + 2 - (iz + 2 >= nmesh ? nmesh : 0);
+        const long long row = (long long) iy * nmesh, col = (long long) ix * plane;
+        const long long yz = row + iz;
+        fx[ip] = c1 * (phi[xp1 * plane + yz] - phi[xm1 * plane + yz]) + c2 * (phi[xp2 * plane + yz] - phi[xm2 * plane + yz]);
+        fy[ip] = c1 * (phi[col + (long long) yp1 * nmesh + iz] - phi[col + (long long) ym1 * nmesh + iz])
+               + c2 * (phi[col + (long long) yp2 * nmesh + iz] - phi[col + (long long) ym2 * nmesh + iz]);
+        fz[ip] = c1 * (phi[col + row + zp1] - phi[col + row + zm1]) + c2 * (phi[col + row + zp2] - phi[col + row + zm2]);
+    }
+}
+
+int sq_pm_gradient(sq_ctx * c, const double * phi, int nout, int xwrap, double * fx, double * fy, double * fz)
+{
+    const int N = c->par.Nmesh;
+    const long long total = (long long) N * N * nout;
+    long long need = (total + 255) / 256, cap = (long long) c->num_sms * 16;
+    if(need < 1) need = 1;
+    sq_pm_gradient_kernel<<<(int) (need < cap ? need : cap), 256, 0, c->stream>>>(phi, N, nout, xwrap, (double) N / c->par.BoxSize, fx, fy, fz);
+    c->kernel_launches++;
+    SQ_CUDA(cudaGetLastError());
+    return SQ_OK;
 }
 
 static double h_sinc_unnormed(double x)
@@ -191,10 +241,8 @@ int sq_pm_run(sq_ctx * c, bool paint_only)
         float ms = 0; cudaEventElapsedTime(&ms, c->ev[10], c->ev[11]); c->tm.pm_paint_ms = ms;
         return SQ_OK;
     }
-    for(int f = 0; f < 4; f++) {
-        SQ_TRY(c->pm_cplx[f].reserve(sizeof(double2) * ncplx));
-        if(f) SQ_TRY(c->pm_real[f].reserve(sizeof(double) * nreal));
-    }
+    SQ_TRY(c->pm_cplx[0].reserve(sizeof(double2) * ncplx));
+    for(int f = 1; f < 4; f++) SQ_TRY(c->pm_real[f].reserve(sizeof(double) * nreal));
     SQ_TRY(c->pm_out.reserve(sizeof(double) * 4 * (size_t) (n + 1) + sizeof(double) * 2 * (size_t) N));
     if(c->plan_nmesh != N) {
         sq_pm_destroy(c);
@@ -222,12 +270,12 @@ int sq_pm_run(sq_ctx * c, bool paint_only)
     const double asmth2 = pow((2 * M_PI) * c->par.Asmth / N, 2);
     const double pot_factor = -c->par.G / (M_PI * c->par.BoxSize);
     sq_pm_transfer_kernel<<<pm_grid(c, (long long) ncplx, 16), 256, 0, c->stream>>>(c->pm_cplx[0].as<double2>(), N, asmth2, pot_factor, d_tab, d_tab + N,
-            c->pm_cplx[0].as<double2>(), c->pm_cplx[1].as<double2>(), c->pm_cplx[2].as<double2>(), c->pm_cplx[3].as<double2>());
+            c->pm_cplx[0].as<double2>(), nullptr, nullptr, nullptr);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
     SQ_CUDA(cudaEventRecord(c->ev[13], c->stream));
-    for(int f = 0; f < 4; f++)
-        SQ_CUFFT(cufftExecZ2D(c->plan_c2r, c->pm_cplx[f].as<cufftDoubleComplex>(), c->pm_real[f].as<double>()));
+    SQ_CUFFT(cufftExecZ2D(c->plan_c2r, c->pm_cplx[0].as<cufftDoubleComplex>(), c->pm_real[0].as<double>()));
+    SQ_TRY(sq_pm_gradient(c, c->pm_real[0].as<double>(), N, 1, c->pm_real[1].as<double>(), c->pm_real[2].as<double>(), c->pm_real[3].as<double>()));
     SQ_CUDA(cudaEventRecord(c->ev[14], c->stream));
     if(n > 0) {
         sq_pm_readout_kernel<<<pm_grid(c, n, 8), 256, 0, c->stream>>>(c->pos.as<double>(), n, cell, N, c->pm_real[0].as<double>(), c->pm_real[1].as<double>(),

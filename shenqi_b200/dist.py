@@ -223,21 +223,21 @@ class DistGravity:
         self._mark("pm:transpose_a2a")
         B.fft_x(rho, P, False)
         self._mark("pm:fft")
-        out4 = B.transfer(rho, r, P)                           # [4, N, nyl, nzh]: phi_k, Fx_k, Fy_k, Fz_k
+        phik = B.transfer_phi(rho, r, P)                       # [N, nyl, nzh]: phi_k
         self._mark("pm:transfer")
-        slabs = []
-        for f in range(4):
-            B.fft_x(out4[f], P, True)
-            self._mark("pm:fft")
-            recv = C.alltoall_equal(out4[f].view(P, nxl, nyl, nzh))
-            self._mark("pm:transpose_a2a")
-            s = slab if f == 0 else B.new_slab(P, f)
-            B.fft_inv(recv, P, s)
-            slabs.append(s)
-            self._mark("pm:fft")
-        for s in slabs:                                        # ghost plane = the next rank's first plane
-            s[nxl] = C.shift(s[0], -1)
+        B.fft_x(phik, P, True)
+        self._mark("pm:fft")
+        recv = C.alltoall_equal(phik.view(P, nxl, nyl, nzh))
+        self._mark("pm:transpose_a2a")
+        B.fft_inv(recv, P, slab)                               # the potential on my nxl planes
+        self._mark("pm:fft")
+        # forces = 4-point difference of the potential in real space (the reference's k-space filter, gravpm.cpp:447-475):
+        # planes -2, -1 come from the previous rank, planes nxl .. nxl+2 (CIC ghost + stencil) from the next one
+        lo2 = C.shift(slab[nxl - 2:nxl], +1)
+        hi3 = C.shift(slab[0:3], -1)
         self._mark("pm:paint+ghost")
+        slabs = B.gradient(slab, lo2, hi3, P)                  # [phi, fx, fy, fz], each (nxl + 1) planes
+        self._mark("pm:gradient")
         res = B.readout(part4, r, P, slabs)
         self._mark("pm:readout")
         back = C.alltoall_rows(res, recv_counts, counts)
@@ -375,6 +375,20 @@ class CudaBackend:
         out4 = self._buf("out4", (4, N, N // P, N // 2 + 1), torch.complex128)
         self.loc.pm_slab_transfer(rho.data_ptr(), rank, P, out4.data_ptr())
         return out4
+
+    def transfer_phi(self, rho, rank, P):
+        N = self.nmesh
+        phik = self._buf("phik", (N, N // P, N // 2 + 1), torch.complex128)
+        self.loc.pm_slab_transfer_phi(rho.data_ptr(), rank, P, phik.data_ptr())
+        return phik
+
+    def gradient(self, slab, lo2, hi3, P):
+        N = self.nmesh
+        ext = self._buf("ext", (N // P + 5, N, N), torch.float64)
+        f = [self.new_slab(P, k) for k in (1, 2, 3)]
+        self.loc.pm_slab_gradient(slab.data_ptr(), lo2.contiguous().data_ptr(), hi3.contiguous().data_ptr(), P, ext.data_ptr(),
+                                  f[0].data_ptr(), f[1].data_ptr(), f[2].data_ptr())
+        return [slab] + f
 
     def fft_inv(self, recv, P, slab):
         N = self.nmesh

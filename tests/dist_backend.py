@@ -86,6 +86,24 @@ class OracleBackend:
         oracle().sqo_pm_transfer(ptr(full), c_int(N), c_dbl(self.box), c_dbl(self.par["Asmth"]), c_dbl(self.par["G"]), *[ptr(o) for o in outs])
         return torch.from_numpy(np.ascontiguousarray(np.stack([o[:, rank * nyl:(rank + 1) * nyl] for o in outs], 0)))
 
+    def transfer_phi(self, rho, rank, P):
+        return self.transfer(rho, rank, P)[0].contiguous()
+
+    def gradient(self, slab, lo2, hi3, P):
+        """numpy statement of the 4-point difference on the slab extended by the neighbours' planes"""
+        N, nxl = self.nmesh, self.nmesh // P
+        phi = slab.numpy()
+        ext = np.concatenate([lo2.numpy(), phi[:nxl], hi3.numpy()], 0)          # planes -2 .. nxl+2
+        phi[nxl] = hi3.numpy()[0]
+        scale = N / self.box
+        def d(a, axis):
+            if axis == 0:
+                c = slice(2, 2 + nxl + 1)
+                return -scale * (2. / 3 * (a[3:nxl + 4] - a[1:nxl + 2]) - 1. / 12 * (a[4:nxl + 5] - a[0:nxl + 1]))
+            b = a[2:2 + nxl + 1]
+            return -scale * (2. / 3 * (np.roll(b, -1, axis) - np.roll(b, 1, axis)) - 1. / 12 * (np.roll(b, -2, axis) - np.roll(b, 2, axis)))
+        return [slab] + [torch.from_numpy(np.ascontiguousarray(d(ext, ax))) for ax in (0, 1, 2)]
+
     def fft_inv(self, recv, P, slab):
         N, nxl, nyl = self.nmesh, self.nmesh // P, self.nmesh // P
         r = recv.numpy()
