@@ -60,24 +60,39 @@ __global__ void __launch_bounds__(256) sqd_route_scatter_kernel(const double * _
                                                                  const unsigned char * __restrict__ owner, int * __restrict__ cursor,
                                                                  double4 * __restrict__ send, int * __restrict__ slot)
 {
+    // A CTA takes tiles of 2048 consecutive particles: one global reservation per owner per tile (the cursors are few
+    // and hot), the warps then claim their runs from the CTA's share in shared memory.  Particles that were
+    // neighbours stay within one tile-sized run of the output, so paint and readout keep their cache locality.
+    constexpr int TILE = 2048;
+    __shared__ int h[64], cur[64];
     const unsigned lane = sq_lane();
-    const long long nit = (n + 31) / 32;
-    const long long w0 = ((long long) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long) gridDim.x * blockDim.x) >> 5;
-    for(long long wi = w0; wi < nit; wi += nw) {
-        const long long i = wi * 32 + lane;
-        const bool ok = i < n;
-        const int o = ok ? (int) owner[i] : -1 - (int) lane;
-        // one atomic per distinct owner per warp
-        const unsigned peers = __match_any_sync(SQ_FULL, o);
-        const int leader = __ffs(peers) - 1;
-        int base = 0;
-        if(ok && (int) lane == leader) base = atomicAdd(&cursor[o], __popc(peers));
-        base = __shfl_sync(SQ_FULL, base, leader);
-        if(ok) {
-            const int p = base + __popc(peers & sq_lanemask_lt());
-            send[p] = make_double4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], (double) mass[i]);
-            slot[i] = p;
+    const int warp = threadIdx.x >> 5;
+    const long long ntiles = (n + TILE - 1) / TILE;
+    for(long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long t0 = tile * TILE;
+        if(threadIdx.x < 64) h[threadIdx.x] = 0;
+        __syncthreads();
+        for(int k = threadIdx.x; k < TILE; k += 256)
+            if(t0 + k < n) atomicAdd(&h[owner[t0 + k]], 1);
+        __syncthreads();
+        if(threadIdx.x < 64) cur[threadIdx.x] = h[threadIdx.x] ? atomicAdd(&cursor[threadIdx.x], h[threadIdx.x]) : 0;
+        __syncthreads();
+        for(int k0 = warp * 32; k0 < TILE; k0 += 256) {
+            const long long i = t0 + k0 + lane;
+            const bool ok = i < n;
+            const int o = ok ? (int) owner[i] : -1 - (int) lane;
+            const unsigned peers = __match_any_sync(SQ_FULL, o);
+            const int leader = __ffs(peers) - 1;
+            int base = 0;
+            if(ok && (int) lane == leader) base = atomicAdd(&cur[o], __popc(peers));
+            base = __shfl_sync(SQ_FULL, base, leader);
+            if(ok) {
+                const int p = base + __popc(peers & sq_lanemask_lt());
+                send[p] = make_double4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], (double) mass[i]);
+                slot[i] = p;
+            }
         }
+        __syncthreads();
     }
 }
 
