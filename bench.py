@@ -432,12 +432,8 @@ def main():
     gpm_out, _k7 = pinned(np.zeros((n, 3))); gpot_out, _k8 = pinned(np.zeros(n))
 
     def e2e_step():
-        ctx.upload_particles(ppos, pmass)
-        ctx.set_old_accel(pa0, pg0)
-        ctx.ph_sort()
-        ctx.tree_build()
-        ctx.grav_short_tree(accel=acc_out, potential=pot_out)
-        ctx._check(ctx.L.sq_pm_force(ctx._ctx, gpm_out.ctypes.data_as(sq.api.ctypes.c_void_p), gpot_out.ctypes.data_as(sq.api.ctypes.c_void_p)))
+        # one call of the public API with host buffers: sq_gravity_step (uploads, sort, tree, PM, walk, downloads)
+        ctx.gravity_step(ppos, pmass, pa0, pg0, accel=acc_out, potential=pot_out, gravpm=gpm_out, pm_potential=gpot_out)
 
     e2e_step()
     barrier()

@@ -163,6 +163,16 @@ int sq_pm_force_device(sq_ctx * ctx);
 int sq_pm_paint(sq_ctx * ctx);
 int sq_pm_get_mesh(sq_ctx * ctx, double * mesh);
 
+/* ---- one PM step in one call ------------------------------------------------------------------ */
+/* What run() does on a PM step for gravity (libgadget/run.cpp:538 gravpm_force; run.cpp:556-563 force_tree_full +
+ * grav_short_tree): upload, PH sort, tree, PM force, short-range walk, download - with HOST buffers (pinned for overlap),
+ * the |a_old| inputs uploaded and the PM results downloaded on a second stream underneath the kernels.
+ * pos N x 3, mass N; fulltree / gravpm_old: N x 3 each or NULL (Part[i].FullTreeGravAccel, Part[i].GravPM of the
+ * previous step, gravshort2.hpp:111-121); accel N x 3 (x G), potential N or NULL (tree part);
+ * gravpm N x 3 and pm_potential N: PM outputs, both NULL = no PM force this step.  Results equal the separate calls'. */
+int sq_gravity_step(sq_ctx * ctx, const double * pos, const float * mass, int64_t n, const double * fulltree, const double * gravpm_old,
+                    double * accel, double * potential, double * gravpm, double * pm_potential, sq_walk_stats * stats);
+
 /* ---- multi-GPU: one rank per GPU (README.rst:67 of the reference), exchanges issued by the host over NCCL ------
  * Everything below takes DEVICE pointers and runs on the context's stream; the host layer (shenqi_b200/dist.py with
  * torch.distributed, or a C++ host with raw NCCL) issues the collectives between the calls.

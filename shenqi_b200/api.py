@@ -64,7 +64,7 @@ class Timings(ctypes.Structure):
 EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_set_walk_raw", "sq_sync", "sq_default_aos_layout",
            "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
-           "sq_pm_force", "sq_pm_force_device", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
+           "sq_pm_force", "sq_pm_force_device", "sq_gravity_step", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
            "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
            "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
            "sq_pm_slab_fft_inv", "sq_pm_slab_readout"]
@@ -210,6 +210,26 @@ class Context:
 
     def gravpm_force_device(self):
         self._check(self.L.sq_pm_force_device(self._ctx))
+
+    # ---- one PM step of run(): gravpm_force + force_tree_full + grav_short_tree (run.cpp:538-563), copies overlapped
+    def gravity_step(self, pos, mass, fulltree=None, gravpm_old=None, accel=None, potential=None, gravpm=None, pm_potential=None, pm=True):
+        """pos [N,3] f64, mass [N] f32 and the previous step's FullTreeGravAccel / GravPM [N,3] (or None) on the host
+        (pinned buffers overlap best).  Returns (accel x G, tree potential, gravpm, pm potential, WalkStats)."""
+        assert pos.dtype == np.float64 and pos.flags.c_contiguous and mass.dtype == np.float32 and mass.flags.c_contiguous
+        n = self.n = len(mass)
+        for a in (fulltree, gravpm_old):
+            assert a is None or (a.dtype == np.float64 and a.flags.c_contiguous and a.shape == (n, 3))
+        accel = np.zeros((n, 3)) if accel is None else accel
+        potential = np.zeros(n) if potential is None else potential
+        if pm:
+            gravpm = np.zeros((n, 3)) if gravpm is None else gravpm
+            pm_potential = np.zeros(n) if pm_potential is None else pm_potential
+        else:
+            gravpm = pm_potential = None
+        st = WalkStats()
+        self._check(self.L.sq_gravity_step(self._ctx, _p(pos), _p(mass), c_i64(n), _p(fulltree), _p(gravpm_old), _p(accel), _p(potential),
+                                           _p(gravpm), _p(pm_potential), ctypes.byref(st)))
+        return accel, potential, gravpm, pm_potential, st
 
     def pm_paint(self):
         self._check(self.L.sq_pm_paint(self._ctx))

@@ -111,9 +111,11 @@ void sq_ctx_destroy(sq_ctx * c)
                        &c->t_lk, &c->t_parent, &c->t_rot, &c->t_lvl, &c->t_counters, &c->tree_keys, &c->tree_order, &c->tree_pos, &c->tree_mass,
                        &c->active_sorted, &c->w_accel, &c->w_pot, &c->w_stats, &c->w_targets, &c->w_table, &c->w_out_accel, &c->w_out_pot,
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
-                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp};
+                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for(int i = 0; i < 4; i++) if(c->evx[i]) cudaEventDestroy(c->evx[i]);
+    if(c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if(c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -362,6 +364,67 @@ int sq_pm_force(sq_ctx * c, double * gravpm, double * potential)
         SQ_CUDA(cudaMemcpyAsync(potential, c->w_out_pot.p, sizeof(double) * (size_t) n, cudaMemcpyDeviceToHost, c->stream));
     }
     return sq_sync(c);
+}
+
+// One PM step of the reference's run loop in one call (run.cpp:538 gravpm_force, then run.cpp:556-563 force_tree_full +
+// grav_short_tree) with HOST buffers, the copies overlapped with the kernels on a second stream:
+//   copy stream:  H2D FullTreeGravAccel, GravPM (the |a_old| inputs)        | D2H PM accelerations + potential
+//   main stream:  H2D pos, mass -> keys, sort, tree, PM -> unpermute PM out | |a_old|, gather -> walk -> unpermute -> D2H
+// so that only the first upload and the last download are exposed.  Results equal the separate calls'.
+int sq_gravity_step(sq_ctx * c, const double * pos, const float * mass, int64_t n, const double * fulltree, const double * gravpm_old,
+                    double * accel, double * potential, double * gravpm, double * pm_potential, sq_walk_stats * stats)
+{
+    if(!c || !c->have_params) { sq_set_error("sq_gravity_step: call sq_set_params first"); return SQ_ERR_ARG; }
+    if(n > 0 && (!pos || !mass)) { sq_set_error("sq_gravity_step: null positions or masses"); return SQ_ERR_ARG; }
+    if(!c->copy_stream) {
+        SQ_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        for(int i = 0; i < 4; i++) SQ_CUDA(cudaEventCreateWithFlags(&c->evx[i], cudaEventDisableTiming));
+    }
+    SQ_TRY(sq_reset_particles(c, n));
+    SQ_CUDA(cudaMemcpyAsync(c->pos_in.p, pos, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(c->mass_in.p, mass, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, c->stream));
+    const bool have_old = fulltree || gravpm_old;
+    if(have_old) {
+        // behind the positions on the bus: the sort can start as soon as those are in
+        SQ_CUDA(cudaEventRecord(c->evx[3], c->stream));
+        SQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->evx[3], 0));
+        if(fulltree) { SQ_TRY(c->stage_a.reserve(sizeof(double) * 3 * (size_t) (n + 1))); SQ_CUDA(cudaMemcpyAsync(c->stage_a.p, fulltree, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->copy_stream)); }
+        if(gravpm_old) { SQ_TRY(c->stage_b.reserve(sizeof(double) * 3 * (size_t) (n + 1))); SQ_CUDA(cudaMemcpyAsync(c->stage_b.p, gravpm_old, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->copy_stream)); }
+        SQ_CUDA(cudaEventRecord(c->evx[0], c->copy_stream));
+    }
+    SQ_TRY(sq_ph_sort(c));
+    SQ_TRY(sq_tree_run(c, nullptr, 0, nullptr));
+    const bool want_pm = gravpm || pm_potential;
+    if(want_pm) {
+        SQ_TRY(sq_pm_run(c, false));
+        SQ_TRY(c->w_out_accel.reserve(sizeof(double) * 3 * (size_t) (n + 1)));
+        SQ_TRY(c->w_out_pot.reserve(sizeof(double) * (size_t) (n + 1)));
+        if(n > 0) {
+            if(gravpm) { sq_unpermute_kernel<3><<<api_grid(c, n), 256, 0, c->stream>>>(c->pm_out.as<double>(), 4, 1, c->perm.as<uint32_t>(), nullptr, n, c->w_out_accel.as<double>()); c->kernel_launches++; }
+            if(pm_potential) { sq_unpermute_kernel<1><<<api_grid(c, n), 256, 0, c->stream>>>(c->pm_out.as<double>(), 4, 0, c->perm.as<uint32_t>(), nullptr, n, c->w_out_pot.as<double>()); c->kernel_launches++; }
+        }
+        SQ_CUDA(cudaEventRecord(c->evx[1], c->stream));
+        SQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->evx[1], 0));
+        if(gravpm) SQ_CUDA(cudaMemcpyAsync(gravpm, c->w_out_accel.p, sizeof(double) * 3 * (size_t) n, cudaMemcpyDeviceToHost, c->copy_stream));
+        if(pm_potential) SQ_CUDA(cudaMemcpyAsync(pm_potential, c->w_out_pot.p, sizeof(double) * (size_t) n, cudaMemcpyDeviceToHost, c->copy_stream));
+        SQ_CUDA(cudaEventRecord(c->evx[2], c->copy_stream));
+    }
+    if(have_old) {
+        SQ_CUDA(cudaStreamWaitEvent(c->stream, c->evx[0], 0));
+        if(n > 0) {
+            sq_oldacc_kernel<<<api_grid(c, n), 256, 0, c->stream>>>(fulltree ? c->stage_a.as<double>() : nullptr, gravpm_old ? c->stage_b.as<double>() : nullptr, n, c->par.G, c->oldacc_in.as<double>());
+            c->kernel_launches++;
+            SQ_CUDA(cudaGetLastError());
+        }
+        SQ_TRY(sq_gather_run(c));
+    }
+    SQ_TRY(sq_walk_run(c, nullptr, 0, stats));
+    // the output staging buffers are shared with the PM download
+    if(want_pm) SQ_CUDA(cudaStreamWaitEvent(c->stream, c->evx[2], 0));
+    int rc = sq_download_accel(c, accel, potential);
+    cudaError_t e = cudaStreamSynchronize(c->copy_stream);
+    if(rc == SQ_OK && e != cudaSuccess) { sq_set_error("sq_gravity_step: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; }
+    return rc;
 }
 
 int sq_pm_paint(sq_ctx * c)

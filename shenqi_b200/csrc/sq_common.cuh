@@ -83,6 +83,8 @@ struct sq_ctx {
     int num_sms = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[16] = {};
+    cudaStream_t copy_stream = nullptr;   // sq_gravity_step: host copies overlapped with the kernels
+    cudaEvent_t evx[4] = {};
     sq_params par = {};
     bool have_params = false;
     sq_walk_raw raw = {};
@@ -93,7 +95,7 @@ struct sq_ctx {
 
     // ---- particles, upload order
     int64_t n = 0;
-    sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in, oldacc_tmp;
+    sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in, oldacc_tmp, stage_a, stage_b;
     bool have_types = false;
     // ---- particles, PH-sorted order
     sq_buf pos, mass, oldacc, keys, perm, rank;   // perm[sorted] = upload idx; rank[upload] = sorted pos

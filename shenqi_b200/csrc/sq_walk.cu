@@ -41,7 +41,15 @@
 #include "shortrange_table.h"
 #include <math.h>
 
+#ifndef SQ_EVAL_UNROLL
+#define SQ_EVAL_UNROLL 2
+#endif
+#ifndef SQ_PREFETCH
+#define SQ_PREFETCH 0
+#endif
+#ifndef WALK_WARPS
 #define WALK_WARPS 16
+#endif
 #define WALK_THREADS (WALK_WARPS * 32)
 #define STACK_CAP 384
 #define STACK_RESERVE 160   /* 7 siblings x 22 levels: room a depth-first descent can always need */
@@ -53,6 +61,7 @@
 #define TAB_BYTES (TAB_ROWS * TAB_COPIES * 8)
 #define SQ_EPS 4e-6f        /* relative slack on every FP32 threshold (>> 2^-24 rounding chains) */
 #define SQ_FAR 3.0e4f       /* padding entries: far beyond the table, zero mask */
+#define SQ_R2MAX 261888.f   /* 511.75^2: rows 511.. of the split table are zero */
 #define SQ_MAGIC 12582912.f /* 1.5 * 2^23: adding it rounds to the nearest integer, kept in the mantissa */
 
 struct sq_walk_par {
@@ -114,6 +123,13 @@ __device__ __forceinline__ float sq_rsqrt(float x)
 {
     float y;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__device__ __forceinline__ float sq_sqrt(float x)
+{
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
 
@@ -208,10 +224,11 @@ __device__ __forceinline__ int sq_list_slot(int p)
 // Every genuine entry is farther than the softening length from every target of the group (the others are in the
 // near list), padding entries are SQ_FAR away, so r2 > 0 and no softening or wrap test is needed.
 // Table (gravity.h:50-60): i = floor(r), linear interpolation, zero from row 511 on.
-//   !POT: row i = (force value at the middle of [i, i+1], slope), 16 copies of 8 bytes per 128-byte row
-//    POT: row i = (force middle, force slope, potential middle, potential slope), 8 copies of 16 bytes per row: a
+//   !POT: row i = (intercept, slope) of the line through table points i and i+1 (value = intercept + r * slope: no
+//         fractional part needed), 16 copies of 8 bytes per 128-byte row
+//    POT: row i = (force intercept, force slope, potential intercept, potential slope), 8 copies of 16 bytes per row: a
 //         128-bit LDS is served 8 lanes at a time, each lane of a quarter warp has its own copy (conflict-free)
-//   rows 511.. = 0: the clamp of r - 1/2 to 511 lands there, which is the reference's "outside the table"
+//   rows 511.. = 0: the clamp of r2 to 511.75^2 lands there, which is the reference's "outside the table"
 struct sq_acc2 { float2 x, y, z, p; };
 
 template <bool POT>
@@ -219,21 +236,20 @@ __device__ __forceinline__ void sq_eval_pair(float x0, float x1, float y0, float
                                              unsigned tabaddr, float2 ntx, float2 nty, float2 ntz, sq_acc2 & A)
 {
     const float2 dx = __fadd2_rn(make_float2(x0, x1), ntx), dy = __fadd2_rn(make_float2(y0, y1), nty), dz = __fadd2_rn(make_float2(z0, z1), ntz);
-    const float2 r2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+    float2 r2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+    // beyond the table every row is zero: clamping r2 (and with it rinv) only keeps the row index in range
+    r2.x = fminf(r2.x, SQ_R2MAX); r2.y = fminf(r2.y, SQ_R2MAX);
     const float2 rinv = make_float2(sq_rsqrt(r2.x), sq_rsqrt(r2.y));
-    // xq = r - 1/2; round-to-nearest of xq = floor(r); d = r - floor(r) - 1/2
-    float2 xq = __ffma2_rn(r2, rinv, make_float2(-0.5f, -0.5f));
-    xq.x = fminf(xq.x, 511.f); xq.y = fminf(xq.y, 511.f);
-    const float2 tt = __fadd2_rn(xq, make_float2(SQ_MAGIC, SQ_MAGIC));
-    const float2 fl = __fadd2_rn(tt, make_float2(-SQ_MAGIC, -SQ_MAGIC));
-    const float2 d = __ffma2_rn(fl, make_float2(-1.f, -1.f), xq);
+    // r for the interpolation; floor(r) straight into the mantissa by a round-down FMA onto 1.5 * 2^23
+    const float2 r = __fmul2_rn(r2, rinv);
+    const float2 tt = __ffma2_rd(r2, rinv, make_float2(SQ_MAGIC, SQ_MAGIC));
     const unsigned a0 = ((unsigned) __float_as_int(tt.x) << 7) + tabaddr, a1 = ((unsigned) __float_as_int(tt.y) << 7) + tabaddr;
     const float2 rinv2 = __fmul2_rn(rinv, rinv);
     if(POT) {
         const float4 e0 = sq_lds_f4(a0), e1 = sq_lds_f4(a1);
         // scalar FMAs here: pairing (e0.y, e1.y) etc. for the packed form costs more register moves than it saves
-        const float2 wf = make_float2(fmaf(d.x, e0.y, e0.x), fmaf(d.y, e1.y, e1.x));
-        const float2 wp = make_float2(fmaf(d.x, e0.w, e0.z), fmaf(d.y, e1.w, e1.z));
+        const float2 wf = make_float2(fmaf(r.x, e0.y, e0.x), fmaf(r.y, e1.y, e1.x));
+        const float2 wp = make_float2(fmaf(r.x, e0.w, e0.z), fmaf(r.y, e1.w, e1.z));
         const float2 mm = make_float2(on0 ? m0 : 0.f, on1 ? m1 : 0.f);
         const float2 mr = __fmul2_rn(mm, rinv);
         const float2 fac = __fmul2_rn(__fmul2_rn(mr, rinv2), wf);
@@ -243,7 +259,7 @@ __device__ __forceinline__ void sq_eval_pair(float x0, float x1, float y0, float
         A.p = __ffma2_rn(mr, wp, A.p);       // sign applied at the flush
     } else {
         const float2 w0 = sq_lds_f2(a0), w1 = sq_lds_f2(a1);
-        const float2 wf = make_float2(fmaf(d.x, w0.y, w0.x), fmaf(d.y, w1.y, w1.x));
+        const float2 wf = make_float2(fmaf(r.x, w0.y, w0.x), fmaf(r.y, w1.y, w1.x));
         const float2 mm = make_float2(on0 ? m0 : 0.f, on1 ? m1 : 0.f);
         const float2 fac = __fmul2_rn(__fmul2_rn(mm, rinv2), __fmul2_rn(rinv, wf));
         A.x = __ffma2_rn(dx, fac, A.x);
@@ -263,7 +279,8 @@ __device__ __forceinline__ void sq_eval_list(const sq_walk_warp_smem & W, int ns
     sq_acc2 A;
     A.x = A.y = A.z = A.p = make_float2(0.f, 0.f);
     const int nb = nsteps4 >> 2;
-    #pragma unroll 2
+    constexpr int eval_unroll = SQ_EVAL_UNROLL;
+    #pragma unroll eval_unroll
     for(int b = 0; b < nb; b++) {
         const uint4 w4 = mw4[b];
         const float4 x4 = X[b * S], y4 = Y[b * S], z4 = Z[b * S], m4 = M[b * S];
@@ -299,15 +316,14 @@ __device__ __forceinline__ void sq_near_pair(const float4 src, unsigned tabrow0,
     }
     // i = floor(r) clamped to the zero rows from 511 on
     const float fl = fminf(floorf(r), 511.f);
-    const float d = (r - fl) - 0.5f;
     const unsigned addr = tabrow0 + ((unsigned) (int) fl << 7);
     float wf, wp = 0.f;
     if(POT) {
         const float4 e = sq_lds_f4(addr);
-        wf = fmaf(d, e.y, e.x); wp = fmaf(d, e.w, e.z);
+        wf = fmaf(r, e.y, e.x); wp = fmaf(r, e.w, e.z);
     } else {
         const float2 w = sq_lds_f2(addr);
-        wf = fmaf(d, w.y, w.x);
+        wf = fmaf(r, w.y, w.x);
     }
     const float f = src.w * fac * wf;
     ax = fmaf(dx, f, ax);
@@ -411,6 +427,8 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             // errtol*|a_old| in the scaled system: M l^2 > r^4 a  <=>  M' l'^2 > r'^4 a / (munit s^2); BH mode: never
             if(P.relative) ta = (float) (P.errtol * toldacc[tidx] * (P.minv / (P.s * P.s)));
         }
+        // 1 / sqrt(errtol |a_old|) for the per-target relative criterion (0: never opens - Barnes-Hut mode, idle lanes)
+        const float rta = (valid && P.relative) ? sq_rsqrt(ta) : 0.f;
         // group bounding box in fixed point, relative to the first target (always valid)
         const unsigned ix0 = __shfl_sync(SQ_FULL, ix, 0), iy0 = __shfl_sync(SQ_FULL, iy, 0), iz0 = __shfl_sync(SQ_FULL, iz, 0);
         const int rx = valid ? (int) (ix - ix0) : 0, ry = valid ? (int) (iy - iy0) : 0, rz = valid ? (int) (iz - iz0) : 0;
@@ -623,7 +641,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                             t2_need = need;
                             t2_cm = make_float4(cmx, cmy, cmz, dr2);
                             t2_cl = make_float4(cx, cy, cz, de);
-                            t2_lm = make_float4(len, ml2, 0.f, relonly ? 1.f : 0.f);
+                            t2_lm = make_float4(len, sq_sqrt(ml2), 0.f, relonly ? 1.f : 0.f);
                         }
                     }
                 }
@@ -646,14 +664,15 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                         const bool act = idx < nf;
                         const int ii = act ? idx : nf - 1;
                         const float4 a = W.nrec[ii][0], c4 = W.nrec[ii][1], lm = W.nrec[ii][2];
-                        const float dr2 = a.w, de = c4.w, len = lm.x, ml2 = lm.y;
+                        const float dr2 = a.w, de = c4.w, len = lm.x;
                         const bool mine = act && ((__float_as_uint(lm.z) >> t) & 1u);
-                        const float mlA = ml2 * (1.f + SQ_EPS), mlB = ml2 * (1.f - SQ_EPS);
                         const float dx = a.x - tx, dy = a.y - ty, dz = a.z - tz;
                         const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                        const float r2l = fmaxf(r2 - dr2, 0.f), r2h = r2 + dr2;
                         bool k_lo = true, k_hi = true;
-                        bool o_lo = mlA > r2l * r2l * ta, o_hi = mlB > r2h * r2h * ta;
+                        // M l^2 > r^4 a  <=>  r^2 < sqrt(M l^2) / sqrt(a): one threshold per (node, target), its rounding
+                        // (sqrt, rsqrt.approx, products: < 1e-6) inside the relative slack, the coordinate error added
+                        const float th = lm.y * rta;
+                        bool o_lo = r2 < fmaf(th, 1.f + SQ_EPS, dr2), o_hi = r2 < fmaf(th, 1.f - SQ_EPS, -dr2);
                         if(lm.w == 0.f) {
                             const float eff = fmaf(0.5f, len, P.f_rcut), ins = 0.6f * len, bhq = len * len * P.f_invbh2;
                             const float rcA = P.f_rc2_hi + dr2, rcB = P.f_rc2_lo - dr2;
@@ -730,6 +749,16 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             __syncwarp();
             // ---- sources join the lists, 32 per round: round 0 = accepted nodes, then the leaf particles
             const int nrounds = 1 + ((tot_leaf + 31) >> 5);
+            // leaf particles are fetched one round ahead of their use (the load latency hides behind the previous round)
+            uint4 qn = make_uint4(0u, 0u, 0u, 0u);
+            unsigned mn = 0u;
+#if SQ_PREFETCH
+            if((int) lane < tot_leaf) {
+                const int lo = W.src[lane];
+                qn = ipart[(long long) W.s_first[lo] + (int) lane];
+                mn = W.s_mask[lo];
+            }
+#endif
             for(int rd = 0; rd < nrounds; rd++) {
                 bool v = false;
                 float4 e = nodeE;
@@ -738,14 +767,27 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                     if(!drain && anyacc == 0u) continue;
                     v = acc_mask != 0u;
                 } else {
-                    const int j = ((rd - 1) << 5) + (int) lane;
-                    if(j < tot_leaf) {
-                        const int lo = W.src[j];
-                        const uint4 q4 = ipart[(long long) W.s_first[lo] + j];
-                        e = make_float4((float) (int) (q4.x - gcix) * P.qs, (float) (int) (q4.y - gciy) * P.qs, (float) (int) (q4.z - gciz) * P.qs, __uint_as_float(q4.w));
-                        m = W.s_mask[lo];
-                        v = true;
+#if SQ_PREFETCH
+                    const uint4 q4 = qn;
+                    m = mn;
+                    v = ((rd - 1) << 5) + (int) lane < tot_leaf;
+                    const int jn = (rd << 5) + (int) lane;
+                    if(jn < tot_leaf) {
+                        const int lo = W.src[jn];
+                        qn = ipart[(long long) W.s_first[lo] + jn];
+                        mn = W.s_mask[lo];
                     }
+#else
+                    const int j = ((rd - 1) << 5) + (int) lane;
+                    v = j < tot_leaf;
+                    uint4 q4 = qn;
+                    if(v) {
+                        const int lo = W.src[j];
+                        q4 = ipart[(long long) W.s_first[lo] + j];
+                        m = W.s_mask[lo];
+                    }
+#endif
+                    if(v) e = make_float4((float) (int) (q4.x - gcix) * P.qs, (float) (int) (q4.y - gciy) * P.qs, (float) (int) (q4.z - gciz) * P.qs, __uint_as_float(q4.w));
                 }
                 // ---- near list
                 const bool near = v && (pairwrap || (fabsf(e.x) <= nhx && fabsf(e.y) <= nhy && fabsf(e.z) <= nhz));
@@ -779,7 +821,9 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                         sq_store_field<G>(W.mw, kk, 0u);
                     }
                     __syncwarp();
+#ifndef SQ_NOEVAL
                     sq_eval_list<POT, S>(W, nsteps4, tabaddr, tx, ty, tz, s, lanebit, ax, ay, az, ap);
+#endif
                     st_ent += nsteps4;
                     dax += (double) ax; day += (double) ay; daz += (double) az;
                     ax = ay = az = 0.f;
@@ -864,8 +908,8 @@ static const double h_sr_force[SQ_NGRAVTAB] = SQ_SHORTRANGE_FORCE_INIT;
 
 // GravShortTable, libgadget/gravshort-tree2.cpp:29-69: float tables; lookup gravity.h:50-60 (i = floor(r / dx),
 // linear interpolation between rows i and i+1, nothing from row 511 on).  Two device forms, TAB_ROWS float2 rows:
-//   force only:  row i = (force value at the middle of [i, i+1], slope), rows 511.. = (0, 0)
-//   force + pot: row i = (force[i], potential[i]), row 512 = (0, 0)
+//   force only:  row i = (intercept at r = 0, slope) of the line through points i and i+1, rows 511.. = (0, 0)
+//   force + pot: row i = (force intercept, force slope, potential intercept, potential slope), rows 511.. = 0
 static int sq_walk_table(sq_ctx * c)
 {
     float ft[SQ_NTAB], pt[SQ_NTAB];
@@ -888,8 +932,10 @@ static int sq_walk_table(sq_ctx * c)
     memset(&h, 0, sizeof(h));
     for(int i = 0; i + 1 < SQ_NTAB; i++) {
         const double sf = (double) ft[i + 1] - (double) ft[i], sp = (double) pt[i + 1] - (double) pt[i];
-        h.f[i] = make_float2((float) ((double) ft[i] + 0.5 * sf), (float) sf);
-        h.fp[i] = make_float4((float) ((double) ft[i] + 0.5 * sf), (float) sf, (float) ((double) pt[i] + 0.5 * sp), (float) sp);
+        // the line through rows i and i+1 as (intercept at r = 0, slope): value = intercept + r * slope for r in [i, i+1)
+        const float fsf = (float) sf, fsp = (float) sp;
+        h.f[i] = make_float2((float) ((double) ft[i] - (double) i * (double) fsf), fsf);
+        h.fp[i] = make_float4((float) ((double) ft[i] - (double) i * (double) fsf), fsf, (float) ((double) pt[i] - (double) i * (double) fsp), fsp);
     }
     SQ_TRY(c->w_table.reserve(sizeof(h)));
     SQ_CUDA(cudaMemcpyAsync(c->w_table.p, &h, sizeof(h), cudaMemcpyHostToDevice, c->stream));

@@ -381,3 +381,30 @@ def test_golden_reference_fixture(ctx):
     a1, _, st1 = ctx.grav_short_tree()
     assert st1.interactions == int(g["count_rel"])
     assert_accel_parity(a1, g["acc_rel"])
+
+
+def test_gravity_step_equals_separate_calls(ctx):
+    """sq_gravity_step (one call, copies overlapped on a second stream) returns what the separate entry points return:
+    the walk bit for bit (same kernels, same |a_old|), the PM force to the rounding of its atomics."""
+    box = 8.0; n = 20 ** 3; nmesh = 40
+    pos = random_clustered(n, box, 11); mass = (1.0 + 0.1 * np.random.default_rng(5).random(n)).astype(np.float32)
+    P = make_params(box, nmesh, n, TreeUseBH=1)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    a0, _, _ = ctx.grav_short_tree()
+    g0, _ = ctx.gravpm_force()
+    P.TreeUseBH = 0
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.set_old_accel(a0, g0); ctx.ph_sort(); ctx.tree_build()
+    a1, p1, st1 = ctx.grav_short_tree()
+    g1, q1 = ctx.gravpm_force()
+    a2, p2, g2, q2, st2 = ctx.gravity_step(pos, mass, a0, g0)
+    assert st2.interactions == st1.interactions
+    assert np.array_equal(a1, a2) and np.array_equal(p1, p2)
+    assert np.abs(g1 - g2).max() <= 1e-12 * np.abs(g1).max()
+    assert np.abs(q1 - q2).max() <= 1e-12 * np.abs(q1).max()
+    # without the |a_old| inputs and without PM: Barnes-Hut-free first call semantics (|a_old| = 0 opens everything it may)
+    a3, p3, g3, q3, st3 = ctx.gravity_step(pos, mass, pm=False)
+    ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
+    a4, p4, st4 = ctx.grav_short_tree()
+    assert g3 is None and q3 is None and st3.interactions == st4.interactions and np.array_equal(a3, a4)
