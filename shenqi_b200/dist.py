@@ -124,9 +124,12 @@ class Comm:
 class DistGravity:
     """One rank of the distributed force step.  `backend` does the local compute (CudaBackend or the tests' CPU one)."""
 
-    def __init__(self, backend, comm=None, profile=False):
+    def __init__(self, backend, comm=None, profile=False, comm_pm=None):
         self.B = backend
         self.comm = comm or Comm()
+        # a second communicator lets step() run the PM exchanges concurrently with the tree's (NCCL serialises the
+        # collectives of one communicator)
+        self.comm_pm = comm_pm
         self.rank, self.world = self.comm.rank, self.comm.world
         self.profile = profile and torch.cuda.is_available()
         self._marks = []
@@ -149,7 +152,7 @@ class DistGravity:
         return out
 
     # ------------------------------------------------------------------ short-range tree force
-    def tree_force(self, pos, mass, oldacc=None):
+    def tree_force(self, pos, mass, oldacc=None, after_sort=None, before_walk=None):
         """pos [n,3] f64, mass [n] f32: this rank's particles (it must own a consecutive Peano-Hilbert key range, ranks in
         key order); oldacc [n] = |FullTreeGravAccel + GravPM| / G for the relative criterion or None.
         Returns (accel [n,3] already x G, potential [n] or None, stats) in the caller's particle order."""
@@ -158,6 +161,9 @@ class DistGravity:
         self._mark("begin")
         srt = B.sort_local(pos, mass)
         self._mark("tree:local_sort")
+        self._sorted = srt          # PH-sorted copies of this rank's particles: pm_force(reuse_sorted=True) paints from them
+        if after_sort is not None:
+            after_sort()
         kmin = int(srt["keys"][0].item()) if n else 2 ** 63 - 1
         kmax = int(srt["keys"][-1].item()) if n else -1
         info = C.allgather_ints([n, kmin, kmax, int(srt["geo"])], B.device)
@@ -178,9 +184,10 @@ class DistGravity:
         self._mark("tree:global_build")
         first = sum(counts[: self.rank])
         perm = srt["perm"]
-        self._sorted = srt          # PH-sorted copies of this rank's particles: pm_force(reuse_sorted=True) paints from them
         if oldacc is not None:
             B.set_oldacc_range(first, oldacc[perm].contiguous())
+        if before_walk is not None:
+            before_walk()
         acc_s, pot_s, st = B.walk_range(first, n)
         self._mark("tree:walk")
         accel = torch.empty_like(acc_s)
@@ -193,12 +200,12 @@ class DistGravity:
         return accel, pot, st
 
     # ------------------------------------------------------------------ particle-mesh force
-    def pm_force(self, pos, mass, reuse_sorted=False):
+    def pm_force(self, pos, mass, reuse_sorted=False, comm=None):
         """Returns out4 [n,4] = (PM potential, fx, fy, fz) for this rank's particles, in their order.
         reuse_sorted: pos/mass are the arrays the last tree_force() was called with; the PH-sorted copies it left are
         routed instead (PH-adjacent particles share mesh cells, so paint and readout stay cache-coherent, as on the
         single-GPU path and as after the reference's slots_gc_sorted) and the result is put back in the caller's order."""
-        B, C = self.B, self.comm
+        B, C = self.B, (comm or self.comm)
         perm = None
         if reuse_sorted and getattr(self, "_sorted", None) is not None and self._sorted["pos"].shape[0] == pos.shape[0]:
             pos, mass, perm = self._sorted["pos"], self._sorted["mass"], self._sorted["perm"]
@@ -251,6 +258,43 @@ class DistGravity:
         return out
 
 
+    # ------------------------------------------------------------------ one PM step: both forces, chains overlapped
+    def step(self, pos, mass, oldacc=None, pm_host_out=None):
+        """tree_force + pm_force of one PM step (run.cpp:538-563).  With a backend that has a second stream and a second
+        communicator the PM chain (route, all-to-all, paint, FFTs, transposes, readout) runs on that stream from the
+        moment the local sort is done, underneath the tree chain (all-gather, global build); both join before the
+        walk, which wants every SM.  pm_host_out: pinned host tensor [n, 4]; the PM result is also copied there on the
+        second stream, underneath the walk.  Returns (accel, potential, out4, stats) like the two calls."""
+        B = self.B
+        side = getattr(B, "pm_stream", None)
+        if side is None or self.comm_pm is None or self.profile or self.world == 1:
+            a, p, st = self.tree_force(pos, mass, oldacc)
+            o = self.pm_force(pos, mass, reuse_sorted=True)
+            if pm_host_out is not None:
+                pm_host_out.copy_(o, non_blocking=True)
+            return a, p, o, st
+        main = torch.cuda.current_stream(B.device)
+        box = {}
+
+        def fork():
+            ev = torch.cuda.Event()
+            ev.record(main)
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                box["out"] = self.pm_force(pos, mass, reuse_sorted=True, comm=self.comm_pm)
+                box["done"] = torch.cuda.Event()
+                box["done"].record(side)
+                if pm_host_out is not None:
+                    pm_host_out.copy_(box["out"], non_blocking=True)      # a DMA: runs while the walk owns the SMs
+
+        def join():
+            main.wait_event(box["done"])
+            box["out"].record_stream(main)
+
+        a, p, st = self.tree_force(pos, mass, oldacc, after_sort=fork, before_walk=join)
+        return a, p, box["out"], st
+
+
 class CudaBackend:
     """Local compute of DistGravity on one B200 through the C ABI (device pointers of torch tensors).
     Two library contexts: `loc` sorts and routes this rank's own particles, `glob` holds the all-gathered set, the tree
@@ -265,6 +309,10 @@ class CudaBackend:
         self.glob = api.Context(self.device.index)
         stream = torch.cuda.current_stream(self.device).cuda_stream
         self.loc.set_stream(stream); self.glob.set_stream(stream)
+        # PM kernels have their own context; DistGravity.step() moves it to `pm_stream` while the tree chain runs
+        self.pmc = api.Context(self.device.index)
+        self.pmc.set_stream(stream)
+        self.pm_stream = torch.cuda.Stream(self.device)
         self.set_params(params)
         self._slabs = {}
 
@@ -273,9 +321,10 @@ class CudaBackend:
         self.nmesh = params.Nmesh
         self.loc.set_params(params)
         self.glob.set_params(params)
+        self.pmc.set_params(params)
 
     def close(self):
-        self.loc.close(); self.glob.close()
+        self.loc.close(); self.glob.close(); self.pmc.close()
 
     def _wrap(self, ptr, shape, dtype):
         """torch view of library-owned device memory (valid until the library reallocates it)"""
@@ -329,16 +378,24 @@ class CudaBackend:
         return acc, pot, st
 
     # ---- PM side
+    def _pm(self):
+        """the PM context, on whatever stream is current (cuFFT plans follow the stream)"""
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        if st != getattr(self, "_pm_bound", None):
+            self.pmc.set_stream(st)
+            self._pm_bound = st
+        return self.pmc
+
     def route(self, pos, mass, P):
         n = pos.shape[0]
         send4 = torch.empty((n, 4), dtype=torch.float64, device=self.device)
         slot = torch.empty(n, dtype=torch.int32, device=self.device)
-        counts = self.loc.pm_slab_route(pos.data_ptr(), mass.data_ptr(), n, P, send4.data_ptr(), slot.data_ptr())
+        counts = self._pm().pm_slab_route(pos.data_ptr(), mass.data_ptr(), n, P, send4.data_ptr(), slot.data_ptr())
         return send4, slot, counts
 
     def unroute(self, back4, slot):
         out = torch.empty_like(back4)
-        self.loc.pm_slab_unroute(back4.data_ptr(), slot.data_ptr(), slot.shape[0], out.data_ptr())
+        self._pm().pm_slab_unroute(back4.data_ptr(), slot.data_ptr(), slot.shape[0], out.data_ptr())
         return out
 
     def new_slab(self, P, f):
@@ -355,7 +412,7 @@ class CudaBackend:
     def slab_paint(self, part4, rank, P):
         N = self.nmesh
         slab = self._buf("slab0", (N // P + 1, N, N), torch.float64)
-        self.loc.pm_slab_paint(part4.data_ptr(), part4.shape[0], rank, P, slab.data_ptr())
+        self._pm().pm_slab_paint(part4.data_ptr(), part4.shape[0], rank, P, slab.data_ptr())
         return slab
 
     def fft_fwd(self, slab, P):
@@ -363,39 +420,39 @@ class CudaBackend:
         nxl, nzh = N // P, N // 2 + 1
         work = self._buf("work", (nxl, N, nzh), torch.complex128)
         packed = self._buf("packed", (P, nxl, N // P, nzh), torch.complex128)
-        self.loc.pm_slab_fft_fwd(slab.data_ptr(), P, work.data_ptr(), packed.data_ptr())
+        self._pm().pm_slab_fft_fwd(slab.data_ptr(), P, work.data_ptr(), packed.data_ptr())
         return packed
 
     def fft_x(self, data, P, inverse):
         assert data.is_contiguous()
-        self.loc.pm_slab_fft_x(data.data_ptr(), P, inverse)
+        self._pm().pm_slab_fft_x(data.data_ptr(), P, inverse)
 
     def transfer(self, rho, rank, P):
         N = self.nmesh
         out4 = self._buf("out4", (4, N, N // P, N // 2 + 1), torch.complex128)
-        self.loc.pm_slab_transfer(rho.data_ptr(), rank, P, out4.data_ptr())
+        self._pm().pm_slab_transfer(rho.data_ptr(), rank, P, out4.data_ptr())
         return out4
 
     def transfer_phi(self, rho, rank, P):
         N = self.nmesh
         phik = self._buf("phik", (N, N // P, N // 2 + 1), torch.complex128)
-        self.loc.pm_slab_transfer_phi(rho.data_ptr(), rank, P, phik.data_ptr())
+        self._pm().pm_slab_transfer_phi(rho.data_ptr(), rank, P, phik.data_ptr())
         return phik
 
     def gradient(self, slab, lo2, hi3, P):
         N = self.nmesh
         ext = self._buf("ext", (N // P + 5, N, N), torch.float64)
         f = [self.new_slab(P, k) for k in (1, 2, 3)]
-        self.loc.pm_slab_gradient(slab.data_ptr(), lo2.contiguous().data_ptr(), hi3.contiguous().data_ptr(), P, ext.data_ptr(),
+        self._pm().pm_slab_gradient(slab.data_ptr(), lo2.contiguous().data_ptr(), hi3.contiguous().data_ptr(), P, ext.data_ptr(),
                                   f[0].data_ptr(), f[1].data_ptr(), f[2].data_ptr())
         return [slab] + f
 
     def fft_inv(self, recv, P, slab):
         N = self.nmesh
         work = self._buf("work", (N // P, N, N // 2 + 1), torch.complex128)
-        self.loc.pm_slab_fft_inv(recv.data_ptr(), P, work.data_ptr(), slab.data_ptr())
+        self._pm().pm_slab_fft_inv(recv.data_ptr(), P, work.data_ptr(), slab.data_ptr())
 
     def readout(self, part4, rank, P, slabs):
         out = torch.empty_like(part4)
-        self.loc.pm_slab_readout(part4.data_ptr(), part4.shape[0], rank, P, [s.data_ptr() for s in slabs], out.data_ptr())
+        self._pm().pm_slab_readout(part4.data_ptr(), part4.shape[0], rank, P, [s.data_ptr() for s in slabs], out.data_ptr())
         return out

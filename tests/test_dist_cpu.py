@@ -54,6 +54,11 @@ def _worker(rank, world, port, q):
         # the PM step from the PH-sorted copies tree_force left: same particles, other routing order
         out4s = D.pm_force(lp, lm, reuse_sorted=True).numpy()
         assert np.abs(out4s - out4.numpy()).max() <= 1e-12 * np.abs(out4.numpy()).max()
+        # step() = both forces of one PM step; without a second stream (CPU backend) it is the two calls in sequence,
+        # with a second communicator for the PM exchanges it must give the same numbers
+        a2, p2, o2, tot2 = DistGravity(OracleBackend(par), Comm(), comm_pm=Comm(dist.new_group())).step(lp, lm)
+        assert tot2 == tot and torch.equal(a2, acc) and torch.equal(p2, pot)
+        assert np.abs(o2.numpy() - out4s).max() <= 1e-12 * np.abs(out4s).max()
         res = {
             "tree_acc": float(np.abs(acc.numpy() - oacc[inv[mine]]).max()),
             "tree_pot": float(np.abs(pot.numpy() - opot[inv[mine]]).max()),

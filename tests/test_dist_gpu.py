@@ -78,6 +78,13 @@ def _worker(rank, world, port, q):
         out4 = D.pm_force(dpos, dmass)
         tot = torch.tensor([st.interactions], device="cuda"); dist.all_reduce(tot)
         res = {"a": a.cpu().numpy(), "p": p.cpu().numpy(), "out4": out4.cpu().numpy(), "mine": mine, "tot": int(tot.item())}
+        # the overlapped step (PM chain on a second stream and communicator) must return the same numbers
+        D2 = DistGravity(B, Comm(), comm_pm=Comm(dist.new_group()))
+        for _ in range(2):
+            a2, p2, o2, st2 = D2.step(dpos, dmass)
+        torch.cuda.synchronize()
+        res.update(step_same_tree=bool(torch.equal(a2, a) and torch.equal(p2, p) and st2.interactions == st.interactions),
+                   step_pm_err=float((o2 - out4).abs().max() / out4.abs().max()))
         if rank == 0:
             res.update(acc=acc, pot=pot, nint=nint, gpm=gpm, ppot=ppot)
         q.put((rank, res))
@@ -105,6 +112,8 @@ def test_world2_nccl_equals_single_gpu():
         assert p.exitcode == 0
     ref = out[0]
     assert ref["tot"] == ref["nint"]
+    for r in range(world):
+        assert out[r]["step_same_tree"] and out[r]["step_pm_err"] <= 1e-12, (r, out[r]["step_same_tree"], out[r]["step_pm_err"])
     for r in range(world):
         m = out[r]["mine"]
         # every opening decision is the single-GPU one (interaction totals equal); the FP32 pair sums differ by rounding
