@@ -63,7 +63,7 @@ struct sq_buf {
 //   lk[i]  = {first, count, sibling, info}        16 B   (one 128-bit load)
 //     internal node: first = index of first child, count = number of children (contiguous, Morton order)
 //     leaf:          first = first particle (tree order), count = particles (<= 8)
-//     info = level | type << 8 | toplevel << 12 | internaltop << 13 | dependslocal << 14 | octant << 16
+//     info = level | type << 8 | toplevel << 12 | internaltop << 13 | dependslocal << 14 | octant << 16 | child octant mask << 24
 struct sq_tree_dev {
     double4 * cm = nullptr;
     double4 * cl = nullptr;
@@ -77,6 +77,7 @@ struct sq_tree_dev {
 #define SQ_INFO_ITOP(i) (((i) >> 13) & 1)
 #define SQ_INFO_LOCAL(i) (((i) >> 14) & 1)
 #define SQ_INFO_OCT(i) (((i) >> 16) & 7)
+#define SQ_INFO_CHILDMASK(i) (((unsigned) (i)) >> 24)   /* internal nodes: octants (x + 2y + 4z) that have a child; children are stored in this order */
 
 struct sq_ctx {
     int device = 0;

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
                     rot[c] = rot1[rotn * 8 + pix];
                 }
                 if(sl == 0)
-                    lk[i] = make_int4(tbase, nchild, link.z, link.w | (1 << 8));
+                    lk[i] = make_int4(tbase, nchild, link.z, link.w | (1 << 8) | (int) (mm << 24));   // + which octants exist
             }
         }
     }

@@ -51,11 +51,17 @@
 #define WALK_WARPS 16
 #endif
 #define WALK_THREADS (WALK_WARPS * 32)
+#ifndef STACK_CAP
 #define STACK_CAP 384
+#endif
 #define STACK_RESERVE 160   /* 7 siblings x 22 levels: room a depth-first descent can always need */
+#ifndef LIST_CAP
 #define LIST_CAP 128        /* interaction-list entries per flush */
+#endif
 #define LIST_PAD 16         /* room to pad the last steps (4 steps x S entries) */
+#ifndef NEAR_CAP
 #define NEAR_CAP 32
+#endif
 #define TAB_ROWS (SQ_NTAB + 1)
 #define TAB_COPIES 16
 #define TAB_BYTES (TAB_ROWS * TAB_COPIES * 8)
@@ -78,6 +84,9 @@ struct sq_walk_par {
     // exact keep test per tree level: |centre - x| <= e_in certainly inside the keep box, > e_out certainly outside
     // (fixed-point quanta); e_in < 0: -1 = every target is inside (Rcut + len/2 >= Box/2), -2 = use the FP32/FP64 tiers
     int e_in[SQ_MAXLEVEL + 3], e_out[SQ_MAXLEVEL + 3];
+    // children of a level-L node sit at centre +- q4[L] (len / 4 in quanta, rounded down); e_child[L] = half size of a
+    // child's keep box + slack (e_out[L + 1] + 8), or -1 when no child can be ruled out at push time
+    int q4[SQ_MAXLEVEL + 3], e_child[SQ_MAXLEVEL + 3];
 };
 
 struct sq_walk_warp_smem {
@@ -94,7 +103,8 @@ struct sq_walk_warp_smem {
     unsigned s_mask[32];
     int sx[3][32];                     // target coordinates per axis, sorted (fixed point, relative to the first target)
     unsigned pmk[3][36];               // pmk[a][k] = targets among the k smallest coordinates of axis a
-    unsigned char scnt[STACK_CAP];     // child count of stack entry i
+    unsigned char scnt[STACK_CAP];     // stack entry i: octants of its children that survived the push-time box test
+    unsigned char scm[STACK_CAP];      // stack entry i: octants that have a child (child k = k-th set bit)
     unsigned char src[256];            // slot j of an expansion (children of popped entries / particles of opened leaves) -> lane that owns it
 };
 
@@ -496,7 +506,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         if(lane == 0) {
             // the root is "the only child" of a virtual entry reached by every target
             W.stack[0] = make_int2(0, nt >= 32 ? (int) 0xffffffffu : (int) ((1u << nt) - 1u));
-            W.scnt[0] = 1;
+            W.scnt[0] = 1; W.scm[0] = 1;
         }
         __syncwarp();
 
@@ -506,6 +516,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             unsigned acc_mask = 0, open_mask = 0;
             int4 L = make_int4(0, 0, -1, 0);
             float4 nodeE = make_float4(0.f, 0.f, 0.f, 0.f);
+            uint4 nodeC = make_uint4(0u, 0u, 0u, 0u);
             int node = 0;
             unsigned t2_need = 0, risky_exact = 0;
             bool relonly = false;
@@ -513,7 +524,8 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             if(!drain) {
                 // pop the entries whose children fit the 32 lanes (always at least one: <= 8 children); every child can
                 // push one entry, so wide pops only while a depth-first descent (<= 7 entries per level) still fits
-                const int cnt = (int) lane < top ? (int) W.scnt[top - 1 - lane] : 64;
+                const unsigned sv = (int) lane < top ? (unsigned) W.scnt[top - 1 - lane] : 0u;
+                const int cnt = (int) lane < top ? __popc(sv) : 64;
                 int tot_all;
                 const int exc = sq_warp_excl_scan(cnt, tot_all);
                 int npop = __popc(__ballot_sync(SQ_FULL, exc + cnt <= 32));
@@ -521,9 +533,16 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 const int nchild = __shfl_sync(SQ_FULL, exc + cnt, npop - 1);
                 if((int) lane < npop) {
                     const int2 e = W.stack[top - 1 - lane];
-                    W.s_first[lane] = e.x - exc;
+                    const unsigned cmk = W.scm[top - 1 - lane];
+                    W.s_first[lane] = e.x;
                     W.s_mask[lane] = (unsigned) e.y;
-                    for(int k = 0; k < cnt; k++) W.src[exc + k] = (unsigned char) lane;
+                    unsigned b = sv;
+                    for(int k = 0; k < cnt; k++) {
+                        const unsigned ob = b & (0u - b);          // lowest surviving octant
+                        b ^= ob;
+                        W.src[exc + k] = (unsigned char) lane;
+                        W.src[32 + exc + k] = (unsigned char) __popc(cmk & (ob - 1u));   // its position among the children
+                    }
                 }
                 top -= npop;
                 __syncwarp();
@@ -531,13 +550,14 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 unsigned mask = 0;
                 if(have) {
                     const int o = W.src[lane];
-                    node = W.s_first[o] + (int) lane;
+                    node = W.s_first[o] + (int) W.src[32 + lane];
                     mask = W.s_mask[o];
                 }
                 __syncwarp();
                 if(have) {
                     L = lk[node];
                     const uint4 A = icm[node], B = icl[node];
+                    nodeC = B;
                     st_tst++;
                     const float cmx = (float) (int) (A.x - gcix) * P.qs, cmy = (float) (int) (A.y - gciy) * P.qs, cmz = (float) (int) (A.z - gciz) * P.qs;
                     const float cx = (float) (int) (B.x - gcix) * P.qs, cy = (float) (int) (B.y - gciy) * P.qs, cz = (float) (int) (B.z - gciz) * P.qs;
@@ -723,12 +743,34 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             const int type = SQ_INFO_TYPE(L.w);
             // ---- opened internal nodes -> push children with the open mask (pseudo nodes are skipped: gravshort2.hpp:305-314)
             {
-                const bool pushes = open_mask && type == 1;
+                const unsigned cmk = SQ_INFO_CHILDMASK(L.w);
+                unsigned sv = cmk;
+                if(open_mask && type == 1 && intkeep) {
+                    // children whose keep box (Rcut + len/2 around the cell centre, gravshort2.hpp:160) misses the whole
+                    // group are dropped here, before anyone loads them: the reference would discard them for every
+                    // target.  Child centres = this centre +- len/4, in quanta to within 2; e_child carries the slack.
+                    const int lvl = SQ_INFO_LEVEL(L.w);
+                    const int ec = P.e_child[lvl], q = P.q4[lvl];
+                    if(ec >= 0) {
+                        const int c0 = (int) (nodeC.x - ix0), c1 = (int) (nodeC.y - iy0), c2 = (int) (nodeC.z - iz0);
+                        const int x0 = sq_sub_sat(c0, q), x1 = sq_add_sat(c0, q), y0 = sq_sub_sat(c1, q), y1 = sq_add_sat(c1, q), z0 = sq_sub_sat(c2, q), z1 = sq_add_sat(c2, q);
+                        unsigned okx = 0, oky = 0, okz = 0;
+                        if(!(sq_sub_sat(x0, ec) > mxx || sq_add_sat(x0, ec) < mnx)) okx |= 0x55u;
+                        if(!(sq_sub_sat(x1, ec) > mxx || sq_add_sat(x1, ec) < mnx)) okx |= 0xAAu;
+                        if(!(sq_sub_sat(y0, ec) > mxy || sq_add_sat(y0, ec) < mny)) oky |= 0x33u;
+                        if(!(sq_sub_sat(y1, ec) > mxy || sq_add_sat(y1, ec) < mny)) oky |= 0xCCu;
+                        if(!(sq_sub_sat(z0, ec) > mxz || sq_add_sat(z0, ec) < mnz)) okz |= 0x0Fu;
+                        if(!(sq_sub_sat(z1, ec) > mxz || sq_add_sat(z1, ec) < mnz)) okz |= 0xF0u;
+                        sv &= okx & oky & okz;
+                    }
+                }
+                const bool pushes = open_mask && type == 1 && sv != 0u;
                 const unsigned bp = __ballot_sync(SQ_FULL, pushes);
                 if(pushes) {
                     const int p = top + __popc(bp & sq_lanemask_lt());
                     W.stack[p] = make_int2(L.x, (int) open_mask);
-                    W.scnt[p] = (unsigned char) L.y;
+                    W.scnt[p] = (unsigned char) sv;
+                    W.scm[p] = (unsigned char) cmk;
                 }
                 top += __popc(bp);
             }
@@ -1025,6 +1067,12 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
         if(effq >= 2147483648.0 + 8.0) { P.e_in[L] = -1; P.e_out[L] = -1; }              // >= Box/2: |NEAREST()| never exceeds it
         else if(effq > 2147483648.0 - 8.0 || effq < 8.0) { P.e_in[L] = -2; P.e_out[L] = -2; }
         else { P.e_in[L] = (int) floor(effq) - 2; P.e_out[L] = (int) ceil(effq) + 2; }
+    }
+    for(int L = 0; L < SQ_MAXLEVEL + 3; L++) {
+        const double q = 0.25 * ldexp(1.001 * par.BoxSize, -L) * P.qinv;
+        const bool ok = L + 1 < SQ_MAXLEVEL + 3 && P.e_out[L + 1] >= 0 && P.e_out[L + 1] < (1 << 30) - 16 && q < (double) (1 << 30);
+        P.q4[L] = ok ? (int) floor(q) : 0;
+        P.e_child[L] = ok ? P.e_out[L + 1] + 8 : -1;
     }
 
     const int64_t n = c->n;
