@@ -28,7 +28,7 @@ import numpy as np
 FLOP_PER_INTERACTION = 28
 # dram__bytes_read.sum + dram__bytes_write.sum of one sq_walk_kernel launch on the N=1 workload (256^3), from the
 # `ncu --set full` capture summarised in profiles/r1_walk_v5c_sections.txt (1.663 GB + 0.526 GB); None for other sizes
-WALK_DRAM_TRAFFIC_256 = 2.189e9
+WALK_DRAM_TRAFFIC_256 = 2.178e9     # ncu --set full, walk v6 at 256^3: dram__bytes_read.sum 1.652 GB + dram__bytes_write.sum 0.526 GB (profiles/r1_walk_v6_sections.txt)
 DIST_NGRID = {2: 320, 4: 400, 8: 512}   # ~256^3 particles per GPU (weak scaling), Nmesh = 2 Ngrid divisible by the ranks
 
 
@@ -418,10 +418,12 @@ def main():
     nm3 = float(nmesh) ** 3
     bytes_model = {"keys": 32.0 * n, "sort": 8 * 32.0 * n, "gather": 2 * 36.0 * n + 8.0 * n,
                    "tree_build": 8.0 * n + 28.0 * n + 80.0 * numnodes, "pm_paint": 28.0 * n + 16.0 * nm3,
-                   "pm_readout": 24.0 * n + 32.0 * n + 4 * 8.0 * nm3, "pm_transfer": 80.0 * (nm3 / 2)}
+                   "pm_readout": 24.0 * n + 32.0 * n + 4 * 8.0 * nm3,
+                   "pm_transfer": 32.0 * (nm3 / 2),                      # rho_k -> phi_k in place: 16 B read + 16 B written per mode
+                   "pm_fft_gradient": (16.0 + 16.0 + 32.0) * nm3}          # D2Z + Z2D (8 B in, 8 B out each, ideal) + 4-point gradient (8 B in, 24 B out)
     hbm = {}
     for k, ms_key in (("keys", "keys_ms"), ("sort", "sort_ms"), ("gather", "gather_ms"), ("tree_build", "tree_build_ms"),
-                      ("pm_paint", "pm_paint_ms"), ("pm_readout", "pm_readout_ms"), ("pm_transfer", "pm_transfer_ms")):
+                      ("pm_paint", "pm_paint_ms"), ("pm_readout", "pm_readout_ms"), ("pm_transfer", "pm_transfer_ms"), ("pm_fft_gradient", "pm_fft_ms")):
         if stage_ms[ms_key] > 0:
             gbs = bytes_model[k] / (stage_ms[ms_key] * 1e-3) / 1e9
             hbm[k] = {"achieved_gbs": gbs, "frac": gbs / hbm_peak, "ms": stage_ms[ms_key]}

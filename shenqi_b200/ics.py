@@ -81,3 +81,40 @@ def zeldovich_torch(ngrid, box, device, rms_disp=0.2, seed=181170, index=-1.0):
 
 def rho0():
     return OMEGA0 * 3 * HUBBLE ** 2 / (8 * np.pi * G_INTERNAL)
+
+
+def clustered(ngrid, box, halo_fraction=0.5, nhalo=None, seed=181170):
+    """Deterministic stand-in for evolved (z = 0-like) particle loads: the Zel'dovich
+    load above with `halo_fraction` of the particles moved into Hernquist-profile halos (rho ~ 1 / (r (r + a)^3)) whose
+    masses follow dn/dM ~ M^-1.9 and whose centres are drawn from the particles themselves (so halos sit in the
+    overdense regions).  Deep trees, long interaction lists, strong load imbalance between groups: the stress case of
+    the walk.  Returns pos, mass, ids like zeldovich()."""
+    pos, mass, ids = zeldovich(ngrid, box, rms_disp=0.6, seed=seed)
+    n = len(pos)
+    rng = np.random.default_rng(seed + 1)
+    nmove = int(halo_fraction * n)
+    if nmove == 0:
+        return pos, mass, ids
+    nhalo = nhalo or max(8, n // 4096)
+    u = rng.random(nhalo)
+    mmin, mmax, al = 32.0, max(64.0, 0.02 * n), -0.9            # cumulative of M^-1.9
+    hm = (mmin ** al + u * (mmax ** al - mmin ** al)) ** (1.0 / al)
+    cnt = np.maximum(1, np.floor(hm * nmove / hm.sum())).astype(np.int64)
+    cnt[-1] += nmove - cnt.sum()
+    if cnt[-1] < 1:
+        cnt[-1] = 1
+    nmove = int(cnt.sum())
+    moved = rng.choice(n, nmove, replace=False)
+    centres = pos[rng.choice(n, nhalo, replace=False)]
+    spacing = box / ngrid
+    a = 0.35 * spacing * np.cbrt(cnt.astype(np.float64))        # scale radius ~ virial radius / 5 at 200 x mean density
+    hid = np.repeat(np.arange(nhalo), cnt)
+    q = rng.random(nmove) * 0.98                                  # enclosed-mass fraction, truncated at ~100 a
+    r = a[hid] * np.sqrt(q) / (1.0 - np.sqrt(q))
+    mu = 2.0 * rng.random(nmove) - 1.0
+    ph = 2.0 * np.pi * rng.random(nmove)
+    st = np.sqrt(1.0 - mu * mu)
+    pos[moved] = centres[hid] + r[:, None] * np.stack([st * np.cos(ph), st * np.sin(ph), mu], 1)
+    np.mod(pos, box, out=pos)
+    pos[pos >= box] = 0.0
+    return pos, mass, ids

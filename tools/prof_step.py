@@ -12,8 +12,12 @@ ap.add_argument("--ngrid", type=int, default=128)
 ap.add_argument("--steps", type=int, default=1)
 ap.add_argument("--group-width", type=int, default=32)
 ap.add_argument("--no-pm", action="store_true")
+ap.add_argument("--clustered", type=float, default=0.0, help="fraction of the particles in Hernquist halos (shenqi_b200.ics.clustered)")
 a = ap.parse_args()
 pos, mass, par = bench.workload(a.ngrid, 2 * a.ngrid)
+if a.clustered > 0:
+    from shenqi_b200.ics import clustered
+    pos, mass, _ = clustered(a.ngrid, par["BoxSize"], a.clustered)
 ctx = sq.Context(0)
 ctx.set_group_width(a.group_width)
 P = sq.Params.defaults(par["BoxSize"], 2 * a.ngrid, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
