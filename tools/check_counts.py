@@ -11,8 +11,12 @@ import shenqi_b200 as sq
 ap = argparse.ArgumentParser()
 ap.add_argument("--ngrid", type=int, default=64)
 ap.add_argument("--with-pm", action="store_true", help="|a_old| from tree + PM (as bench.py / prof_step.py) instead of the tree alone")
+ap.add_argument("--clustered", type=float, default=0.0, help="fraction of the particles in Hernquist halos (shenqi_b200.ics.clustered)")
 a = ap.parse_args()
 pos, mass, par = bench.workload(a.ngrid, 2 * a.ngrid)
+if a.clustered > 0:
+    from shenqi_b200.ics import clustered
+    pos, mass, _ = clustered(a.ngrid, par["BoxSize"], a.clustered)
 n = len(pos); box = par["BoxSize"]
 ctx = sq.Context(0)
 P = sq.Params.defaults(box, 2 * a.ngrid, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
