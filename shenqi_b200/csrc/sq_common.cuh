@@ -108,6 +108,7 @@ struct sq_ctx {
     sq_buf t_cm, t_cl, t_lk, t_parent, t_rot, t_lvl, t_counters;
     sq_buf tree_keys, tree_order, tree_pos, tree_mass;   // only when the tree order differs from particle order
     sq_buf active_sorted;            // sorted positions of the active set the tree was built from
+    sq_buf act_tmp;                  // the caller's active list on the device
     int64_t tree_np = 0;             // particles in the tree
     int64_t tree_maxnodes = 0, tree_numnodes = 0;
     int tree_maxlevel = 0;

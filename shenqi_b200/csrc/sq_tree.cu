@@ -243,7 +243,7 @@ static int grid_for(const sq_ctx * c, int64_t n, int threads, int per_sm)
 int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_buf * out, int64_t * count)
 {
     const int64_t n = c->n;
-    sq_buf d_act;
+    sq_buf & d_act = c->act_tmp;     // kept across calls: hierarchical sub-steps come by the thousand
     SQ_TRY(c->flag_tmp.reserve(sizeof(uint32_t) * (size_t) (n + 4)));
     SQ_TRY(out->reserve(sizeof(uint32_t) * (size_t) (nactive + 1)));
     SQ_TRY(d_act.reserve(sizeof(int32_t) * (size_t) (nactive + 1)));
@@ -268,7 +268,6 @@ int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_
         if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if(e != cudaSuccess) { sq_set_error("active list compaction: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
     } while(0);
-    d_act.release();
     *count = h_total;
     return rc;
 }
