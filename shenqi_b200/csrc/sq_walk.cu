@@ -524,34 +524,36 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             if(!drain) {
                 // pop the entries whose children fit the 32 lanes (always at least one: <= 8 children); every child can
                 // push one entry, so wide pops only while a depth-first descent (<= 7 entries per level) still fits
-                const unsigned sv = (int) lane < top ? (unsigned) W.scnt[top - 1 - lane] : 0u;
-                const int cnt = (int) lane < top ? __popc(sv) : 64;
+                const bool ontop = (int) lane < top;
+                const int2 ent = ontop ? W.stack[top - 1 - lane] : make_int2(0, 0);
+                const unsigned sv = ontop ? (unsigned) W.scnt[top - 1 - lane] : 0u;
+                const unsigned cmk = ontop ? (unsigned) W.scm[top - 1 - lane] : 0u;
+                const int cnt = ontop ? __popc(sv) : 64;
                 int tot_all;
                 const int exc = sq_warp_excl_scan(cnt, tot_all);
                 int npop = __popc(__ballot_sync(SQ_FULL, exc + cnt <= 32));
                 if(top - npop + 32 > STACK_CAP - STACK_RESERVE) npop = 1;
                 const int nchild = __shfl_sync(SQ_FULL, exc + cnt, npop - 1);
-                if((int) lane < npop) {
-                    const int2 e = W.stack[top - 1 - lane];
-                    const unsigned cmk = W.scm[top - 1 - lane];
-                    W.s_first[lane] = e.x;
-                    W.s_mask[lane] = (unsigned) e.y;
-                    unsigned b = sv;
-                    for(int k = 0; k < cnt; k++) {
-                        const unsigned ob = b & (0u - b);          // lowest surviving octant
-                        b ^= ob;
-                        W.src[exc + k] = (unsigned char) lane;
-                        W.src[32 + exc + k] = (unsigned char) __popc(cmk & (ob - 1u));   // its position among the children
-                    }
-                }
-                top -= npop;
-                __syncwarp();
+                // slot j of the expansion belongs to the popped entry whose first slot is the last start marker <= j
+                const unsigned starts = __reduce_or_sync(SQ_FULL, (int) lane < npop ? (1u << (exc & 31)) : 0u);
                 const bool have = (int) lane < nchild;
+                const int el = have ? __popc(starts & ((2u << lane) - 1u)) - 1 : 0;
+                const int e_first = __shfl_sync(SQ_FULL, ent.x, el);
+                const unsigned e_mask = (unsigned) __shfl_sync(SQ_FULL, ent.y, el);
+                const unsigned e_pack = __shfl_sync(SQ_FULL, sv | (cmk << 8) | ((unsigned) exc << 16), el);
+                top -= npop;
                 unsigned mask = 0;
                 if(have) {
-                    const int o = W.src[lane];
-                    node = W.s_first[o] + (int) W.src[32 + lane];
-                    mask = W.s_mask[o];
+                    // the (lane - first slot)-th surviving octant of that entry -> its position among the children
+                    unsigned m8 = e_pack & 0xffu;
+                    int nth = (int) lane - (int) (e_pack >> 16), pos = 0;
+                    int c = __popc(m8 & 0xfu);
+                    if(nth >= c) { nth -= c; pos = 4; m8 >>= 4; }
+                    c = __popc(m8 & 3u);
+                    if(nth >= c) { nth -= c; pos += 2; m8 >>= 2; }
+                    if(nth >= (int) (m8 & 1u)) pos += 1;
+                    node = e_first + __popc((e_pack >> 8) & 0xffu & ((1u << pos) - 1u));
+                    mask = e_mask;
                 }
                 __syncwarp();
                 if(have) {
