@@ -28,7 +28,7 @@ import numpy as np
 FLOP_PER_INTERACTION = 28
 # dram__bytes_read.sum + dram__bytes_write.sum of one sq_walk_kernel launch on the N=1 workload (256^3), from the
 # `ncu --set full` capture summarised in profiles/r1_walk_v5c_sections.txt (1.663 GB + 0.526 GB); None for other sizes
-WALK_DRAM_TRAFFIC_256 = 2.178e9     # ncu --set full, walk v6 at 256^3: dram__bytes_read.sum 1.652 GB + dram__bytes_write.sum 0.526 GB (profiles/r1_walk_v6_sections.txt)
+WALK_DRAM_TRAFFIC_256 = 2.176e9     # ncu --set full, walk v6b at 256^3: dram__bytes_read.sum 1.650 GB + dram__bytes_write.sum 0.526 GB (profiles/r1_walk_v6_sections.txt)
 DIST_NGRID = {2: 320, 4: 400, 8: 512}   # ~256^3 particles per GPU (weak scaling), Nmesh = 2 Ngrid divisible by the ranks
 
 

@@ -408,3 +408,57 @@ def test_gravity_step_equals_separate_calls(ctx):
     ctx.upload_particles(pos, mass); ctx.ph_sort(); ctx.tree_build()
     a4, p4, st4 = ctx.grav_short_tree()
     assert g3 is None and q3 is None and st3.interactions == st4.interactions and np.array_equal(a3, a4)
+
+
+def test_full_size_properties_config2():
+    """BASELINE.json config 2 at its FULL size (Zel'dovich 256^3, Nmesh 512, the bench workload), where the oracle no
+    longer finishes in seconds: size-independent properties instead.
+      * sortedness of the key sequence, the permutation is a permutation (checksums), sorting is idempotent;
+      * tree: every particle is in the tree, node count in the range the reference expects (forcetree.cpp:33-35);
+      * walk: the interaction count does not depend on how targets are grouped (every opening decision is per target,
+        the reference's): 32-wide and 16-wide groups give the same total; accelerations agree to the FP32 pair-sum rounding;
+      * PM: the painted mesh holds the total mass; the PM force conserves momentum (same CIC kernel in and out,
+        antisymmetric difference operator)."""
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import shenqi_b200 as sq
+    ng = 256
+    pos, mass, par = bench.workload(ng, 2 * ng)
+    n = len(pos)
+    c = sq.Context(0)
+    try:
+        P = sq.Params.defaults(par["BoxSize"], 2 * ng, par["GravitySoftening"], G=par["G"], rho0=par["rho0"], TreeRcut=par["TreeRcut"], TreeUseBH=1)
+        c.set_params(P)
+        c.upload_particles(pos, mass); c.ph_sort()
+        keys, perm = c.sorted_keys_perm()
+        assert np.all(keys[1:] >= keys[:-1])
+        p64 = perm.astype(np.int64)
+        assert p64.sum() == n * (n - 1) // 2 and np.bitwise_xor.reduce(p64) == np.bitwise_xor.reduce(np.arange(n, dtype=np.int64))
+        assert len(np.unique(keys)) > 0.99 * n
+        info = c.tree_build()
+        assert info.numparticles == n and 0.2 * n < info.numnodes < 0.9 * n
+        a32, p32, st32 = c.grav_short_tree()
+        c.set_group_width(16)
+        a16, p16, st16 = c.grav_short_tree()
+        c.set_group_width(32)
+        assert st32.interactions == st16.interactions and st32.interactions > 500 * n
+        e = np.linalg.norm(a32 - a16, axis=1) / np.linalg.norm(a32, axis=1)
+        assert np.median(e) <= 1e-5 and np.percentile(e, 99.9) <= 1e-4, (np.median(e), np.percentile(e, 99.9))
+        ep = np.abs(p32 - p16) / np.abs(p32)
+        assert np.median(ep) <= 1e-5 and np.percentile(ep, 99.9) <= 1e-4
+        mesh = c.pm_paint()
+        mtot = float(mass.astype(np.float64).sum())
+        assert abs(mesh.sum() - mtot) <= 1e-10 * mtot
+        del mesh
+        gpm, ppot = c.gravpm_force()
+        mom = (mass[:, None].astype(np.float64) * gpm).sum(0)
+        assert np.abs(mom).max() <= 1e-9 * float((mass.astype(np.float64) * np.linalg.norm(gpm, axis=1)).sum())
+        # idempotence: the sorted set sorts to itself
+        spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
+        c.upload_particles(spos, smass); c.ph_sort()
+        keys2, perm2 = c.sorted_keys_perm()
+        assert np.array_equal(keys2, keys)
+        assert np.array_equal(perm2, np.arange(n, dtype=perm2.dtype))        # stable: ties keep their order too
+    finally:
+        c.close()
