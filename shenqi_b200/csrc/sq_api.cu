@@ -371,6 +371,9 @@ int sq_pm_force(sq_ctx * c, double * gravpm, double * potential)
 //   copy stream:  H2D FullTreeGravAccel, GravPM (the |a_old| inputs)        | D2H PM accelerations + potential
 //   main stream:  H2D pos, mass -> keys, sort, tree, PM -> unpermute PM out | |a_old|, gather -> walk -> unpermute -> D2H
 // so that only the first upload and the last download are exposed.  Results equal the separate calls'.
+static int sq_gravity_step_body(sq_ctx * c, const double * pos, const float * mass, int64_t n, const double * fulltree, const double * gravpm_old,
+                                double * accel, double * potential, double * gravpm, double * pm_potential, sq_walk_stats * stats);
+
 int sq_gravity_step(sq_ctx * c, const double * pos, const float * mass, int64_t n, const double * fulltree, const double * gravpm_old,
                     double * accel, double * potential, double * gravpm, double * pm_potential, sq_walk_stats * stats)
 {
@@ -380,6 +383,18 @@ int sq_gravity_step(sq_ctx * c, const double * pos, const float * mass, int64_t 
         SQ_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         for(int i = 0; i < 4; i++) SQ_CUDA(cudaEventCreateWithFlags(&c->evx[i], cudaEventDisableTiming));
     }
+    const int rc = sq_gravity_step_body(c, pos, mass, n, fulltree, gravpm_old, accel, potential, gravpm, pm_potential, stats);
+    if(rc != SQ_OK) {
+        // the caller's buffers must not be in flight when the call returns, whatever went wrong (keep the first message)
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamSynchronize(c->stream);
+    }
+    return rc;
+}
+
+static int sq_gravity_step_body(sq_ctx * c, const double * pos, const float * mass, int64_t n, const double * fulltree, const double * gravpm_old,
+                                double * accel, double * potential, double * gravpm, double * pm_potential, sq_walk_stats * stats)
+{
     SQ_TRY(sq_reset_particles(c, n));
     SQ_CUDA(cudaMemcpyAsync(c->pos_in.p, pos, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice, c->stream));
     SQ_CUDA(cudaMemcpyAsync(c->mass_in.p, mass, sizeof(float) * (size_t) n, cudaMemcpyHostToDevice, c->stream));

@@ -235,11 +235,8 @@ int sq_sort_pairs(sq_ctx * c, uint64_t * keys, uint32_t * vals, int64_t n, int b
     SQ_TRY(c->sort_tmp_keys.reserve(sizeof(uint64_t) * (size_t) n));
     SQ_TRY(c->sort_tmp_vals.reserve(sizeof(uint32_t) * (size_t) n));
     SQ_TRY(c->sort_hist.reserve(sizeof(uint32_t) * 256 * (size_t) nblocks));
-    static bool attr_set = false;
-    if(!attr_set) {
-        SQ_CUDA(cudaFuncSetAttribute(sq_sort_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(sq_sort_smem)));
-        attr_set = true;
-    }
+    // per device, not per process: set it on every call (a cheap driver query) rather than behind a process-wide flag
+    SQ_CUDA(cudaFuncSetAttribute(sq_sort_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(sq_sort_smem)));
     uint64_t * kin = keys, * kout = c->sort_tmp_keys.as<uint64_t>();
     uint32_t * vin = vals, * vout = c->sort_tmp_vals.as<uint32_t>();
     uint32_t * hist = c->sort_hist.as<uint32_t>();
