@@ -164,7 +164,9 @@ def run_reference_arm(args):
     line = {"impl": "reference", "metric": "short-range gravity particles/s", "value": v, "unit": "particles/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "zeldovich-%d^3-nmesh%d (headline config: 256^3/512)" % (ngrid, 2 * ngrid)},
+            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9" % (args.ngrid, args.nmesh or 2 * args.ngrid),
+                       "sample": "each step = the %d^3 / Nmesh %d sub-box of that workload (same spacing, softening, Rcut, ErrTolForceAcc), per-particle rate" % (ngrid, 2 * ngrid),
+                       "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5},
             "interactions_per_s": res["interactions"] / res["walk_s"],
             "cpu_baseline": {"value": v, "unit": "particles/s", "cores": res["cores"], "kind": res["kind"],
                              "sample": "%d^3 Zel'dovich sub-box (same spacing, softening, Rcut, ErrTolForceAcc as the 256^3 workload): sort+tree+walk by the %s, PM by the numpy restatement" % (ngrid, "reference's own OpenMP code" if res["kind"] == "reference" else "C port"),
