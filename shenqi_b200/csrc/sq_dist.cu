@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) sqd_route_scatter_kernel(const double * _
             const long long i = t0 + k0 + lane;
             const bool ok = i < n;
             const int o = ok ? (int) owner[i] : -1 - (int) lane;
-            const unsigned peers = __match_any_sync(SQ_FULL, o);
+            const unsigned peers = sq_match64((long long) o, (unsigned) o & 255u);
             const int leader = __ffs(peers) - 1;
             int base = 0;
             if(ok && (int) lane == leader) base = atomicAdd(&cur[o], __popc(peers));
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(256) sqd_slab_paint_kernel(const double4 * __r
             const double v = w * m;
             const long long lin = ok ? ((long long) (lx + ox) * nmesh + (oy ? iy1 : iy)) * nmesh + (oz ? iz1 : iz) : -1 - (long long) lane;
             // warp-aggregated: lanes that hit the same cell are summed, one red.add.f64 per distinct cell
-            const unsigned peers = __match_any_sync(SQ_FULL, lin);
+            const unsigned peers = sq_match64(lin, (unsigned) ((lx + ox) & 7) | ((unsigned) ((oy ? iy1 : iy) & 7) << 3) | ((unsigned) ((oz ? iz1 : iz) & 3) << 6));
             unsigned rem = peers;
             double sum = 0;
             while(__any_sync(SQ_FULL, rem != 0)) {

@@ -59,8 +59,8 @@ __global__ void __launch_bounds__(256) sq_pm_paint_kernel(const double * __restr
             w *= oz ? rz : (1 - rz);
             const double v = w * m;
             const long long lin = ok ? ((long long) ix[ox] * nmesh + iy[oy]) * nmesh + iz[oz] : -1 - (long long) lane;
-            // combine lanes that hit the same cell
-            const unsigned peers = __match_any_sync(SQ_FULL, lin);
+            // combine lanes that hit the same cell (hash = low bits of the three cell indices)
+            const unsigned peers = sq_match64(lin, (unsigned) (ix[ox] & 7) | ((unsigned) (iy[oy] & 7) << 3) | ((unsigned) (iz[oz] & 3) << 6));
             unsigned rem = peers;
             double sum = 0;
             while(__any_sync(SQ_FULL, rem != 0)) {

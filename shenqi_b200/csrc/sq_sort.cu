@@ -4,7 +4,7 @@
 //
 // 8-bit digits.  Per pass: (1) per-tile digit histogram, (2) exclusive scan of the bin-major
 // histogram matrix, (3) re-read the tile, rank every key inside the block with warp match/ballot
-// (no atomics, stable), stage the tile in shared memory in digit order and write each digit run
+// (eight ballots per key - MATCH.ANY is slow on sm_100 -, stable), stage the tile in shared memory in digit order and write each digit run
 // out contiguously.  Algorithmic traffic per pass: 8 B (histogram read) + 12 B read + 12 B written.
 #include "sq_common.cuh"
 
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sq_sort_hist_kernel(const uint64
             // warp-aggregate equal digits before touching shared memory
             const unsigned d = sq_digit(keys[i], shift);
             const unsigned active = __activemask();
-            const unsigned peers = __match_any_sync(active, d);
+            const unsigned peers = sq_match8(active, d);
             if((peers & sq_lanemask_lt()) == 0) atomicAdd(&h[d], (uint32_t) __popc(peers));
         }
     }
@@ -169,18 +169,17 @@ __global__ void __launch_bounds__(SORT_THREADS) sq_sort_scatter_kernel(const uin
         rnk[r] = 0;
         if(ok) {
             const unsigned d = sq_digit(key[r], shift);
-            const unsigned peers = __match_any_sync(valid, d);
+            const unsigned peers = sq_match8(valid, d);
             const int leader = __ffs(peers) - 1;
             uint32_t b = 0;
-            if((int) lane == leader) {
-                b = s.warp_hist[w][d];
-                s.warp_hist[w][d] = b + (uint32_t) __popc(peers);
-            }
+            // one shared-memory atomic per digit group: the rounds do not wait for each other (the atomics of one warp
+            // are applied in issue order, which keeps the sort stable), so the 12 rounds pipeline
+            if((int) lane == leader) b = atomicAdd(&s.warp_hist[w][d], (uint32_t) __popc(peers));
             b = __shfl_sync(peers, b, leader);
             rnk[r] = b + (uint32_t) __popc(peers & sq_lanemask_lt());
         }
-        __syncwarp();
     }
+    __syncwarp();
     __syncthreads();
     // thread d: exclusive scan of bin d over warps, then block-wide exclusive scan over bins
     {
