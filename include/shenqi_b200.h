@@ -32,6 +32,7 @@ extern "C" {
 #define SQ_ERR_ARG (-3)           /* bad argument or call order */
 #define SQ_ERR_NODE_POOL (-4)     /* tree needs more nodes than the pool holds even after growth (TreeAllocFactor > 3, forcetree.cpp:215-231) */
 #define SQ_ERR_TREE_DEPTH (-5)    /* more than 8 particles share one 2^-21 cell */
+#define SQ_ERR_NONFINITE (-7)     /* a non-finite position after the drift (drift.cpp:70-73) */
 #define SQ_ERR_MASS (-6)          /* a particle with Mass <= 0 (forcetree.cpp:808) */
 
 typedef struct sq_ctx sq_ctx;
@@ -212,6 +213,25 @@ int sq_pm_slab_gradient(sq_ctx * ctx, double * phi, const double * lo2, const do
 int sq_pm_slab_fft_inv(sq_ctx * ctx, const double * recv, int nranks, double * work, double * slab);
 int sq_pm_slab_readout(sq_ctx * ctx, const double * part4, int64_t m, int rank, int nranks, const double * s0, const double * s1,
                        const double * s2, const double * s3, double * out4);
+
+/* ---- drift, hierarchical gravity kick and active sub-list on DEVICE arrays --------
+ * All pointers except random_shift and nsub are device pointers on the context's device; work is queued on the
+ * context's stream.  `skip` (may be NULL) holds one byte per particle, non-zero = IsGarbage || Swallowed.
+ *
+ * sq_drift_device replaces drift_all_particles / real_drift_particle (libgadget/drift.cpp:16-81, 84-103) for
+ * collisionless particles: Pos += Vel * ddrift + random_shift, wrapped into (0, BoxSize]; skipped particles only
+ * follow the shift.  A non-finite result is fatal in the reference (endrun 5): SQ_ERR_NONFINITE here.
+ * sq_kick_device replaces the loop of apply_hierarchical_grav_kick (libgadget/timestep.cpp:270-287, 962-968):
+ * Vel[pa] += Accel[pa] * gravkick over the active list (NULL = all of [0, nactive)).
+ * sq_active_sublist_device replaces build_active_sublist (libgadget/timestep.cpp:1353-1397): the stable selection of
+ * the entries of `active` (NULL = 0 .. nactive-1) with TimeBinGravity <= maxtimebin whose bin is active at
+ * Ti_Current (is_timebin_active, timestep.cpp:132-139); *nsub receives the count (the call synchronises). */
+int sq_drift_device(sq_ctx * ctx, double * pos, const double * vel, const unsigned char * skip, int64_t n, double ddrift,
+                    const double * random_shift, double BoxSize);
+int sq_kick_device(sq_ctx * ctx, double * vel, const double * accel, const int32_t * active, const unsigned char * skip,
+                   int64_t nactive, double gravkick);
+int sq_active_sublist_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, const unsigned char * timebin,
+                             const unsigned char * skip, int maxtimebin, int64_t Ti_Current, int32_t * sublist, int64_t * nsub);
 
 /* ---- timing of the last device stages (CUDA events on the launching stream), milliseconds ------ */
 typedef struct sq_timings {

@@ -10,6 +10,7 @@
  *   grav_short_tree                libgadget/gravshort-tree2.cpp:141
  *   GravLocalTreeWalk::visit       libgadget/gravshort2.hpp:227   (interaction counts)
  *   grav_short_pair                libgadget/gravshort-pair.c:22
+ *   drift_all_particles            libgadget/drift.cpp:84
  * the way libgadget/tests/test_forcetree.cpp:294-331 and test_gravity.cpp:197-247 do
  * (single rank, trivial domain).  Only tests/, smoke() and bench.py's CPU-baseline leg load it.
  */
@@ -31,6 +32,7 @@
 #include <libgadget/gravity_old.h>
 #include <libgadget/petapm.h>
 #include <libgadget/timestep.h>
+#include <libgadget/drift.h>
 #include <libgadget/gravshort2.hpp>
 
 /* ---- symbols the path references but which live in reference files we do not build ---- */
@@ -46,6 +48,9 @@ ActiveParticles init_empty_active_particles(struct part_manager_type * pman)
 }
 /* libgadget/timebinmgr.cpp: only consulted for gas/BH hmax; DM-only path never reaches it */
 int is_timebin_active(int bin, inttime_t current_ti) { (void) bin; (void) current_ti; return 1; }
+
+/* libgadget/bhdynfric.h:22, consulted by drift.cpp:32 for Type 5 only; black holes are not built here */
+int BHGetRepositionEnabled(void) { return 0; }
 
 static struct ClockTable RefClocks;
 static DomainDecomp RefDomain;
@@ -151,6 +156,21 @@ void ref_get_particles(double * pos, float * mass, uint64_t * ids, double * full
         if(ids) ids[i] = p->ID;
         if(potential) potential[i] = p->Potential;
     }
+}
+
+/* drift_all_particles (drift.cpp:84-103) on the loaded particles with the given velocities; flags: bit0 IsGarbage, bit1 Swallowed */
+void ref_drift_all(const double * vel, const unsigned char * flags, double ddrift, const double * random_shift)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++) {
+        struct particle_data * p = &PartManager->Base[i];
+        for(int j = 0; j < 3; j++)
+            p->Vel[j] = vel[3 * i + j];
+        p->IsGarbage = flags ? (flags[i] & 1) : 0;
+        p->Swallowed = flags ? ((flags[i] >> 1) & 1) : 0;
+        p->Ti_drift = 0;
+    }
+    drift_all_particles(0, 1, ddrift, random_shift);
 }
 
 /* raw access to the reference's AoS, for boundary-layout tests */

@@ -556,3 +556,78 @@ void sqo_pm_transfer(const double * rho_k, int nmesh, double box, double asmth, 
                 }
             }
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * drift, hierarchical gravity kick, active sub-list
+ * ------------------------------------------------------------------------------------------- */
+
+/* libgadget/drift.cpp:16-81.  Type 1 particles: no Hsml prediction (:54-67), no black-hole jump (:32-53). */
+int64_t sqo_drift(double * pos, const double * vel, const unsigned char * skip, int64_t n, double ddrift,
+                  const double * random_shift, double box)
+{
+    int64_t bad = 0;
+    const double zero[3] = {0, 0, 0};
+    const double * sh = random_shift ? random_shift : zero;
+    #pragma omp parallel for reduction(+: bad)
+    for(int64_t i = 0; i < n; i++) {
+        double * p = pos + 3 * i;
+        int ok = 1;
+        if(skip && skip[i]) {            /* :20-29 */
+            for(int j = 0; j < 3; j++)
+                p[j] += sh[j];
+        } else {
+            for(int j = 0; j < 3; j++) { /* :68-75 */
+                /* rounded product, no contraction; association (Pos + shift) + Vel*ddrift: what g++ -O3 -ffast-math
+                 * (Options.mk.example:9) makes of drift.cpp:69, verified bit for bit against oracle/_ref; the
+                 * source order Pos + (Vel*ddrift + shift) differs from it by at most 1 ulp. */
+                volatile double t = vel[3 * i + j] * ddrift;
+                volatile double q = p[j] + sh[j];
+                p[j] = q + t;
+                if(!isfinite(p[j])) { bad++; ok = 0; }
+            }
+        }
+        if(!ok) continue;
+        for(int j = 0; j < 3; j++) {     /* :76-79 */
+            while(p[j] > box) p[j] -= box;
+            while(p[j] <= 0) p[j] += box;
+        }
+    }
+    return bad;
+}
+
+/* libgadget/timestep.cpp:270-279, 962-968 */
+void sqo_kick(double * vel, const double * accel, const int32_t * active, const unsigned char * skip, int64_t nactive, double gravkick)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < nactive; i++) {
+        const int64_t pa = active ? active[i] : i;
+        if(skip && skip[pa]) continue;
+        for(int j = 0; j < 3; j++) {
+            volatile double t = accel[3 * pa + j] * gravkick;
+            vel[3 * pa + j] += t;
+        }
+    }
+}
+
+/* libgadget/timestep.cpp:132-139, dti_from_timebin libgadget/timebinmgr.h:42-45 */
+int sqo_is_timebin_active(int bin, int64_t current)
+{
+    if(bin <= 0 || current <= 0) return 1;
+    return current % (int64_t) (1ull << (uint64_t) bin) == 0;
+}
+
+/* libgadget/timestep.cpp:1353-1397 */
+int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsigned char * timebin, const unsigned char * skip,
+                           int maxtimebin, int64_t ti_current, int32_t * sublist)
+{
+    int64_t m = 0;
+    for(int64_t i = 0; i < nactive; i++) {
+        const int32_t pi = active ? active[i] : (int32_t) i;
+        const int bin = timebin[pi];
+        if(skip && skip[pi]) continue;
+        if(bin > maxtimebin) continue;
+        if(!sqo_is_timebin_active(bin, ti_current)) continue;
+        sublist[m++] = pi;
+    }
+    return m;
+}

@@ -97,6 +97,19 @@ void sqo_pm_transfer(const double * rho_k, int nmesh, double box, double asmth, 
 /* Window table as GravShortTable builds it (libgadget/gravshort-tree2.cpp:29-69): floats. */
 void sqo_window_table(int windowtype, double asmth, float * force_tab, float * pot_tab, double * dx);
 
+/* ---- drift, hierarchical gravity kick, active sub-list ---- */
+/* libgadget/drift.cpp:16-81 (collisionless particles; skip[i] != 0 = IsGarbage || Swallowed) applied to all n
+ * particles as drift_all_particles does (:84-103).  Returns the number of non-finite coordinates (fatal there). */
+int64_t sqo_drift(double * pos, const double * vel, const unsigned char * skip, int64_t n, double ddrift,
+                  const double * random_shift, double box);
+/* libgadget/timestep.cpp:270-279 + 962-968: Vel[pa] += Accel[pa] * gravkick over the active list (NULL = all). */
+void sqo_kick(double * vel, const double * accel, const int32_t * active, const unsigned char * skip, int64_t nactive, double gravkick);
+/* libgadget/timestep.cpp:132-139 */
+int sqo_is_timebin_active(int bin, int64_t current);
+/* libgadget/timestep.cpp:1353-1397 (SubActivePredicate + build_active_sublist, std::copy_if = stable). Returns the count. */
+int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsigned char * timebin, const unsigned char * skip,
+                           int maxtimebin, int64_t ti_current, int32_t * sublist);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,7 +67,7 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_pm_force", "sq_pm_force_device", "sq_gravity_step", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
            "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
            "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
-           "sq_pm_slab_fft_inv", "sq_pm_slab_readout"]
+           "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
@@ -320,3 +320,23 @@ class Context:
     def pm_slab_readout(self, part4_ptr, m, rank, nranks, slab_ptrs, out4_ptr):
         self._check(self.L.sq_pm_slab_readout(self._ctx, ctypes.c_void_p(part4_ptr), c_i64(m), c_int(rank), c_int(nranks),
                                               *[ctypes.c_void_p(p) for p in slab_ptrs], ctypes.c_void_p(out4_ptr)))
+
+    # ---- drift_all_particles / apply_hierarchical_grav_kick / build_active_sublist on device arrays
+    def drift_device(self, pos_ptr, vel_ptr, n, ddrift, random_shift, BoxSize, skip_ptr=None):
+        """drift_all_particles (libgadget/drift.cpp:84-103): pos, vel = device double[n][3]; skip = device uint8[n] or None."""
+        sh = (c_dbl * 3)(*[float(x) for x in random_shift]) if random_shift is not None else None
+        self._check(self.L.sq_drift_device(self._ctx, ctypes.c_void_p(pos_ptr), ctypes.c_void_p(vel_ptr), ctypes.c_void_p(skip_ptr),
+                                           c_i64(n), c_dbl(ddrift), sh, c_dbl(BoxSize)))
+
+    def kick_device(self, vel_ptr, accel_ptr, nactive, gravkick, active_ptr=None, skip_ptr=None):
+        """the kick loop of apply_hierarchical_grav_kick (libgadget/timestep.cpp:270-279, 962-968)."""
+        self._check(self.L.sq_kick_device(self._ctx, ctypes.c_void_p(vel_ptr), ctypes.c_void_p(accel_ptr), ctypes.c_void_p(active_ptr),
+                                          ctypes.c_void_p(skip_ptr), c_i64(nactive), c_dbl(gravkick)))
+
+    def build_active_sublist_device(self, nactive, timebin_ptr, maxtimebin, Ti_Current, sublist_ptr, active_ptr=None, skip_ptr=None):
+        """build_active_sublist (libgadget/timestep.cpp:1371-1397); returns NumActiveParticle of the sub-list."""
+        nsub = c_i64(0)
+        self._check(self.L.sq_active_sublist_device(self._ctx, ctypes.c_void_p(active_ptr), c_i64(nactive), ctypes.c_void_p(timebin_ptr),
+                                                    ctypes.c_void_p(skip_ptr), c_int(maxtimebin), c_i64(Ti_Current),
+                                                    ctypes.c_void_p(sublist_ptr), ctypes.byref(nsub)))
+        return int(nsub.value)

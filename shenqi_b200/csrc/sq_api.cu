@@ -111,7 +111,7 @@ void sq_ctx_destroy(sq_ctx * c)
                        &c->t_lk, &c->t_parent, &c->t_rot, &c->t_lvl, &c->t_counters, &c->tree_keys, &c->tree_order, &c->tree_pos, &c->tree_mass,
                        &c->active_sorted, &c->w_accel, &c->w_pot, &c->w_stats, &c->w_targets, &c->w_table, &c->w_out_accel, &c->w_out_pot,
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
-                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b, &c->act_tmp};
+                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b, &c->act_tmp, &c->step_tmp};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
     for(int i = 0; i < 4; i++) if(c->evx[i]) cudaEventDestroy(c->evx[i]);

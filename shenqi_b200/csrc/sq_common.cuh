@@ -133,6 +133,7 @@ struct sq_ctx {
     cufftHandle slab_r2c = 0, slab_c2r = 0, slab_x = 0;
     int slab_N = 0, slab_P = 0;
     sq_buf slab_tab, route_tmp;
+    sq_buf step_tmp;                 // sq_step.cu: error counter, compaction block counts
 };
 
 static inline int sq_div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }

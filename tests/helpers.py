@@ -68,6 +68,9 @@ def oracle():
         L.sqo_tree_build.restype = c_i64
         L.sqo_tree_build_opt.restype = c_i64
         L.sqo_grav_short_tree.restype = c_i64
+        L.sqo_drift.restype = c_i64
+        L.sqo_is_timebin_active.argtypes = [c_int, c_i64]
+        L.sqo_active_sublist.restype = c_i64
         _oracle = L
     return _oracle
 
@@ -159,7 +162,51 @@ def o_pm_force(pos, mass, box, nmesh, asmth, G):
     return res[0], np.stack(res[1:], 1)
 
 
+def o_drift(pos, vel, skip, ddrift, shift, box):
+    """sqo_drift on a copy; returns (new positions, number of non-finite coordinates)."""
+    out = np.array(pos, np.float64, order="C", copy=True)
+    vel = np.ascontiguousarray(vel, np.float64)
+    skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+    shift = None if shift is None else np.ascontiguousarray(shift, np.float64)
+    bad = oracle().sqo_drift(ptr(out), ptr(vel), ptr(skip), c_i64(len(out)), c_dbl(ddrift), ptr(shift), c_dbl(box))
+    return out, int(bad)
+
+
+def o_kick(vel, accel, active, skip, gravkick):
+    out = np.array(vel, np.float64, order="C", copy=True)
+    accel = np.ascontiguousarray(accel, np.float64)
+    active = None if active is None else np.ascontiguousarray(active, np.int32)
+    skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+    na = len(out) if active is None else len(active)
+    oracle().sqo_kick(ptr(out), ptr(accel), ptr(active), ptr(skip), c_i64(na), c_dbl(gravkick))
+    return out
+
+
+def o_active_sublist(active, nactive, timebin, skip, maxtimebin, ti_current):
+    active = None if active is None else np.ascontiguousarray(active, np.int32)
+    timebin = np.ascontiguousarray(timebin, np.uint8)
+    skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+    out = np.zeros(max(int(nactive), 1), np.int32)
+    m = oracle().sqo_active_sublist(ptr(active), c_i64(nactive), ptr(timebin), ptr(skip), c_int(maxtimebin), c_i64(ti_current), ptr(out))
+    return out[:m].copy()
+
+
 # ----------------------------------------------------------------------------- reference wrappers
+def r_drift(pos, vel, flags, ddrift, shift, box):
+    """The reference's drift_all_particles (libgadget/drift.cpp:84) on (pos, vel); flags bit0 IsGarbage, bit1 Swallowed."""
+    R = ref()
+    pos = np.ascontiguousarray(pos, np.float64)
+    r_load(pos, np.ones(len(pos), np.float32), box)
+    vel = np.ascontiguousarray(vel, np.float64)
+    flags = None if flags is None else np.ascontiguousarray(flags, np.uint8)
+    shift = np.ascontiguousarray(shift, np.float64)
+    with quiet_stdout():
+        R.ref_drift_all(ptr(vel), ptr(flags), c_dbl(ddrift), ptr(shift))
+    out = np.zeros((len(pos), 3))
+    R.ref_get_particles(ptr(out), None, None, None, None)
+    return out
+
+
 def r_load(pos, mass, box, ids=None):
     R = ref()
     ids = None if ids is None else np.ascontiguousarray(ids, np.uint64)

@@ -1,0 +1,155 @@
+"""SURVEY 8(f2) on the GPU, through the C ABI: sq_drift_device / sq_kick_device / sq_active_sublist_device against the
+oracle restatement (bit for bit: FP64 with separately rounded products and sums, integer lists), the committed golden
+outputs of the reference's own drift_all_particles (tests/golden/step_ref.npz), and size-independent properties at the
+full 256^3 load of BASELINE config 2."""
+import os
+import sys
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
+from helpers import o_drift, o_kick, o_active_sublist
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(HERE, "golden", "step_ref.npz"))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import shenqi_b200 as sq
+    c = sq.Context(0)
+    c.set_stream(torch.cuda.current_stream().cuda_stream)
+    yield c
+    torch.cuda.synchronize()
+    c.close()
+
+
+def dev(a):
+    return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def dptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def gpu_drift(ctx, pos, vel, skip, ddrift, shift, box):
+    p, v, s = dev(pos), dev(vel), dev(skip)
+    ctx.drift_device(p.data_ptr(), v.data_ptr(), len(pos), ddrift, shift, box, skip_ptr=dptr(s))
+    return p.cpu().numpy()
+
+
+def test_drift_equals_golden_reference_output(ctx):
+    pos, vel, flags, ddrift, shift, box = GOLD["pos"], GOLD["vel"], GOLD["flags"], float(GOLD["ddrift"]), GOLD["shift"], float(GOLD["box"])
+    skip = (flags != 0).astype(np.uint8)
+    assert np.array_equal(gpu_drift(ctx, pos, vel, skip, ddrift, shift, box), GOLD["pos_after"])
+    assert np.array_equal(gpu_drift(ctx, pos, vel, None, -ddrift, None, box), GOLD["pos_after_back"])
+
+
+@pytest.mark.parametrize("n", [1, 33, 100003, 1 << 20])
+def test_drift_equals_oracle(ctx, n):
+    rng = np.random.default_rng(n)
+    box = 250000.0
+    pos = rng.random((n, 3)) * box
+    pos.flat[::7] = box                                   # Pos == BoxSize stays (wrap is `> Box`, drift.cpp:77)
+    vel = rng.standard_normal((n, 3)) * 2e5
+    vel[rng.random(n) < 0.01] *= 30
+    skip = (rng.random(n) < 0.04).astype(np.uint8)
+    shift = np.array([1234.5, -99999.25, 0.0])
+    exp, bad = o_drift(pos, vel, skip, 0.83, shift, box)
+    assert bad == 0
+    got = gpu_drift(ctx, pos, vel, skip, 0.83, shift, box)
+    assert np.array_equal(got, exp)
+    assert got.min() > 0 and got.max() <= box
+
+
+def test_drift_empty_and_nonfinite(ctx):
+    import shenqi_b200 as sq
+    ctx.drift_device(0, 0, 0, 1.0, None, 10.0)            # n = 0: nothing to do
+    pos = np.full((5, 3), 1.0); vel = np.zeros((5, 3)); vel[3, 2] = np.inf
+    with pytest.raises(sq.ShenqiError, match="non-finite"):
+        gpu_drift(ctx, pos, vel, None, 1.0, None, 10.0)    # endrun(5) in the reference, drift.cpp:70-73
+    with pytest.raises(sq.ShenqiError):
+        gpu_drift(ctx, pos, np.zeros((5, 3)), None, 1.0, None, 0.0)
+
+
+@pytest.mark.parametrize("with_list", [False, True])
+def test_kick_equals_oracle(ctx, with_list):
+    rng = np.random.default_rng(11)
+    n = 300007
+    vel = rng.standard_normal((n, 3)) * 100; acc = rng.standard_normal((n, 3)) * 1e4
+    skip = (rng.random(n) < 0.05).astype(np.uint8)
+    act = np.sort(rng.choice(n, n // 5, replace=False)).astype(np.int32) if with_list else None
+    na = n if act is None else len(act)
+    v, a, s, l = dev(vel), dev(acc), dev(skip), dev(act)
+    ctx.kick_device(v.data_ptr(), a.data_ptr(), na, 0.00271, active_ptr=dptr(l), skip_ptr=s.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(v.cpu().numpy(), o_kick(vel, acc, act, skip, 0.00271))
+    ctx.kick_device(v.data_ptr(), a.data_ptr(), 0, 1.0)   # empty active set
+
+
+@pytest.mark.parametrize("n", [1, 31, 2047, 2048, 2049, 10241, 3000017])
+@pytest.mark.parametrize("with_list", [False, True])
+def test_active_sublist_equals_oracle(ctx, n, with_list):
+    rng = np.random.default_rng(n + with_list)
+    timebin = rng.integers(0, 10, n).astype(np.uint8)
+    skip = (rng.random(n) < 0.03).astype(np.uint8)
+    act = np.sort(rng.choice(n, max(1, n // 2), replace=False)).astype(np.int32) if with_list else None
+    na = n if act is None else len(act)
+    tb, s, l = dev(timebin), dev(skip), dev(act)
+    out = torch.empty(na, dtype=torch.int32, device="cuda")
+    for ti, mtb in ((0, 46), (1 << 4, 46), (1 << 4, 2), (3 << 3, 5), ((1 << 9) + 1, 46), (1 << 9, 0)):
+        m = ctx.build_active_sublist_device(na, tb.data_ptr(), mtb, ti, out.data_ptr(), active_ptr=dptr(l), skip_ptr=s.data_ptr())
+        exp = o_active_sublist(act, na, timebin, skip, mtb, ti)
+        assert m == len(exp)
+        assert np.array_equal(out[:m].cpu().numpy(), exp)
+    assert ctx.build_active_sublist_device(0, tb.data_ptr(), 46, 0, out.data_ptr()) == 0
+
+
+def test_full_size_properties(ctx):
+    """256^3 particles (BASELINE config 2): the drift against the same IEEE operations done by torch elementwise kernels,
+    positions inside (0, Box], zero drift = identity; the sub-list is strictly increasing, its length equals the
+    predicate count, selecting from it again changes nothing (idempotence), and nested bins give nested lists."""
+    n, box = 256 ** 3, 100000.0
+    g = torch.Generator(device="cuda").manual_seed(3)
+    pos = torch.rand((n, 3), dtype=torch.float64, device="cuda", generator=g) * box
+    pos.clamp_(min=1e-9)
+    vel = torch.randn((n, 3), dtype=torch.float64, device="cuda", generator=g) * 4e4
+    shift = torch.tensor([17.0, -3.25, 50000.0], dtype=torch.float64, device="cuda")
+    exp = (pos + shift) + vel * 1.7
+    for _ in range(8):
+        exp = torch.where(exp > box, exp - box, exp)
+    for _ in range(8):
+        exp = torch.where(exp <= 0, exp + box, exp)
+    p = pos.clone()
+    ctx.drift_device(p.data_ptr(), vel.data_ptr(), n, 1.7, shift.tolist(), box)
+    assert torch.equal(p, exp)
+    assert float(p.min()) > 0 and float(p.max()) <= box
+    q = p.clone()
+    ctx.drift_device(q.data_ptr(), vel.data_ptr(), n, 0.0, None, box)
+    assert torch.equal(q, p)
+    del exp, q, pos
+
+    acc = torch.randn((n, 3), dtype=torch.float64, device="cuda", generator=g)
+    v2 = vel.clone()
+    ctx.kick_device(v2.data_ptr(), acc.data_ptr(), n, 0.125)
+    torch.cuda.synchronize()
+    assert torch.equal(v2, vel + acc * 0.125)
+    del v2, acc
+
+    timebin = torch.randint(0, 12, (n,), dtype=torch.uint8, device="cuda", generator=g)
+    out = torch.empty(n, dtype=torch.int32, device="cuda")
+    ti = 3 << 6
+    m = ctx.build_active_sublist_device(n, timebin.data_ptr(), 8, ti, out.data_ptr())
+    tb = timebin.long()
+    pred = (tb <= 8) & ((tb == 0) | (torch.remainder(torch.full_like(tb, ti), torch.bitwise_left_shift(torch.ones_like(tb), tb)) == 0))
+    assert m == int(pred.sum())
+    sub = out[:m]
+    assert bool((sub[1:] > sub[:-1]).all())
+    assert torch.equal(sub.long(), torch.nonzero(pred).flatten())
+    out2 = torch.empty(m, dtype=torch.int32, device="cuda")
+    m2 = ctx.build_active_sublist_device(m, timebin.data_ptr(), 8, ti, out2.data_ptr(), active_ptr=sub.data_ptr())
+    assert m2 == m and torch.equal(out2, sub)
+    m3 = ctx.build_active_sublist_device(m, timebin.data_ptr(), 4, ti, out2.data_ptr(), active_ptr=sub.data_ptr())
+    assert 0 < m3 < m and bool((timebin[out2[:m3].long()] <= 4).all())
