@@ -233,6 +233,33 @@ int sq_kick_device(sq_ctx * ctx, double * vel, const double * accel, const int32
 int sq_active_sublist_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, const unsigned char * timebin,
                              const unsigned char * skip, int maxtimebin, int64_t Ti_Current, int32_t * sublist, int64_t * nsub);
 
+/* Gravity time-bin assignment of hierarchical_gravity_accelerations (libgadget/timestep.cpp:351-377), per active particle:
+ * get_timestep_gravity_dloga (:1029-1039, grav_acceleration2 :1012-1027) -> convert_timestep_to_ti (:157-174, with
+ * TimeBinMgr::dti_from_dloga / ti_from_loga_snap, libgadget/timebinmgr.h:123-156) -> round_down_power_of_two
+ * (libgadget/timebinmgr.cpp:190) -> get_timestep_bin (:1236-1250) -> min(bin, largest_active) -> TimeBinGravity.
+ * The host fills the scalars from its Cosmology / TimeBinMgr state. */
+typedef struct sq_timebin_params {
+    double atime, hubble;              /* scale factor and H(a) at Ti_Current */
+    double ErrTolIntAccuracy;          /* TimestepParams, timestep.cpp:58 */
+    double MinSizeTimestep;            /* timestep.cpp:62 */
+    double softening;                  /* FORCE_SOFTENING() / 2.8 */
+    int64_t Ti_Current, dti_max;
+    double loga;                       /* TimeBinMgr::loga_from_ti(Ti_Current) */
+    int64_t lastsnap;                  /* Ti_Current >> TIMEBINS, clamped as timebinmgr.h:139-150 */
+    int can_advance;                   /* lastsnap < NSyncPoints - 2 */
+    double sync_loga[3];               /* SyncPoints[lastsnap .. lastsnap+2].loga (the third only if can_advance) */
+    int largest_active;
+} sq_timebin_params;
+#define SQ_TIMEBINS 46                 /* libgadget/timebinmgr.h:16 */
+/* accel = the acceleration store (or FullTreeGravAccel), gravpm = GravPM, both device double[n][3]; timebin = device
+ * uint8[n], written for every active, non-skipped particle; counts[SQ_TIMEBINS + 1] (host) receives timebincounts of
+ * this rank (the caller all-reduces them, timestep.cpp:378); *nbad = particles print_bad_timebin would report. */
+int sq_gravity_timebins_device(sq_ctx * ctx, const sq_timebin_params * par, const double * accel, const double * gravpm,
+                               const int32_t * active, const unsigned char * skip, int64_t nactive, unsigned char * timebin,
+                               int64_t * counts, int64_t * nbad);
+/* timestep.cpp:399-407: TimeBinGravity = min(TimeBinGravity, push_down_bin) over the active list. */
+int sq_timebin_pushdown_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, unsigned char * timebin, int push_down_bin);
+
 /* ---- timing of the last device stages (CUDA events on the launching stream), milliseconds ------ */
 typedef struct sq_timings {
     double keys_ms, sort_ms, gather_ms, tree_build_ms, tree_moments_ms, walk_ms;

@@ -631,3 +631,98 @@ int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsign
     }
     return m;
 }
+
+/* libgadget/timebinmgr.cpp:190-203 */
+int64_t sqo_round_down_power_of_two(int64_t dti)
+{
+    int64_t ti_min = (int64_t) 1 << 46;
+    int sign = 1;
+    if(dti < 0) { dti = -dti; sign = -1; }
+    while(ti_min > dti) ti_min >>= 1;
+    return ti_min * sign;
+}
+
+/* libgadget/timestep.cpp:1236-1250 */
+int sqo_get_timestep_bin(int64_t dti)
+{
+    int bin = -1;
+    if(dti <= 1) return 0;
+    while(dti) { bin++; dti >>= 1; }
+    return bin;
+}
+
+/* libgadget/timestep.cpp:351-377; volatile temporaries keep every product / sum separately rounded in source order. */
+int64_t sqo_gravity_timebins(const sqo_timebin_params * P, const double * accel, const double * gravpm, const int32_t * active,
+                             const unsigned char * skip, int64_t nactive, unsigned char * timebin, int64_t * counts)
+{
+    int64_t nbad = 0;
+    for(int k = 0; k <= 46; k++) counts[k] = 0;
+    for(int64_t i = 0; i < nactive; i++) {
+        const int64_t pa = active ? active[i] : i;
+        if(skip && skip[pa]) continue;
+        const double * ga = accel + 3 * pa, * pm = gravpm + 3 * pa;
+        /* grav_acceleration2, :1012-1027 */
+        volatile double aa = P->atime * P->atime;
+        volatile double a2inv = 1 / aa;
+        volatile double a[3];
+        for(int j = 0; j < 3; j++) {
+            volatile double t1 = a2inv * ga[j], t2 = a2inv * pm[j];
+            a[j] = t1 + t2;
+        }
+        volatile double s0 = a[0] * a[0], s1 = a[1] * a[1], s2 = a[2] * a[2];
+        volatile double s01 = s0 + s1;
+        volatile double ac2 = s01 + s2;
+        if(ac2 == 0) ac2 = 1.0e-60;
+        /* get_timestep_gravity_dloga, :1029-1039 */
+        volatile double ac = sqrt(ac2);
+        volatile double n1 = 2 * P->ErrTolIntAccuracy;
+        volatile double n2 = n1 * P->atime;
+        volatile double n3 = n2 * P->softening;
+        volatile double q = n3 / ac;
+        volatile double dt = sqrt(q);
+        volatile double dloga = dt * P->hubble;
+        /* convert_timestep_to_ti, :157-174 */
+        int64_t dti;
+        if(P->dti_max == 0)
+            dti = 0;
+        else {
+            if(dloga < P->MinSizeTimestep) dloga = P->MinSizeTimestep;
+            /* dti_from_dloga, timebinmgr.h:135-156; ti_from_loga_snap :123-132 */
+            volatile double target = dloga + P->loga;
+            int64_t snap = P->lastsnap; int k = 0;
+            if(P->can_advance && P->sync_loga[1] <= target) { snap++; k = 1; }
+            volatile double seg = P->sync_loga[k + 1] - P->sync_loga[k];
+            volatile double logDTime = seg / (double) ((uint64_t) 1 << 46);
+            int64_t tip = snap << 46;
+            volatile double off = target - P->sync_loga[k];
+            volatile double frac = off / logDTime;
+            volatile double tnew = (double) tip + frac;
+            tip = (tnew >= 9223372036854775808.0 || tnew < -9223372036854775808.0 || tnew != tnew) ? INT64_MIN : (int64_t) tnew;
+            dti = tip - P->Ti_Current;
+            if(dti > P->dti_max || dti < 0) dti = P->dti_max;
+        }
+        dti = sqo_round_down_power_of_two(dti);
+        if(dti <= 1 || dti > ((int64_t) 1 << 46)) nbad++;
+        int bin = sqo_get_timestep_bin(dti);
+        if(bin > P->largest_active) bin = P->largest_active;
+        counts[bin]++;
+        timebin[pa] = (unsigned char) bin;
+    }
+    return nbad;
+}
+
+/* libgadget/timestep.cpp:379-398 */
+int sqo_pushdown_bin(int64_t * counts, int largest_active, int isPM)
+{
+    for(int ti = largest_active; ti >= 1; ti--)
+        if(counts[ti] > 0) { largest_active = ti; break; }
+    int push_down_bin = largest_active;
+    if(isPM) {
+        for(int ti = largest_active; ti >= 1; ti--) {
+            if(counts[ti] / 3 > counts[ti - 1]) break;
+            push_down_bin = ti - 1;
+            counts[ti - 1] += counts[ti];
+        }
+    }
+    return push_down_bin;
+}

@@ -110,6 +110,28 @@ int sqo_is_timebin_active(int bin, int64_t current);
 int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsigned char * timebin, const unsigned char * skip,
                            int maxtimebin, int64_t ti_current, int32_t * sublist);
 
+/* libgadget/timestep.cpp:351-377 (gravity time-bin assignment of hierarchical_gravity_accelerations) with
+ * grav_acceleration2 / get_timestep_gravity_dloga (:1012-1039), convert_timestep_to_ti (:157-174),
+ * TimeBinMgr::dti_from_dloga / ti_from_loga_snap (libgadget/timebinmgr.h:123-156), round_down_power_of_two
+ * (libgadget/timebinmgr.cpp:190-203), get_timestep_bin (:1236-1250).  Same scalars as sq_timebin_params. */
+typedef struct sqo_timebin_params {
+    double atime, hubble, ErrTolIntAccuracy, MinSizeTimestep, softening;
+    int64_t Ti_Current, dti_max;
+    double loga;
+    int64_t lastsnap;
+    int can_advance;
+    double sync_loga[3];
+    int largest_active;
+} sqo_timebin_params;
+int64_t sqo_round_down_power_of_two(int64_t dti);
+int sqo_get_timestep_bin(int64_t dti);
+/* returns the number of particles print_bad_timebin would report; counts[47] */
+int64_t sqo_gravity_timebins(const sqo_timebin_params * par, const double * accel, const double * gravpm, const int32_t * active,
+                             const unsigned char * skip, int64_t nactive, unsigned char * timebin, int64_t * counts);
+/* libgadget/timestep.cpp:386-412: largest occupied bin, push-down rule on PM steps; returns the new largest_active
+ * (0 = the reference's endrun(77)); counts are updated as the reference does. */
+int sqo_pushdown_bin(int64_t * counts, int largest_active, int isPM);
+
 #ifdef __cplusplus
 }
 #endif

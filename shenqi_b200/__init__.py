@@ -5,7 +5,7 @@ of include/shenqi_b200.h).  There is no CPU fallback: importing works without a 
 checked), creating a Context does not.
 """
 from .api import (Context, Params, WalkStats, TreeInfo, Timings, ShenqiError, load_library, library_path,
-                  NODE_DTYPE, PARTICLE_DTYPE)
+                  NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin)
 
 __all__ = ["Context", "Params", "WalkStats", "TreeInfo", "Timings", "ShenqiError", "load_library", "library_path",
-           "NODE_DTYPE", "PARTICLE_DTYPE"]
+           "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin"]

@@ -61,13 +61,23 @@ class Timings(ctypes.Structure):
                                      "pm_paint_ms", "pm_fft_ms", "pm_transfer_ms", "pm_readout_ms")] + [("kernel_launches", c_i64)]
 
 
+class TimebinParams(ctypes.Structure):
+    """sq_timebin_params: the scalars of the gravity time-bin assignment (libgadget/timestep.cpp:351-377)."""
+    _fields_ = [("atime", c_dbl), ("hubble", c_dbl), ("ErrTolIntAccuracy", c_dbl), ("MinSizeTimestep", c_dbl), ("softening", c_dbl),
+                ("Ti_Current", c_i64), ("dti_max", c_i64), ("loga", c_dbl), ("lastsnap", c_i64), ("can_advance", c_int),
+                ("sync_loga", c_dbl * 3), ("largest_active", c_int)]
+
+
+TIMEBINS = 46
+
 EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq_set_params", "sq_set_walk_raw", "sq_sync", "sq_default_aos_layout",
            "sq_upload_particles_aos", "sq_upload_particles_soa", "sq_set_old_accel", "sq_set_oldacc", "sq_ph_sort", "sq_get_keys",
            "sq_get_sorted", "sq_tree_build", "sq_tree_export_nodes", "sq_tree_walk", "sq_tree_walk_device", "sq_download_accel",
            "sq_pm_force", "sq_pm_force_device", "sq_gravity_step", "sq_pm_paint", "sq_pm_get_mesh", "sq_get_timings", "sq_reset_timings", "sq_measure_fp32_peak",
            "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
            "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
-           "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device"]
+           "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device",
+           "sq_gravity_timebins_device", "sq_timebin_pushdown_device"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
@@ -340,3 +350,35 @@ class Context:
                                                     ctypes.c_void_p(skip_ptr), c_int(maxtimebin), c_i64(Ti_Current),
                                                     ctypes.c_void_p(sublist_ptr), ctypes.byref(nsub)))
         return int(nsub.value)
+
+    def gravity_timebins_device(self, par, accel_ptr, gravpm_ptr, nactive, timebin_ptr, active_ptr=None, skip_ptr=None):
+        """the bin-assignment loop of hierarchical_gravity_accelerations (libgadget/timestep.cpp:351-377):
+        returns (timebincounts[47] of this rank, number of bad time steps)."""
+        counts = (c_i64 * (TIMEBINS + 1))()
+        nbad = c_i64(0)
+        self._check(self.L.sq_gravity_timebins_device(self._ctx, ctypes.byref(par), ctypes.c_void_p(accel_ptr), ctypes.c_void_p(gravpm_ptr),
+                                                      ctypes.c_void_p(active_ptr), ctypes.c_void_p(skip_ptr), c_i64(nactive),
+                                                      ctypes.c_void_p(timebin_ptr), counts, ctypes.byref(nbad)))
+        return [int(x) for x in counts], int(nbad.value)
+
+    def timebin_pushdown_device(self, nactive, timebin_ptr, push_down_bin, active_ptr=None):
+        """libgadget/timestep.cpp:399-407."""
+        self._check(self.L.sq_timebin_pushdown_device(self._ctx, ctypes.c_void_p(active_ptr), c_i64(nactive), ctypes.c_void_p(timebin_ptr), c_int(push_down_bin)))
+
+
+def pushdown_bin(counts, largest_active, isPM):
+    """Host side of libgadget/timestep.cpp:379-398 on the (all-reduced) timebincounts: the largest occupied bin, then on PM
+    steps the push-down rule; returns (push_down_bin, counts after the merges).  0 is the reference's endrun(77)."""
+    counts = list(counts)
+    for ti in range(largest_active, 0, -1):
+        if counts[ti] > 0:
+            largest_active = ti
+            break
+    push = largest_active
+    if isPM:
+        for ti in range(largest_active, 0, -1):
+            if counts[ti] // 3 > counts[ti - 1]:
+                break
+            push = ti - 1
+            counts[ti - 1] += counts[ti]
+    return push, counts

@@ -145,6 +145,76 @@ __global__ void __launch_bounds__(1024) sqs_scan_kernel(int * __restrict__ count
     if(threadIdx.x == 0) *total = carry_s;
 }
 
+// timestep.cpp:351-377 per active particle.  Every FP64 operation is rounded separately in source order (IEEE division and
+// square root), so the integer step and the bin equal the CPU restatement's.
+__device__ __forceinline__ long long sqs_gravity_dti(const sq_timebin_params & P, const double * __restrict__ ga, const double * __restrict__ pm, double * dloga_out)
+{
+    // grav_acceleration2, timestep.cpp:1012-1027
+    const double a2inv = __ddiv_rn(1.0, __dmul_rn(P.atime, P.atime));
+    const double ax = __dadd_rn(__dmul_rn(a2inv, ga[0]), __dmul_rn(a2inv, pm[0]));
+    const double ay = __dadd_rn(__dmul_rn(a2inv, ga[1]), __dmul_rn(a2inv, pm[1]));
+    const double az = __dadd_rn(__dmul_rn(a2inv, ga[2]), __dmul_rn(a2inv, pm[2]));
+    double ac2 = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az));
+    if(ac2 == 0) ac2 = 1.0e-60;
+    // get_timestep_gravity_dloga, timestep.cpp:1029-1039
+    const double ac = __dsqrt_rn(ac2);
+    const double dt = __dsqrt_rn(__ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, P.ErrTolIntAccuracy), P.atime), P.softening), ac));
+    double dloga = __dmul_rn(dt, P.hubble);
+    *dloga_out = dloga;
+    // convert_timestep_to_ti, timestep.cpp:157-174
+    if(P.dti_max == 0) return 0;
+    if(dloga < P.MinSizeTimestep) dloga = P.MinSizeTimestep;
+    // TimeBinMgr::dti_from_dloga + ti_from_loga_snap, timebinmgr.h:123-156
+    const double target = __dadd_rn(dloga, P.loga);
+    long long snap = P.lastsnap;
+    int k = 0;
+    if(P.can_advance && P.sync_loga[1] <= target) { snap++; k = 1; }
+    const double logDTime = __ddiv_rn(__dadd_rn(P.sync_loga[k + 1], -P.sync_loga[k]), (double) (1ull << SQ_TIMEBINS));
+    long long tip = snap << SQ_TIMEBINS;
+    const double tnew = __dadd_rn((double) tip, __ddiv_rn(__dadd_rn(target, -P.sync_loga[k]), logDTime));
+    // `ti += double` converts back to inttime_t; the x86 conversion of an out-of-range or NaN value gives INT64_MIN
+    tip = (tnew >= 9223372036854775808.0 || tnew < -9223372036854775808.0 || tnew != tnew) ? (long long) 0x8000000000000000ull : (long long) tnew;
+    long long dti = tip - P.Ti_Current;
+    if(dti > P.dti_max || dti < 0) dti = P.dti_max;
+    return dti;
+}
+
+__global__ void __launch_bounds__(256) sqs_timebin_kernel(sq_timebin_params P, const double * __restrict__ accel, const double * __restrict__ gravpm,
+                                                          const int * __restrict__ active, const unsigned char * __restrict__ skip, long long nactive,
+                                                          unsigned char * __restrict__ timebin, unsigned long long * __restrict__ counts /* [48]: bins, then nbad */)
+{
+    __shared__ unsigned int hist[SQ_TIMEBINS + 2];
+    for(int k = threadIdx.x; k < SQ_TIMEBINS + 2; k += blockDim.x) hist[k] = 0;
+    __syncthreads();
+    const long long stride = (long long) gridDim.x * blockDim.x;
+    for(long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nactive; i += stride) {
+        const long long pa = active ? (long long) active[i] : i;
+        if(skip && skip[pa]) continue;
+        double dloga;
+        long long dti = sqs_gravity_dti(P, accel + 3 * pa, gravpm + 3 * pa, &dloga);
+        // round_down_power_of_two (timebinmgr.cpp:190) and get_timestep_bin (timestep.cpp:1236-1250)
+        if(dti > 0) dti = 1ll << (63 - __clzll(dti));      // largest power of two <= dti ...
+        if(dti > (1ll << SQ_TIMEBINS)) dti = 1ll << SQ_TIMEBINS;   // ... starting from TIMEBASE (timebinmgr.cpp:193-200)
+        if(dti <= 1 || dti > (1ll << SQ_TIMEBINS)) atomicAdd(&hist[SQ_TIMEBINS + 1], 1u);
+        int bin = dti <= 1 ? 0 : 63 - __clzll(dti);
+        if(bin > P.largest_active) bin = P.largest_active;
+        timebin[pa] = (unsigned char) bin;
+        atomicAdd(&hist[bin], 1u);
+    }
+    __syncthreads();
+    for(int k = threadIdx.x; k < SQ_TIMEBINS + 2; k += blockDim.x)
+        if(hist[k]) atomicAdd(&counts[k], (unsigned long long) hist[k]);
+}
+
+__global__ void __launch_bounds__(256) sqs_pushdown_kernel(const int * __restrict__ active, long long nactive, unsigned char * __restrict__ timebin, int push_down_bin)
+{
+    const long long stride = (long long) gridDim.x * blockDim.x;
+    for(long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nactive; i += stride) {
+        const long long pa = active ? (long long) active[i] : i;
+        if(timebin[pa] > push_down_bin) timebin[pa] = (unsigned char) push_down_bin;
+    }
+}
+
 extern "C" {
 
 int sq_drift_device(sq_ctx * c, double * pos, const double * vel, const unsigned char * skip, int64_t n, double ddrift,
@@ -201,6 +271,43 @@ int sq_active_sublist_device(sq_ctx * c, const int32_t * active, int64_t nactive
     SQ_CUDA(cudaMemcpyAsync(&h, total, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));
     *nsub = h;
+    return SQ_OK;
+}
+
+int sq_gravity_timebins_device(sq_ctx * c, const sq_timebin_params * par, const double * accel, const double * gravpm, const int32_t * active,
+                               const unsigned char * skip, int64_t nactive, unsigned char * timebin, int64_t * counts, int64_t * nbad)
+{
+    if(!c || !par || !counts || nactive < 0 || (nactive > 0 && (!accel || !gravpm || !timebin)) || par->largest_active < 0 ||
+       par->largest_active > SQ_TIMEBINS || !(par->atime > 0)) {
+        sq_set_error("sq_gravity_timebins_device: bad argument");
+        return SQ_ERR_ARG;
+    }
+    for(int k = 0; k <= SQ_TIMEBINS; k++) counts[k] = 0;
+    if(nbad) *nbad = 0;
+    if(nactive == 0) return SQ_OK;
+    SQ_CUDA(cudaSetDevice(c->device));
+    SQ_TRY(c->step_tmp.reserve(64 + 8 * (SQ_TIMEBINS + 2)));
+    unsigned long long * dcounts = (unsigned long long *) (c->step_tmp.as<char>() + 64);
+    SQ_CUDA(cudaMemsetAsync(dcounts, 0, 8 * (SQ_TIMEBINS + 2), c->stream));
+    sqs_timebin_kernel<<<step_grid(c, nactive, 8), 256, 0, c->stream>>>(*par, accel, gravpm, active, skip, nactive, timebin, dcounts);
+    c->kernel_launches++;
+    SQ_CUDA(cudaGetLastError());
+    unsigned long long h[SQ_TIMEBINS + 2];
+    SQ_CUDA(cudaMemcpyAsync(h, dcounts, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    SQ_CUDA(cudaStreamSynchronize(c->stream));
+    for(int k = 0; k <= SQ_TIMEBINS; k++) counts[k] = (int64_t) h[k];
+    if(nbad) *nbad = (int64_t) h[SQ_TIMEBINS + 1];
+    return SQ_OK;
+}
+
+int sq_timebin_pushdown_device(sq_ctx * c, const int32_t * active, int64_t nactive, unsigned char * timebin, int push_down_bin)
+{
+    if(!c || nactive < 0 || (nactive > 0 && !timebin) || push_down_bin < 0 || push_down_bin > SQ_TIMEBINS) { sq_set_error("sq_timebin_pushdown_device: bad argument"); return SQ_ERR_ARG; }
+    if(nactive == 0) return SQ_OK;
+    SQ_CUDA(cudaSetDevice(c->device));
+    sqs_pushdown_kernel<<<step_grid(c, nactive, 8), 256, 0, c->stream>>>(active, nactive, timebin, push_down_bin);
+    c->kernel_launches++;
+    SQ_CUDA(cudaGetLastError());
     return SQ_OK;
 }
 

@@ -71,6 +71,10 @@ def oracle():
         L.sqo_drift.restype = c_i64
         L.sqo_is_timebin_active.argtypes = [c_int, c_i64]
         L.sqo_active_sublist.restype = c_i64
+        L.sqo_gravity_timebins.restype = c_i64
+        L.sqo_round_down_power_of_two.restype = c_i64
+        L.sqo_round_down_power_of_two.argtypes = [c_i64]
+        L.sqo_get_timestep_bin.argtypes = [c_i64]
         _oracle = L
     return _oracle
 
@@ -189,6 +193,37 @@ def o_active_sublist(active, nactive, timebin, skip, maxtimebin, ti_current):
     out = np.zeros(max(int(nactive), 1), np.int32)
     m = oracle().sqo_active_sublist(ptr(active), c_i64(nactive), ptr(timebin), ptr(skip), c_int(maxtimebin), c_i64(ti_current), ptr(out))
     return out[:m].copy()
+
+
+class TimebinParams(ctypes.Structure):
+    """sqo_timebin_params (same fields as the product's sq_timebin_params)."""
+    _fields_ = [("atime", c_dbl), ("hubble", c_dbl), ("ErrTolIntAccuracy", c_dbl), ("MinSizeTimestep", c_dbl), ("softening", c_dbl),
+                ("Ti_Current", c_i64), ("dti_max", c_i64), ("loga", c_dbl), ("lastsnap", c_i64), ("can_advance", c_int),
+                ("sync_loga", c_dbl * 3), ("largest_active", c_int)]
+
+
+def timebin_params(cls=TimebinParams, **kw):
+    """A state like the reference's at z = 9 -> 8 with one sync point ahead: loga segments [ln 0.1, ln 0.111, ln 0.125]."""
+    import math
+    d = dict(atime=0.1, hubble=3.2, ErrTolIntAccuracy=0.02, MinSizeTimestep=0.0, softening=1.0 / 30, Ti_Current=0, dti_max=1 << 40,
+             loga=math.log(0.1), lastsnap=0, can_advance=1, sync_loga=(math.log(0.1), math.log(0.111), math.log(0.125)), largest_active=40)
+    d.update(kw)
+    sl = d.pop("sync_loga")
+    P = cls(**d)
+    for k in range(3):
+        P.sync_loga[k] = sl[k]
+    return P
+
+
+def o_gravity_timebins(P, accel, gravpm, active, skip, n, timebin=None):
+    accel = np.ascontiguousarray(accel, np.float64); gravpm = np.ascontiguousarray(gravpm, np.float64)
+    active = None if active is None else np.ascontiguousarray(active, np.int32)
+    skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+    tb = np.full(n, 255, np.uint8) if timebin is None else np.array(timebin, np.uint8, copy=True)
+    counts = np.zeros(47, np.int64)
+    na = n if active is None else len(active)
+    nbad = oracle().sqo_gravity_timebins(ctypes.byref(P), ptr(accel), ptr(gravpm), ptr(active), ptr(skip), c_i64(na), ptr(tb), ptr(counts))
+    return tb, counts, int(nbad)
 
 
 # ----------------------------------------------------------------------------- reference wrappers

@@ -5,7 +5,7 @@ made by tests/golden/make_golden_step.py), and the literal semantics of libgadge
 import os
 import numpy as np
 import pytest
-from helpers import ROOT, oracle, ref, o_drift, o_kick, o_active_sublist, r_drift
+from helpers import ROOT, oracle, ref, o_drift, o_kick, o_active_sublist, r_drift, o_gravity_timebins, timebin_params, c_i64, c_int, ptr
 
 needs_ref = pytest.mark.skipif(ref() is None, reason="oracle/_ref was not built (no /root/reference at build time)")
 GOLD = np.load(os.path.join(ROOT, "tests", "golden", "step_ref.npz"))
@@ -94,3 +94,81 @@ def test_oracle_active_sublist(with_list):
             got = o_active_sublist(act, na, timebin, skip, mtb, ti)
             assert np.array_equal(got, numpy_sublist(act, n, timebin, skip, mtb, ti))
     assert len(o_active_sublist(act, 0, timebin, skip, 46, 0)) == 0
+
+
+def test_oracle_round_down_power_of_two_known_answers():
+    """libgadget/tests/test_timebinmgr.cpp:143-145, and get_timestep_bin (timestep.cpp:1236-1250)."""
+    L = oracle()
+    TB = 1 << 46
+    assert L.sqo_round_down_power_of_two(TB) == TB
+    assert L.sqo_round_down_power_of_two(TB + 1) == TB
+    assert L.sqo_round_down_power_of_two(TB - 1) == TB // 2
+    assert L.sqo_round_down_power_of_two(0) == 0 and L.sqo_round_down_power_of_two(1) == 1 and L.sqo_round_down_power_of_two(-5) == -4
+    assert [L.sqo_get_timestep_bin(x) for x in (0, 1, 2, 3, 4, 1 << 20, (1 << 21) - 1, TB)] == [0, 0, 1, 1, 2, 20, 20, 46]
+
+
+def numpy_timebins(P, accel, gravpm):
+    """The same chain in numpy float64 (elementwise IEEE operations in source order)."""
+    a2inv = 1 / (P.atime * P.atime)
+    a = a2inv * accel + a2inv * gravpm
+    ac2 = a[:, 0] * a[:, 0] + a[:, 1] * a[:, 1] + a[:, 2] * a[:, 2]
+    ac2[ac2 == 0] = 1e-60
+    dloga = np.sqrt(2 * P.ErrTolIntAccuracy * P.atime * P.softening / np.sqrt(ac2)) * P.hubble
+    dloga = np.maximum(dloga, P.MinSizeTimestep)
+    target = dloga + P.loga
+    adv = (target >= P.sync_loga[1]) & bool(P.can_advance)
+    s0 = np.where(adv, P.sync_loga[1], P.sync_loga[0]); s1 = np.where(adv, P.sync_loga[2], P.sync_loga[1])
+    tnew = ((P.lastsnap + adv.astype(np.int64)) << 46).astype(np.float64) + (target - s0) / ((s1 - s0) / float(1 << 46))
+    tip = np.where(np.abs(tnew) < 2.0 ** 63, tnew, -2.0 ** 63).astype(np.int64)
+    dti = tip - P.Ti_Current
+    dti[(dti > P.dti_max) | (dti < 0)] = P.dti_max
+    dti = np.minimum(dti, 1 << 46)
+    bins = np.where(dti <= 1, 0, np.floor(np.log2(np.maximum(dti, 1).astype(np.float64))).astype(np.int64))
+    # log2 of an int64 near a power of two can round up: fix by the exact integer test
+    bins = np.where((np.int64(1) << bins) > np.maximum(dti, 1), bins - 1, bins)
+    return np.minimum(bins, P.largest_active)
+
+
+def test_oracle_gravity_timebins():
+    rng = np.random.default_rng(8)
+    n = 40000
+    acc = rng.standard_normal((n, 3)) * 10.0 ** rng.uniform(-2, 6, (n, 1))
+    pm = rng.standard_normal((n, 3)) * 10.0
+    acc[:3] = 0; pm[:3] = 0                                  # ac2 == 0 -> 1e-60 (timestep.cpp:1024)
+    skip = (rng.random(n) < 0.05).astype(np.uint8)
+    for kw in (dict(), dict(Ti_Current=(1 << 45) + (1 << 30), loga=np.log(0.1) + ((1 << 45) + (1 << 30)) * (np.log(0.111) - np.log(0.1)) / (1 << 46)),
+               dict(largest_active=33), dict(dti_max=1 << 31), dict(MinSizeTimestep=1e-4), dict(can_advance=0)):
+        P = timebin_params(**kw)
+        tb, counts, nbad = o_gravity_timebins(P, acc, pm, None, skip, n)
+        exp = numpy_timebins(P, acc, pm)
+        sel = skip == 0
+        assert np.array_equal(tb[sel], exp[sel]) and np.all(tb[~sel] == 255)
+        assert np.array_equal(counts, np.bincount(exp[sel], minlength=47)) and counts.sum() == sel.sum()
+        assert len(np.unique(tb[sel])) >= 3 or "largest_active" in kw or "dti_max" in kw
+        assert nbad == 0
+    act = np.sort(rng.choice(n, n // 4, replace=False)).astype(np.int32)
+    P = timebin_params()
+    tb, counts, _ = o_gravity_timebins(P, acc, pm, act, skip, n)
+    exp = numpy_timebins(P, acc, pm)
+    sel = act[skip[act] == 0]
+    assert np.array_equal(tb[sel], exp[sel]) and counts.sum() == len(sel) and (tb != 255).sum() == len(sel)
+    # dti_max == 0 -> dti 0 -> bin 0, reported as bad (timestep.cpp:161-162, 369-370)
+    tb, counts, nbad = o_gravity_timebins(timebin_params(dti_max=0), acc, pm, None, None, n)
+    assert nbad == n and counts[0] == n
+
+
+def test_pushdown_rule_host_equals_oracle():
+    """timestep.cpp:379-398: product host helper (shenqi_b200.pushdown_bin) against the C restatement."""
+    import shenqi_b200 as sq
+    rng = np.random.default_rng(9)
+    L = oracle()
+    for trial in range(200):
+        counts = np.zeros(47, np.int64)
+        top = int(rng.integers(2, 30))
+        occ = rng.integers(0, 2, top + 1).astype(bool)
+        counts[:top + 1] = rng.integers(0, 10 ** int(rng.integers(1, 7)), top + 1) * occ
+        for isPM in (0, 1):
+            c2 = counts.copy()
+            exp = L.sqo_pushdown_bin(ptr(c2), c_int(40), c_int(isPM))
+            got, c3 = sq.pushdown_bin(counts.tolist(), 40, isPM)
+            assert got == exp and c3 == c2.tolist()

@@ -10,7 +10,7 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
-from helpers import o_drift, o_kick, o_active_sublist
+from helpers import o_drift, o_kick, o_active_sublist, o_gravity_timebins, timebin_params
 
 pytestmark = pytest.mark.gpu
 GOLD = np.load(os.path.join(HERE, "golden", "step_ref.npz"))
@@ -153,3 +153,71 @@ def test_full_size_properties(ctx):
     assert m2 == m and torch.equal(out2, sub)
     m3 = ctx.build_active_sublist_device(m, timebin.data_ptr(), 4, ti, out2.data_ptr(), active_ptr=sub.data_ptr())
     assert 0 < m3 < m and bool((timebin[out2[:m3].long()] <= 4).all())
+
+
+@pytest.mark.parametrize("with_list", [False, True])
+def test_gravity_timebins_equal_oracle(ctx, with_list):
+    """timestep.cpp:351-377: bins and timebincounts identical to the restatement (integer result of an FP64 chain whose
+    every operation is IEEE-rounded in source order on both sides)."""
+    import shenqi_b200 as sq
+    rng = np.random.default_rng(21)
+    n = 500009
+    acc = rng.standard_normal((n, 3)) * 10.0 ** rng.uniform(-2, 6, (n, 1))
+    pm = rng.standard_normal((n, 3)) * 10.0
+    acc[:3] = 0; pm[:3] = 0
+    skip = (rng.random(n) < 0.05).astype(np.uint8)
+    act = np.sort(rng.choice(n, n // 3, replace=False)).astype(np.int32) if with_list else None
+    na = n if act is None else len(act)
+    a, g, s, l = dev(acc), dev(pm), dev(skip), dev(act)
+    ti = (1 << 45) + (1 << 30)
+    for kw in (dict(), dict(Ti_Current=ti, loga=np.log(0.1) + ti * (np.log(0.111) - np.log(0.1)) / (1 << 46)), dict(largest_active=33),
+               dict(dti_max=1 << 31), dict(MinSizeTimestep=1e-4), dict(can_advance=0), dict(dti_max=0)):
+        exp_tb, exp_counts, exp_bad = o_gravity_timebins(timebin_params(**kw), acc, pm, act, skip, n)
+        tb = torch.full((n,), 255, dtype=torch.uint8, device="cuda")
+        counts, nbad = ctx.gravity_timebins_device(timebin_params(cls=sq.TimebinParams, **kw), a.data_ptr(), g.data_ptr(), na, tb.data_ptr(),
+                                                   active_ptr=dptr(l), skip_ptr=s.data_ptr())
+        assert np.array_equal(tb.cpu().numpy(), exp_tb)
+        assert counts == exp_counts.tolist() and nbad == exp_bad
+    # push-down (timestep.cpp:399-407) with the host rule on the counts
+    P = timebin_params(cls=sq.TimebinParams)
+    tb = torch.full((n,), 255, dtype=torch.uint8, device="cuda")
+    counts, _ = ctx.gravity_timebins_device(P, a.data_ptr(), g.data_ptr(), na, tb.data_ptr(), active_ptr=dptr(l), skip_ptr=s.data_ptr())
+    before = tb.cpu().numpy()
+    occupied = [b for b in range(47) if counts[b]]
+    push = occupied[len(occupied) // 2]
+    ctx.timebin_pushdown_device(na, tb.data_ptr(), push, active_ptr=dptr(l))
+    torch.cuda.synchronize()
+    exp = before.copy()
+    idx = np.arange(n) if act is None else act
+    exp[idx] = np.minimum(before[idx], push)                 # the reference clamps every listed particle, skipped or not
+    assert np.array_equal(tb.cpu().numpy(), exp)
+    pd, merged = sq.pushdown_bin(counts, 40, True)
+    assert 0 < pd <= max(occupied) and sum(merged[:pd + 1]) >= sum(counts) - sum(counts[pd + 1:])
+    ctx.gravity_timebins_device(P, 0, 0, 0, 0)               # empty active set
+
+
+def test_hierarchical_cycle_at_full_size(ctx):
+    """256^3: assign bins -> counts sum to N -> sub-lists per bin partition the particles the way the counts say -> kick of a
+    sub-list touches exactly its members (a whole hierarchical bookkeeping cycle, timestep.cpp:351-472, on the device)."""
+    import shenqi_b200 as sq
+    n = 256 ** 3
+    g = torch.Generator(device="cuda").manual_seed(5)
+    acc = torch.randn((n, 3), dtype=torch.float64, device="cuda", generator=g) * torch.pow(10.0, torch.rand((n, 1), dtype=torch.float64, device="cuda", generator=g) * 6 - 1)
+    pm = torch.randn((n, 3), dtype=torch.float64, device="cuda", generator=g)
+    tb = torch.empty(n, dtype=torch.uint8, device="cuda")
+    P = timebin_params(cls=sq.TimebinParams)
+    counts, nbad = ctx.gravity_timebins_device(P, acc.data_ptr(), pm.data_ptr(), n, tb.data_ptr())
+    assert nbad == 0 and sum(counts) == n
+    assert counts == torch.bincount(tb.long(), minlength=47).tolist()
+    occupied = [b for b in range(47) if counts[b]]
+    assert len(occupied) >= 4
+    out = torch.empty(n, dtype=torch.int32, device="cuda")
+    vel = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+    b = occupied[1]
+    m = ctx.build_active_sublist_device(n, tb.data_ptr(), b, 1 << b, out.data_ptr())
+    assert m == sum(counts[:b + 1])                          # Ti = 2^b: exactly the bins <= b are active
+    ctx.kick_device(vel.data_ptr(), acc.data_ptr(), m, 0.5, active_ptr=out.data_ptr())
+    torch.cuda.synchronize()
+    touched = (vel != 0).any(dim=1)
+    assert int(touched.sum()) == m and bool((tb[touched] <= b).all())
+    assert torch.equal(vel[out[:m].long()], acc[out[:m].long()] * 0.5)

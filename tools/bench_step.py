@@ -57,6 +57,16 @@ def main():
         ms = timed(lambda: ctx.build_active_sublist_device(m, timebin.data_ptr(), 2, ti, out2.data_ptr(), active_ptr=sub.data_ptr()))
         m2 = ctx.build_active_sublist_device(m, timebin.data_ptr(), 2, ti, out2.data_ptr(), active_ptr=sub.data_ptr())
         put("sublist_of_" + label, ms, 10 * m + 4 * m2, candidates=m, selected=m2)
+    import math
+    pm = torch.randn((n, 3), dtype=torch.float64, device="cuda", generator=g)
+    P = sq.TimebinParams(atime=0.1, hubble=3.2, ErrTolIntAccuracy=0.02, MinSizeTimestep=0.0, softening=1.0 / 30, Ti_Current=0, dti_max=1 << 40,
+                         loga=math.log(0.1), lastsnap=0, can_advance=1, largest_active=40)
+    P.sync_loga[0], P.sync_loga[1], P.sync_loga[2] = math.log(0.1), math.log(0.111), math.log(0.125)
+    tb = torch.empty(n, dtype=torch.uint8, device="cuda")
+    ms = timed(lambda: ctx.gravity_timebins_device(P, acc.data_ptr(), pm.data_ptr(), n, tb.data_ptr()))
+    put("gravity_timebins", ms, 49 * n, note="48 B accelerations read + 1 B bin written per particle; includes the read-back of the 47 counts and the stream sync")
+    ms = timed(lambda: ctx.timebin_pushdown_device(n, tb.data_ptr(), 20))
+    put("timebin_pushdown", ms, 1 * n, note="1 B read per particle, writes only where the bin changes")
     print(json.dumps(res))
     ctx.close()
 
