@@ -40,6 +40,14 @@ class Comm:
         dist.all_gather_into_tensor(out, t, group=self.group)
         return out.view(self.world, len(vals)).tolist()
 
+    def allreduce_counts(self, counts, device):
+        """sum of a list of python ints over the ranks (MPI_Allreduce of timebincounts, libgadget/timestep.cpp:378)"""
+        if self.world == 1:
+            return list(counts)
+        t = torch.tensor(counts, dtype=torch.int64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t.tolist()
+
     def allgather_rows(self, t, counts):
         """t: [counts[rank], ...] -> concatenation over ranks in rank order"""
         if self.world == 1:
@@ -456,3 +464,11 @@ class CudaBackend:
         out = torch.empty_like(part4)
         self._pm().pm_slab_readout(part4.data_ptr(), part4.shape[0], rank, P, [s.data_ptr() for s in slabs], out.data_ptr())
         return out
+
+
+def global_pushdown_bin(comm, local_counts, largest_active, isPM, device="cpu"):
+    """libgadget/timestep.cpp:378-398 across ranks: all-reduce this rank's timebincounts (the output of
+    Context.gravity_timebins_device), then the largest occupied bin and the PM-step push-down rule on the GLOBAL counts,
+    so that every rank clamps to the same bin (Context.timebin_pushdown_device).  Returns (push_down_bin, global counts)."""
+    from .api import pushdown_bin
+    return pushdown_bin(comm.allreduce_counts(local_counts, device), largest_active, isPM)

@@ -112,3 +112,41 @@ def test_wrong_domain_order_is_refused():
     D = DistGravity(FakeBackend(), FakeComm())
     with pytest.raises(ValueError):
         D.tree_force(torch.zeros(2, 3, dtype=torch.float64), torch.ones(2))
+
+
+def _timebin_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from helpers import o_gravity_timebins, timebin_params
+        from shenqi_b200.dist import Comm, global_pushdown_bin
+        from shenqi_b200 import pushdown_bin
+        rng = np.random.default_rng(31)
+        n = 30000
+        acc = rng.standard_normal((n, 3)) * 10.0 ** rng.uniform(-1, 5, (n, 1)); pm = rng.standard_normal((n, 3))
+        cut = [0, int(0.3 * n), n]
+        P = timebin_params()
+        sl = slice(cut[rank], cut[rank + 1])
+        _, local, _ = o_gravity_timebins(P, acc[sl], pm[sl], None, None, cut[rank + 1] - cut[rank])
+        _, whole, _ = o_gravity_timebins(P, acc, pm, None, None, n)
+        push, merged = global_pushdown_bin(Comm(), local.tolist(), 40, True)
+        assert (push, merged) == pushdown_bin(whole.tolist(), 40, True)
+        assert push != pushdown_bin(local.tolist(), 40, True)[0] or local.sum() < whole.sum()
+        q.put((rank, push))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_timebin_counts_allreduce_world2():
+    """hierarchical bin assignment across 2 ranks (timestep.cpp:378-398): the push-down bin from the all-reduced counts
+    equals the single-rank rule on the whole particle set, on both ranks."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue(); port = _free_port()
+    procs = [ctx.Process(target=_timebin_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert got[0] == got[1] and got[0] > 0
