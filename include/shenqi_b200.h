@@ -17,6 +17,11 @@
  *   sq_tree_walk             grav_short_tree (libgadget/gravity.h:89, gravshort-tree2.cpp:141)
  *   sq_set_walk_raw          the GravTreeParams argument of grav_short_tree_cuda (libgadget/gravshort2.hpp:21-55, 440-443)
  *   sq_pm_force              gravpm_force -> petapm_force (libgadget/gravity.h:86, petapm.cpp:472)
+ *   sq_drift_device          drift_all_particles (libgadget/drift.h:9, drift.cpp:84)
+ *   sq_kick_device           apply_hierarchical_grav_kick (libgadget/timestep.cpp:249)
+ *   sq_active_sublist_device build_active_sublist (libgadget/timestep.cpp:111, 1373)
+ *   sq_gravity_timebins_device / sq_timebin_pushdown_device
+ *                            the bin loop and push-down of hierarchical_gravity_accelerations (libgadget/timestep.cpp:351-407)
  */
 #ifndef SHENQI_B200_H
 #define SHENQI_B200_H
