@@ -144,6 +144,8 @@ int sq_get_sorted(sq_ctx * ctx, uint64_t * sorted_keys, int32_t * perm);
 /* Build the oct-tree (leaf capacity 8, root 1.001*Box) and monopole moments from the sorted
  * particles.  active: upload-order indices of the particles to put in the tree, or NULL for all
  * (force_tree_active_moments vs force_tree_full). */
+/* `active` may be a host, managed (the reference's mymanagedmalloc lists, timestep.cpp:1319, 1376) or device pointer,
+ * e.g. the list sq_active_sublist_device wrote: the copy is by unified virtual addressing. Same for sq_tree_walk*. */
 int sq_tree_build(sq_ctx * ctx, const int32_t * active, int64_t nactive, sq_tree_info * info);
 /* Write the tree as the reference's NODE[numnodes] image (120 B each), node numbers starting at
  * firstnode, particle numbers = sorted positions (or upload indices if upload_order != 0). */

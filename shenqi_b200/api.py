@@ -207,6 +207,19 @@ class Context:
         self._check(self.L.sq_tree_walk_device(self._ctx, _p(act), c_i64(0 if act is None else len(act)), ctypes.byref(st)))
         return st
 
+    def tree_build_device_list(self, active_ptr, nactive):
+        """force_tree_active_moments with a DEVICE-resident active list (e.g. from build_active_sublist_device)."""
+        info = TreeInfo()
+        self._check(self.L.sq_tree_build(self._ctx, ctypes.c_void_p(active_ptr), c_i64(nactive), ctypes.byref(info)))
+        self.tree_info = info
+        return info
+
+    def grav_short_tree_device_list(self, active_ptr, nactive):
+        """grav_short_tree over a DEVICE-resident active list; results stay on the device (download_accel / device_ptr)."""
+        st = WalkStats()
+        self._check(self.L.sq_tree_walk_device(self._ctx, ctypes.c_void_p(active_ptr), c_i64(nactive), ctypes.byref(st)))
+        return st
+
     def download_accel(self):
         accel = np.zeros((self.n, 3)); pot = np.zeros(self.n)
         self._check(self.L.sq_download_accel(self._ctx, _p(accel), _p(pot)))

@@ -251,7 +251,7 @@ int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_
     int rc = SQ_OK;
     uint32_t h_total = 0;
     do {
-        cudaError_t e = cudaMemcpyAsync(d_act.p, active, sizeof(int32_t) * (size_t) nactive, cudaMemcpyHostToDevice, c->stream);
+        cudaError_t e = cudaMemcpyAsync(d_act.p, active, sizeof(int32_t) * (size_t) nactive, cudaMemcpyDefault, c->stream);   // host, managed or device list (UVA)
         if(e == cudaSuccess) e = cudaMemsetAsync(flags, 0, sizeof(uint32_t) * (size_t) (n + 4), c->stream);
         if(e != cudaSuccess) { sq_set_error("active list upload: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
         if(nactive > 0) {

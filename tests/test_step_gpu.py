@@ -221,3 +221,43 @@ def test_hierarchical_cycle_at_full_size(ctx):
     touched = (vel != 0).any(dim=1)
     assert int(touched.sum()) == m and bool((tb[touched] <= b).all())
     assert torch.equal(vel[out[:m].long()], acc[out[:m].long()] * 0.5)
+
+
+def test_substep_with_device_resident_list():
+    """One hierarchical sub-step without the list ever visiting the host (timestep.cpp:425-472): bins -> sub-list (device)
+    -> tree of the sub-list -> walk of the sub-list -> kick through the sub-list.  Same tree, interaction count and
+    accelerations (bit for bit) as the same sub-step driven by a host copy of the list."""
+    import shenqi_b200 as sq
+    from helpers import random_clustered
+    box, n, nmesh = 8.0, 60000, 48
+    pos = random_clustered(n, box, 17); mass = np.ones(n, np.float32)
+    P = sq.Params.defaults(box, nmesh, (box / n ** (1 / 3.)) / 30., TreeUseBH=1, TreeRcut=6.0)
+    c = sq.Context(0)
+    try:
+        c.set_params(P)
+        c.upload_particles(pos, mass); c.ph_sort()
+        rng = np.random.default_rng(3)
+        timebin = dev(rng.integers(1, 6, n).astype(np.uint8))
+        out = torch.empty(n, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        m = c.build_active_sublist_device(n, timebin.data_ptr(), 3, 1 << 2, out.data_ptr())     # bins 1 and 2 are active at Ti = 4
+        c._check(c.L.sq_sync(c._ctx))
+        host_list = out[:m].cpu().numpy()
+        assert 0 < m < n and np.array_equal(host_list, np.nonzero(timebin.cpu().numpy() <= 2)[0])
+        info_h = c.tree_build(host_list)
+        st_h = c.grav_short_tree_device(host_list)
+        acc_h, _ = c.download_accel()
+        info_d = c.tree_build_device_list(out.data_ptr(), m)
+        st_d = c.grav_short_tree_device_list(out.data_ptr(), m)
+        acc_d, _ = c.download_accel()
+        assert info_d.numparticles == info_h.numparticles == m and info_d.numnodes == info_h.numnodes
+        assert st_d.interactions == st_h.interactions > 0
+        assert np.array_equal(acc_d, acc_h) and np.abs(acc_d[host_list]).max() > 0
+        a = dev(acc_d); vel = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        c.kick_device(vel.data_ptr(), a.data_ptr(), m, 0.25, active_ptr=out.data_ptr())
+        c._check(c.L.sq_sync(c._ctx))
+        exp = np.zeros((n, 3)); exp[host_list] = acc_d[host_list] * 0.25
+        assert np.array_equal(vel.cpu().numpy(), exp)
+    finally:
+        c.close()
