@@ -280,6 +280,56 @@ int64_t ref_grav_count_interactions(int Nmesh, double Asmth, double G, double Er
     return total;
 }
 
+/* grav_short_tree over an explicit active list (particle indices of the loaded, sorted set), as the hierarchical
+ * stepping calls it (timestep.cpp:297-299).  accel: NumPart x 3, only the rows of active particles are written. */
+double ref_grav_short_tree_active(int Nmesh, double Asmth, double G, double ErrTolForceAcc, double BHOpeningAngle,
+        double MaxBHOpeningAngle, int TreeUseBH, double Rcut, double FracSoft, double MeanSeparation,
+        int windowtype, double rho0, const int * active, int64_t nactive, double * accel)
+{
+    PetaPM pm = ref_make_pm(Nmesh, Asmth, G);
+    set_gravshort_treepar(ref_make_treepar(ErrTolForceAcc, BHOpeningAngle, MaxBHOpeningAngle, TreeUseBH, Rcut, FracSoft, windowtype));
+    gravshort_set_softenings(MeanSeparation);
+    ActiveParticles act = init_empty_active_particles(PartManager);
+    act.ActiveParticle = (int *) active;
+    act.NumActiveParticle = nactive;
+    double t0 = MPI_Wtime();
+    grav_short_tree(&act, &pm, &RefTree, (MyFloat (*)[3]) accel, rho0, 0, RefUseGPU != 0);
+    return MPI_Wtime() - t0;
+}
+
+/* interaction counts of the reference's local walk for the listed particles only; counts[k] belongs to active[k] */
+int64_t ref_grav_count_interactions_active(int Nmesh, double Asmth, double G, double ErrTolForceAcc, double BHOpeningAngle,
+        double MaxBHOpeningAngle, int TreeUseBH, double Rcut, double FracSoft, double MeanSeparation,
+        int windowtype, const int * active, int64_t nactive, int64_t * counts)
+{
+    PetaPM pm = ref_make_pm(Nmesh, Asmth, G);
+    struct gravshort_tree_params tp = ref_make_treepar(ErrTolForceAcc, BHOpeningAngle, MaxBHOpeningAngle, TreeUseBH, Rcut, FracSoft, windowtype);
+    set_gravshort_treepar(tp);
+    gravshort_set_softenings(MeanSeparation);
+    GravShortTable gravtab(tp.ShortRangeForceWindowType, Asmth);
+    GravTreeParams priv(tp, 0, 1.0, &pm, RefTree.BoxSize, gravtab);
+    int64_t total = 0;
+    #pragma omp parallel for schedule(dynamic, 64) reduction(+: total)
+    for(int64_t k = 0; k < nactive; k++) {
+        const int i = active[k];
+        GravTreeQuery input(PartManager->Base[i], NULL, RefTree.firstnode, priv);
+        GravTreeResult output(input);
+        GravLocalTreeWalk lv(RefTree.Nodes, input);
+        const int64_t n = lv.visit<TREEWALK_PRIMARY>(input, &output, priv, PartManager->Base);
+        if(counts) counts[k] = n;
+        total += n;
+    }
+    return total;
+}
+
+/* keys of the loaded particles in their current (after ref_sort_particles: sorted) order */
+void ref_current_keys(uint64_t * keys)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        keys[i] = PEANO(PartManager->Base[i].Pos, PartManager->BoxSize);
+}
+
 /* grav_short_pair: direct sum over r <= Rcut; result lands in FullTreeGravAccel/Potential (tree is full). */
 double ref_grav_short_pair(int Nmesh, double Asmth, double G, double Rcut, double FracSoft, double MeanSeparation,
         int windowtype, double rho0, double * accel)
@@ -304,5 +354,7 @@ double ref_grav_short_pair(int Nmesh, double Asmth, double G, double Rcut, doubl
 
 double ref_force_softening(void) { return FORCE_SOFTENING(); }
 int ref_omp_threads(void) { return omp_get_max_threads(); }
+/* torchrun exports OMP_NUM_THREADS=1: the benchmark's CPU arm asks for every host core explicitly */
+void ref_set_threads(int n) { if(n > 0) omp_set_num_threads(n); }
 
 } /* extern "C" */

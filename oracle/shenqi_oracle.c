@@ -456,6 +456,45 @@ void sqo_grav_short_pair(const double * pos, const float * mass, int64_t n, cons
     }
 }
 
+/* libgadget/tests/test_gravity.cpp:44-83 (grav_force) + :133-153 (force_direct): Newtonian direct sum over the box and its
+ * 26 mirror images with the spline softening below h = FORCE_SOFTENING(), unit masses scaled by mass[j], self pairs (r2 == 0)
+ * skipped.  accn: N x 3, already x G. */
+void sqo_direct_sum_27(const double * pos, const float * mass, int64_t n, double box, double G, double h, double * accn)
+{
+    const double h_inv = 1.0 / h, h3_inv = h_inv * h_inv * h_inv;
+    #pragma omp parallel for schedule(dynamic, 16)
+    for(int64_t i = 0; i < n; i++) {
+        double a[3] = {0, 0, 0};
+        for(int xx = -1; xx <= 1; xx++)
+            for(int yy = -1; yy <= 1; yy++)
+                for(int zz = -1; zz <= 1; zz++) {
+                    const double off[3] = {box * xx, box * yy, box * zz};
+                    for(int64_t j = 0; j < n; j++) {
+                        double d[3], r2 = 0;
+                        for(int k = 0; k < 3; k++) {
+                            d[k] = off[k] + pos[3 * i + k] - pos[3 * j + k];
+                            r2 += d[k] * d[k];
+                        }
+                        if(r2 == 0)
+                            continue;
+                        const double r = sqrt(r2);
+                        double fac = 1 / (r2 * r);
+                        if(r < h) {
+                            const double u = r * h_inv;
+                            if(u < 0.5)
+                                fac = h3_inv * (10.666666666667 + u * u * (32.0 * u - 38.4));
+                            else
+                                fac = h3_inv * (21.333333333333 - 48.0 * u + 38.4 * u * u - 10.666666666667 * u * u * u - 0.066666666667 / (u * u * u));
+                        }
+                        for(int k = 0; k < 3; k++)
+                            a[k] += -d[k] * fac * G * (mass ? mass[j] : 1.0);
+                    }
+                }
+        for(int k = 0; k < 3; k++)
+            accn[3 * i + k] = a[k];
+    }
+}
+
 /* ------------------------------------------------------------------ particle mesh */
 static inline int64_t wrapi(int64_t i, int n) { i %= n; return i < 0 ? i + n : i; }
 

@@ -85,6 +85,9 @@ int64_t sqo_grav_short_tree(const sqo_node * nodes, int64_t firstnode, const dou
 void sqo_grav_short_pair(const double * pos, const float * mass, int64_t n, const sqo_grav_params * par,
                          double * accel, double * potential);
 
+/* libgadget/tests/test_gravity.cpp:44-83, 133-153: the O(N^2) periodic (27 images) checker of the reference's gravity test */
+void sqo_direct_sum_27(const double * pos, const float * mass, int64_t n, double box, double G, double h, double * accn);
+
 /* libgadget/petapm.cpp:1132-1183 + 1304-1310 on one periodic slab: mesh[Nmesh^3], z fastest. */
 void sqo_cic_paint(const double * pos, const float * mass, int64_t n, double box, int nmesh, double * mesh);
 /* libgadget/petapm.cpp:1132-1183 + gravpm.cpp:489-500: out[i] += sum_w mesh */

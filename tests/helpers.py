@@ -226,6 +226,56 @@ def o_gravity_timebins(P, accel, gravpm, active, skip, n, timebin=None):
     return tb, counts, int(nbad)
 
 
+def o_direct27(pos, mass, box, G, h):
+    """force_direct of libgadget/tests/test_gravity.cpp:133-153 (27 images, softened, self pairs skipped), in C."""
+    pos = np.ascontiguousarray(pos, np.float64)
+    mass = None if mass is None else np.ascontiguousarray(mass, np.float32)
+    out = np.zeros((len(pos), 3))
+    oracle().sqo_direct_sum_27(ptr(pos), ptr(mass), c_i64(len(pos)), c_dbl(box), c_dbl(G), c_dbl(h), ptr(out))
+    return out
+
+
+def boost_mt19937_uniform01(seed, count):
+    """The numbers boost::random::uniform_real_distribution<double>(0, 1) draws from boost::random::mt19937(seed):
+    boost 1.7x/1.8x generate_uniform_real() for an integer engine takes ONE 32-bit output per call,
+    (x - min) / (max - min + 1) = x / 2^32 (boost/random/uniform_real_distribution.hpp, detail::generate_uniform_real,
+    is_integral branch); mt19937(seed) is the standard init_genrand (first output for seed 0: 2357136044)."""
+    bg = np.random.MT19937()
+    bg._legacy_seeding(seed)
+    raw = bg.random_raw(count)
+    return raw.astype(np.float64) / 4294967296.0
+
+
+def reference_gravity_test_samples():
+    """The particle sets of libgadget/tests/test_gravity.cpp: (name, positions, check against the direct sum?).
+    16^3 particles in a box of 8, Nmesh 48, Asmth 1.5, Rcut 7 (test_gravity.cpp:26-38, 197-247):
+      flat    regular grid (:249-266), total force must vanish (:288-289)
+      close   all particles within 16/5000 of (4,4,4) (:292-313)
+      random0/1  two consecutive draws of do_random_test from ONE boost mt19937(0) stream (:316-355)."""
+    box, n, nc = 8.0, 4096, 16
+    i = np.arange(n)
+    flat = np.stack([(box / nc) * (i // nc // nc), (box / nc) * ((i // nc) % nc), (box / nc) * (i % nc)], 1).astype(np.float64)
+    close = np.stack([4. + (i // nc // nc) / 5000., 4. + ((i // nc) % nc) / 5000., 4. + (i % nc) / 5000.], 1).astype(np.float64)
+    u = boost_mt19937_uniform01(0, 2 * 3 * n).reshape(2, n, 3)
+    out = [("flat", flat, False), ("close", close, True)]
+    a, b = n // 4, 3 * n // 4
+    for k in range(2):
+        pos = np.zeros((n, 3))
+        pos[:a] = box * u[k, :a]
+        pos[a:b] = box / 2 + box / 8 * np.exp((u[k, a:b] - 0.5) ** 2)
+        pos[b:] = box * 0.1 + box / 32 * np.exp((u[k, b:] - 0.5) ** 2)
+        out.append(("random%d" % k, pos, True))
+    return out
+
+
+def reference_gravity_test_metric(total, direct):
+    """check_accns / find_means of libgadget/tests/test_gravity.cpp:85-131: component errors in units of the mean
+    |component| of the computed force; returns (maxerr, meanerr)."""
+    meanacc = np.abs(total).mean()
+    err = np.abs(direct - total) / meanacc
+    return float(err.max()), float(err.mean())
+
+
 # ----------------------------------------------------------------------------- reference wrappers
 def r_drift(pos, vel, flags, ddrift, shift, box):
     """The reference's drift_all_particles (libgadget/drift.cpp:84) on (pos, vel); flags bit0 IsGarbage, bit1 Swallowed."""

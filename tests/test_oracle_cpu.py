@@ -12,7 +12,8 @@ import numpy as np
 import pytest
 from helpers import (ROOT, oracle, ref, o_keys, o_sort, o_tree, o_walk, o_pair, o_cic_paint, o_cic_readout, o_pm_force,
                      canonical_tree, random_clustered, lattice, rel_err, default_params, r_load, r_sorted_particles, r_tree,
-                     r_walk, r_counts, r_pair, direct_sum_27, ptr, c_i64, c_dbl, NODE_DTYPE)
+                     r_walk, r_counts, r_pair, direct_sum_27, ptr, c_i64, c_dbl, NODE_DTYPE, o_direct27,
+                     reference_gravity_test_samples, reference_gravity_test_metric)
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 needs_ref = pytest.mark.skipif(ref() is None, reason="reference build (oracle/_ref) not present")
@@ -266,26 +267,39 @@ def test_oracle_cic_conserves_mass_and_reads_back():
     assert np.allclose(o_cic_readout(xs, pos, box, nmesh)[inner], pos[inner, 0], rtol=1e-10, atol=1e-10)
 
 
-def test_oracle_tree_plus_pm_vs_direct_sum():
-    """libgadget/tests/test_gravity.cpp:155-169, 197-247: 16^3 particles, box 8, Nmesh 48, Asmth 1.5, Rcut 7:
-    PM + tree against an O(N^2) periodic (27 images) direct sum; maxerr < 3 ErrTol-ish bound on the mean."""
-    box, nmesh = 8.0, 48
-    n = 12 ** 3
-    # clustered set (test_forcetree.cpp:404-430): for a uniform set the 27-image sum lacks the neutralising background
-    pos = random_clustered(n, box, 0)
+def oracle_reference_gravity_test(pos, box=8.0, nmesh=48):
+    """do_force_test of libgadget/tests/test_gravity.cpp:197-247 by the CPU restatement: gravpm_force, force_tree_full,
+    then grav_short_tree twice - Barnes-Hut (TreeUseBH = 2, angle 0.175) and then the relative criterion with the
+    test's own treeacc struct, whose MaxBHOpeningAngle is left at 0 (:226-234), i.e. BHOpeningAngle2 = 0
+    (gravshort2.hpp:52-53): every node is opened on the second call.  Returns PM + tree accelerations (input order)."""
+    n = len(pos)
     mass = np.ones(n, np.float32)
-    par = default_params(box, nmesh, n, TreeUseBH=1, TreeRcut=7.0)
+    par = default_params(box, nmesh, n, TreeUseBH=1, TreeRcut=7.0, GravitySoftening=(box / 16.0) / 30.0)
     perm = o_sort(o_keys(pos, box))
     spos = np.ascontiguousarray(pos[perm]); smass = np.ascontiguousarray(mass[perm])
-    nodes, first = o_tree(spos, smass, box)
-    a0, _, _, _ = o_walk(nodes, first, spos, smass, np.zeros(n), par)
+    nodes, first = o_tree(spos, smass, box, shortcut=False)
     _, gpm = o_pm_force(spos, smass, box, nmesh, 1.5, par["G"])
-    a1, _, _, _ = o_walk(nodes, first, spos, smass, np.linalg.norm(a0 + gpm, axis=1) / par["G"], dict(par, TreeUseBH=0))
-    tot = a1 + gpm
-    direct = direct_sum_27(spos, box, par["G"], 2.8 * par["GravitySoftening"])
-    # metric of test_gravity.cpp:155-169 (check_accns): component error in units of the mean |acceleration component|
-    err = np.abs(tot - direct) / np.abs(direct).mean()
-    assert err.max() < 0.05 and err.mean() < 0.005, (err.max(), err.mean())
+    a0, _, _, _ = o_walk(nodes, first, spos, smass, np.linalg.norm(gpm, axis=1) / par["G"], par)
+    a1, _, _, _ = o_walk(nodes, first, spos, smass, np.linalg.norm(a0 + gpm, axis=1) / par["G"], dict(par, TreeUseBH=0, MaxBHOpeningAngle=0.0))
+    tot = np.zeros((n, 3)); tot[perm] = a1 + gpm
+    return tot, par
+
+
+@pytest.mark.parametrize("case", [0, 1, 2, 3])
+def test_oracle_meets_reference_gravity_test_bounds(case):
+    """THE pin of the PM restatement (the reference holds no golden FFT vectors; its PM is pinned only through
+    the force-error thresholds of libgadget/tests/test_gravity.cpp): the reference's own four particle sets
+    (regular grid, close clump, two boost mt19937(0) draws), its own metric (check_accns :85-110) and its own bounds:
+    maxerr < 3 ErrTol = 0.006 and meanerr < 0.8 ErrTol = 0.0016 against the 27-image direct sum (:165-166); grid:
+    max |a| < 0.015, mean |a| < 0.005 (:288-289)."""
+    name, pos, direct = reference_gravity_test_samples()[case]
+    tot, par = oracle_reference_gravity_test(pos)
+    if direct:
+        d = o_direct27(pos, None, 8.0, par["G"], 2.8 * par["GravitySoftening"])
+        maxerr, meanerr = reference_gravity_test_metric(tot, d)
+        assert maxerr < 3 * 0.002 and meanerr < 0.8 * 0.002, (name, maxerr, meanerr)
+    else:
+        assert np.abs(tot).max() < 0.015 and np.abs(tot).mean() < 0.005, (name, np.abs(tot).max(), np.abs(tot).mean())
 
 
 # ------------------------------------------------------------------------------------------ C ABI
