@@ -80,6 +80,7 @@ typedef struct sq_walk_stats {
     int64_t pair_tests;        /* (target, node) pairs decided in FP32 with error intervals (tier 2) */
     int64_t exact_tests;       /* (target, node) pairs that needed the reference's FP64 expressions (tier 3) */
     double  kernel_ms;         /* device time of the walk kernel (CUDA events) */
+    int64_t pseudo_opened;     /* (target, pseudo node) pairs that opened a pseudo node with nothing imported below it: must be 0 */
 } sq_walk_stats;
 
 typedef struct sq_tree_info {
@@ -220,6 +221,71 @@ int sq_pm_slab_gradient(sq_ctx * ctx, double * phi, const double * lo2, const do
 int sq_pm_slab_fft_inv(sq_ctx * ctx, const double * recv, int nranks, double * work, double * slab);
 int sq_pm_slab_readout(sq_ctx * ctx, const double * part4, int64_t m, int rank, int nranks, const double * s0, const double * s1,
                        const double * s2, const double * s3, double * out4);
+
+/* ---- multi-rank tree: the reference's own partitioning (rows a5 top nodes, a7, a14, a15) ----------------
+ * One rank per GPU.  The domain is the reference's DomainDecomp (libgadget/domain.h:12-43): a top tree over
+ * Peano-Hilbert key ranges whose leaves are assigned to ranks.  Every rank builds the SAME top-level nodes
+ * (force_tree_create_topnodes / force_create_node_for_topnode, forcetree.cpp:654-686, 868-933), the sub-trees of its own
+ * top leaves, and pseudo nodes for the others; top-leaf moments are exchanged (force_exchange_pseudodata :1155-1206)
+ * and the internal top nodes recomputed (force_treeupdate_pseudos :1212-1282).  Boundary walks: where the reference
+ * exports a particle to the owner of every pseudo node it opens (GravTopTreeWalk::toptree_visit gravshort2.hpp:362-438,
+ * export table treewalk2.h:618-677, query / result exchange :742-812, ghost walk :687-733), this library imports, once
+ * per tree build, the part of each remote sub-tree that a local particle can reach - every node whose keep box
+ * (|centre - x| <= Rcut + len/2 on every axis, gravshort2.hpp:152-167) meets the bounding box of a local top leaf,
+ * with its true moments, and the particles of such leaves - and hangs it below the pseudo node.  The local walk then
+ * makes, for every target, exactly the decisions the reference's primary + ghost walks make together: the interaction
+ * set is the single-rank one (sq_walk_stats.interactions summed over ranks equals the one-rank count).
+ * All collectives are raw NCCL on the context's stream, behind this ABI (ncclAllReduce for moments / boxes / counts,
+ * grouped ncclSend / ncclRecv for the imports). */
+#define SQ_NCCL_UNIQUE_ID_BYTES 128
+/* same bytes as struct topnode_data / topleaf_data / task_data (libgadget/domain.h:12-31) */
+typedef struct sq_topnode { uint64_t StartKey; int32_t Daughter; int32_t Shift; int32_t Leaf; int32_t pad_; } sq_topnode;   /* 24 B */
+typedef struct sq_topleaf { int32_t Task; int32_t topnode; int32_t treenode; } sq_topleaf;                                  /* 12 B */
+typedef struct sq_task { int32_t StartLeaf; int32_t EndLeaf; } sq_task;                                                     /*  8 B */
+
+/* ncclGetUniqueId: call on one rank, hand the 128 bytes to every rank (MPI_Bcast in the reference's host). */
+int sq_comm_unique_id(void * id128);
+/* SURVEY 8b's sq_ctx_create(device, ncclUniqueId*, rank, nranks): a context that is one rank of nranks (collective). */
+int sq_ctx_create_dist(sq_ctx ** ctx, int device, const void * nccl_unique_id, int rank, int nranks);
+int sq_comm_rank(sq_ctx * ctx, int * rank, int * nranks);
+/* TEST TRANSPORT: an id for sq_ctx_create_dist that makes the ranks - host threads of ONE process, each with its own
+ * context, on one GPU or several - meet in an in-process hub instead of NCCL (device-to-device copies).  It lets the
+ * multi-rank path run where NCCL cannot (two ranks on one GPU); production runs use sq_comm_unique_id. */
+int sq_comm_loopback_id(void * id128, int key);
+/* Install the domain for the following tree builds (arrays are copied; treenode is filled by the build and can be read
+ * back with sq_domain_get_treenodes).  NULL / 0 removes it (trivial single-leaf domain).  Works with one rank too:
+ * the tree then carries the forced top-level nodes of the domain, as the reference's does. */
+int sq_domain_set(sq_ctx * ctx, const sq_topnode * topnodes, int ntopnodes, const sq_topleaf * topleaves, int ntopleaves,
+                  const sq_task * tasks, int ntasks);
+int sq_domain_get_treenodes(sq_ctx * ctx, int32_t * treenode /* [ntopleaves], node numbers relative to the first node */);
+/* Pure host code, no CUDA device needed: a top tree from a histogram of the particles' Peano-Hilbert keys over the
+ * 8^level cells of level `level` (cell = key >> (63 - 3 level)), refined until no leaf holds more than
+ * total / (overdecomposition * nranks) (domain.cpp:399, 1040-1160), leaves in key order cut into nranks contiguous
+ * segments of equal cost (domain_assign_topleaves_balanced, domain.cpp:620-800); cost may be NULL (= count).
+ * Arrays must hold max_topnodes entries; returns SQ_OK and the sizes. */
+int sq_domain_from_histogram(const int64_t * count, const double * cost, int level, int nranks, int overdecomposition,
+                             sq_topnode * topnodes, sq_topleaf * topleaves, sq_task * tasks, int max_topnodes,
+                             int * ntopnodes, int * ntopleaves);
+/* Histogram of this rank's uploaded particles over the level-`level` cells, summed over ranks (ncclAllReduce when the
+ * context is distributed); weights = per-particle cost in upload order (device or host pointer) or NULL. */
+int sq_domain_histogram(sq_ctx * ctx, int level, int64_t * count, double * cost, const float * weights);
+/* Rank that owns each uploaded particle under the installed domain (domain_get_topleaf, domain.h:68-75); host array. */
+int sq_domain_owner(sq_ctx * ctx, int32_t * owner);
+/* Collective.  sq_tree_build under the installed domain: local sub-trees + top nodes, moment exchange, import of the
+ * reachable parts of the remote sub-trees.  After it sq_tree_walk* walk the local particles against the global tree. */
+typedef struct sq_let_info {
+    int64_t local_nodes, local_particles;        /* this rank's tree before the import */
+    int64_t imported_nodes, imported_particles;  /* received from the other ranks */
+    int64_t exported_nodes, exported_particles;  /* sent to the other ranks (sum over peers) */
+    int64_t bytes_sent, bytes_received;
+    int64_t toptree_exports;                     /* (particle, rank) pairs the reference's toptree walk would export, if counted */
+    double build_ms, moments_exchange_ms, let_mark_ms, let_exchange_ms, let_attach_ms;
+} sq_let_info;
+int sq_tree_build_dist(sq_ctx * ctx, sq_tree_info * info, sq_let_info * let);
+/* GravTopTreeWalk::toptree_visit<TOPTREE_COUNT> (gravshort2.hpp:362-438) for every local particle over the top tree with
+ * exchanged moments: the number of (particle, rank) exports the reference would make - the measured export fraction that
+ * decides between query export and sub-tree import.  Host output. */
+int sq_toptree_export_count(sq_ctx * ctx, int64_t * nexports, int64_t * nparticles_exporting);
 
 /* ---- drift, hierarchical gravity kick and active sub-list on DEVICE arrays --------
  * All pointers except random_shift and nsub are device pointers on the context's device; work is queued on the

@@ -184,10 +184,47 @@ double ref_sort_particles(void)
     return MPI_Wtime() - t0;
 }
 
+/* A multi-leaf DomainDecomp on the single rank (every top leaf owned by task 0): force_tree_full then builds the forced
+ * top-level nodes of force_create_node_for_topnode (forcetree.cpp:868-933) above the sub-trees.  Arrays in the layout of
+ * struct topnode_data (24 B: StartKey, Daughter, Shift, Leaf) and topleaf_data (12 B); ntop == 0 restores the trivial domain. */
+void ref_set_domain(const void * topnodes, int ntop, const void * topleaves, int nleaves)
+{
+    ref_init();
+    if(force_tree_allocated(&RefTree))
+        force_tree_free(&RefTree);
+    free(RefDomain.TopNodes); free(RefDomain.TopLeaves); free(RefDomain.Tasks);
+    if(ntop <= 0) { ref_trivial_domain(&RefDomain); return; }
+    memset(&RefDomain, 0, sizeof(RefDomain));
+    RefDomain.domain_allocated_flag = 1;
+    RefDomain.NTopNodes = ntop;
+    RefDomain.NTopLeaves = nleaves;
+    RefDomain.TopNodes = (struct topnode_data *) calloc(ntop, sizeof(struct topnode_data));
+    RefDomain.TopLeaves = (struct topleaf_data *) calloc(nleaves, sizeof(struct topleaf_data));
+    RefDomain.Tasks = (struct task_data *) calloc(1, sizeof(struct task_data));
+    memcpy(RefDomain.TopNodes, topnodes, ntop * sizeof(struct topnode_data));
+    memcpy(RefDomain.TopLeaves, topleaves, nleaves * sizeof(struct topleaf_data));
+    for(int i = 0; i < nleaves; i++)
+        RefDomain.TopLeaves[i].Task = 0;
+    RefDomain.Tasks[0].StartLeaf = 0;
+    RefDomain.Tasks[0].EndLeaf = nleaves;
+}
+int ref_sizeof_topnode(void) { return (int) sizeof(struct topnode_data); }
+int ref_sizeof_topleaf(void) { return (int) sizeof(struct topleaf_data); }
+/* TopLeaves[].treenode after the build, relative to firstnode */
+void ref_domain_treenodes(int * out)
+{
+    for(int i = 0; i < RefDomain.NTopLeaves; i++)
+        out[i] = RefDomain.TopLeaves[i].treenode - (int) RefTree.firstnode;
+}
+
 /* force_tree_full with the trivial single-rank domain. Returns numnodes; seconds in *secs. */
 int64_t ref_tree_build(double treeallocfactor, double * secs)
 {
     init_forcetree_params(treeallocfactor);
+    /* Part[i].TopLeaf as the domain decomposition leaves it (domain.cpp: domain_get_topleaf of the particle's key) */
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        PartManager->Base[i].TopLeaf = domain_get_topleaf(PEANO(PartManager->Base[i].Pos, PartManager->BoxSize), RefDomain.TopNodes);
     double t0 = MPI_Wtime();
     force_tree_full(&RefTree, &RefDomain, 0, "");
     if(secs) *secs = MPI_Wtime() - t0;

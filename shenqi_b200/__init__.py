@@ -5,7 +5,9 @@ of include/shenqi_b200.h).  There is no CPU fallback: importing works without a 
 checked), creating a Context does not.
 """
 from .api import (Context, Params, WalkStats, TreeInfo, Timings, ShenqiError, load_library, library_path,
-                  NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin)
+                  NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin, Domain, LetInfo, domain_from_histogram,
+                  comm_unique_id, comm_loopback_id, TOPNODE_DTYPE, TOPLEAF_DTYPE, TASK_DTYPE)
 
 __all__ = ["Context", "Params", "WalkStats", "TreeInfo", "Timings", "ShenqiError", "load_library", "library_path",
-           "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin"]
+           "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin", "Domain", "LetInfo", "domain_from_histogram",
+           "comm_unique_id", "comm_loopback_id", "TOPNODE_DTYPE", "TOPLEAF_DTYPE", "TASK_DTYPE"]

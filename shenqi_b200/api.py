@@ -49,11 +49,88 @@ class AosLayout(ctypes.Structure):
 
 class WalkStats(ctypes.Structure):
     _fields_ = [("ntargets", c_i64), ("ngroups", c_i64), ("interactions", c_i64), ("list_entries", c_i64),
-                ("nodes_tested", c_i64), ("pair_tests", c_i64), ("exact_tests", c_i64), ("kernel_ms", c_dbl)]
+                ("nodes_tested", c_i64), ("pair_tests", c_i64), ("exact_tests", c_i64), ("kernel_ms", c_dbl), ("pseudo_opened", c_i64)]
 
 
 class TreeInfo(ctypes.Structure):
     _fields_ = [("numnodes", c_i64), ("numparticles", c_i64), ("maxnodes", c_i64), ("maxlevel", c_int), ("geo_mismatch", c_int)]
+
+
+class LetInfo(ctypes.Structure):
+    """sq_let_info: what sq_tree_build_dist built, imported and exported."""
+    _fields_ = [(n, c_i64) for n in ("local_nodes", "local_particles", "imported_nodes", "imported_particles", "exported_nodes",
+                                     "exported_particles", "bytes_sent", "bytes_received", "toptree_exports")] + \
+               [(n, c_dbl) for n in ("build_ms", "moments_exchange_ms", "let_mark_ms", "let_exchange_ms", "let_attach_ms")]
+
+
+# struct topnode_data / topleaf_data / task_data, libgadget/domain.h:12-31 (24 / 12 / 8 bytes)
+TOPNODE_DTYPE = np.dtype({"names": ["StartKey", "Daughter", "Shift", "Leaf"], "formats": ["<u8", "<i4", "<i4", "<i4"], "offsets": [0, 8, 12, 16], "itemsize": 24})
+TOPLEAF_DTYPE = np.dtype([("Task", "<i4"), ("topnode", "<i4"), ("treenode", "<i4")])
+TASK_DTYPE = np.dtype([("StartLeaf", "<i4"), ("EndLeaf", "<i4")])
+NCCL_UNIQUE_ID_BYTES = 128
+
+
+class Domain:
+    """The reference's DomainDecomp (libgadget/domain.h:33-43) as three arrays."""
+
+    def __init__(self, topnodes, topleaves, tasks):
+        self.topnodes = np.ascontiguousarray(topnodes, TOPNODE_DTYPE)
+        self.topleaves = np.ascontiguousarray(topleaves, TOPLEAF_DTYPE)
+        self.tasks = np.ascontiguousarray(tasks, TASK_DTYPE)
+
+    @property
+    def ntopleaves(self):
+        return len(self.topleaves)
+
+    def topleaf_of(self, keys):
+        """domain_get_topleaf (domain.h:68-75), vectorised."""
+        keys = np.asarray(keys, np.uint64)
+        no = np.zeros(len(keys), np.int64)
+        T = self.topnodes
+        while True:
+            d = T["Daughter"][no]
+            live = d >= 0
+            if not live.any():
+                break
+            sub = ((keys[live] - T["StartKey"][no[live]]) >> (T["Shift"][no[live]] - 3).astype(np.uint64)).astype(np.int64)
+            no[live] = d[live] + sub
+        return T["Leaf"][no]
+
+
+def domain_from_histogram(count, nranks, overdecomposition=4, cost=None, max_topnodes=None):
+    """sq_domain_from_histogram (pure host code, no GPU needed): a Domain from a Peano-Hilbert key histogram over the
+    8^level cells of one level."""
+    L = load_library()
+    count = np.ascontiguousarray(count, np.int64)
+    level = int(round(np.log2(len(count)) / 3))
+    assert 8 ** level == len(count)
+    cost = None if cost is None else np.ascontiguousarray(cost, np.float64)
+    mx = max_topnodes or (8 * len(count) // 7 + 16)
+    tn = np.zeros(mx, TOPNODE_DTYPE); tl = np.zeros(mx, TOPLEAF_DTYPE); tk = np.zeros(nranks, TASK_DTYPE)
+    ntn, ntl = c_int(), c_int()
+    rc = L.sq_domain_from_histogram(_p(count), _p(cost), c_int(level), c_int(nranks), c_int(overdecomposition), _p(tn), _p(tl), _p(tk), c_int(mx),
+                                    ctypes.byref(ntn), ctypes.byref(ntl))
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return Domain(tn[:ntn.value].copy(), tl[:ntl.value].copy(), tk)
+
+
+def comm_unique_id():
+    """ncclGetUniqueId as 128 bytes (numpy uint8): create on one rank, broadcast to all."""
+    L = load_library()
+    buf = np.zeros(NCCL_UNIQUE_ID_BYTES, np.uint8)
+    rc = L.sq_comm_unique_id(_p(buf))
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return buf
+
+
+def comm_loopback_id(key=0):
+    """TEST TRANSPORT id (sq_comm_loopback_id): ranks as threads of this process meet in an in-process hub."""
+    L = load_library()
+    buf = np.zeros(NCCL_UNIQUE_ID_BYTES, np.uint8)
+    L.sq_comm_loopback_id(_p(buf), c_int(key))
+    return buf
 
 
 class Timings(ctypes.Structure):
@@ -77,7 +154,9 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_ctx_set_stream", "sq_device_ptr", "sq_upload_particles_device", "sq_get_geo_mismatch", "sq_set_sorted_device", "sq_set_oldacc_range_device", "sq_tree_walk_range",
            "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
            "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device",
-           "sq_gravity_timebins_device", "sq_timebin_pushdown_device"]
+           "sq_gravity_timebins_device", "sq_timebin_pushdown_device",
+           "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram",
+           "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
@@ -111,10 +190,16 @@ def _p(a):
 class Context:
     """One GPU context (sq_ctx).  Method names follow the reference functions they stand behind."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, nccl_id=None, rank=0, nranks=1):
+        """nranks > 1: one rank of a multi-GPU run (sq_ctx_create_dist, collective); nccl_id = comm_unique_id() of one rank."""
         self.L = load_library()
         self._ctx = ctypes.c_void_p()
-        self._check(self.L.sq_ctx_create(ctypes.byref(self._ctx), c_int(device)))
+        self.rank, self.nranks = rank, nranks
+        if nranks > 1 or nccl_id is not None:
+            idb = None if nccl_id is None else np.ascontiguousarray(nccl_id, np.uint8)
+            self._check(self.L.sq_ctx_create_dist(ctypes.byref(self._ctx), c_int(device), _p(idb), c_int(rank), c_int(nranks)))
+        else:
+            self._check(self.L.sq_ctx_create(ctypes.byref(self._ctx), c_int(device)))
         self.n = 0
 
     def _check(self, rc):
@@ -189,6 +274,44 @@ class Context:
         nodes = np.zeros(self.tree_info.numnodes, NODE_DTYPE)
         self._check(self.L.sq_tree_export_nodes(self._ctx, _p(nodes), c_i64(firstnode), c_int(1 if upload_order else 0)))
         return nodes, firstnode
+
+    # ---- multi-rank tree under the reference's DomainDecomp
+    def domain_set(self, dom):
+        self.domain = dom
+        if dom is None:
+            self._check(self.L.sq_domain_set(self._ctx, None, c_int(0), None, c_int(0), None, c_int(0)))
+        else:
+            self._check(self.L.sq_domain_set(self._ctx, _p(dom.topnodes), c_int(len(dom.topnodes)), _p(dom.topleaves), c_int(len(dom.topleaves)),
+                                             _p(dom.tasks), c_int(len(dom.tasks))))
+
+    def domain_histogram(self, level, weights=None):
+        """key histogram of the uploaded particles over the level's 8^level cells, summed over ranks; returns (count, cost)."""
+        count = np.zeros(8 ** level, np.int64); cost = np.zeros(8 ** level, np.float64)
+        w = None if weights is None else np.ascontiguousarray(weights, np.float32)
+        self._check(self.L.sq_domain_histogram(self._ctx, c_int(level), _p(count), _p(cost), _p(w)))
+        return count, cost
+
+    def domain_owner(self):
+        owner = np.zeros(self.n, np.int32)
+        self._check(self.L.sq_domain_owner(self._ctx, _p(owner)))
+        return owner
+
+    def domain_treenodes(self):
+        tn = np.zeros(self.domain.ntopleaves, np.int32)
+        self._check(self.L.sq_domain_get_treenodes(self._ctx, _p(tn)))
+        return tn
+
+    def tree_build_dist(self):
+        """sq_tree_build_dist (collective): returns (TreeInfo, LetInfo)."""
+        info, let = TreeInfo(), LetInfo()
+        self._check(self.L.sq_tree_build_dist(self._ctx, ctypes.byref(info), ctypes.byref(let)))
+        self.tree_info = info
+        return info, let
+
+    def toptree_export_count(self):
+        a, b = c_i64(), c_i64()
+        self._check(self.L.sq_toptree_export_count(self._ctx, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     # ---- grav_short_tree
     def grav_short_tree(self, active=None, accel=None, potential=None):

@@ -106,12 +106,15 @@ void sq_ctx_destroy(sq_ctx * c)
     cudaStreamSynchronize(c->stream);
     sq_pm_destroy(c);
     sq_dist_destroy(c);
+    sq_comm_destroy(c);
     sq_buf * bufs[] = {&c->pos_in, &c->mass_in, &c->id_in, &c->type_in, &c->oldacc_in, &c->keys_in, &c->pos, &c->mass, &c->oldacc, &c->keys,
                        &c->perm, &c->rank, &c->sort_tmp_keys, &c->sort_tmp_vals, &c->sort_hist, &c->scan_tmp, &c->flag_tmp, &c->t_cm, &c->t_cl,
                        &c->t_lk, &c->t_parent, &c->t_rot, &c->t_lvl, &c->t_counters, &c->tree_keys, &c->tree_order, &c->tree_pos, &c->tree_mass,
                        &c->active_sorted, &c->w_accel, &c->w_pot, &c->w_stats, &c->w_targets, &c->w_table, &c->w_out_accel, &c->w_out_pot,
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
-                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b, &c->act_tmp, &c->step_tmp};
+                       &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b, &c->act_tmp, &c->step_tmp,
+                       &c->d_leafrange, &c->d_topnodes, &c->d_topleaves, &c->d_treenode, &c->t_top, &c->let_leafdata, &c->let_mask, &c->let_scan_n, &c->let_scan_p,
+                       &c->let_roots, &c->let_send, &c->let_recv, &c->let_boxes};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
     for(int i = 0; i < 4; i++) if(c->evx[i]) cudaEventDestroy(c->evx[i]);
@@ -146,6 +149,7 @@ int sq_set_walk_raw(sq_ctx * c, const sq_walk_raw * raw)
     memcpy(c->raw_pt, raw->pot_table, sizeof(float) * SQ_NTAB);
     c->raw.force_table = c->raw_ft; c->raw.pot_table = c->raw_pt;
     c->have_raw = true;
+    c->raw_serial++;
     return SQ_OK;
 }
 

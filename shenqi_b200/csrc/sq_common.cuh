@@ -43,6 +43,18 @@ void sq_set_error(const char * fmt, ...);
 struct sq_buf {
     void * p = nullptr;
     size_t cap = 0;
+    // grow to `bytes`, keeping the first `keep` bytes (device-to-device copy on `stream`)
+    int grow_keep(size_t bytes, size_t keep, cudaStream_t stream)
+    {
+        if(bytes <= cap) return SQ_OK;
+        void * q = nullptr;
+        size_t want = bytes + bytes / 16 + 256;
+        SQ_CUDA(cudaMalloc(&q, want));
+        if(p && keep > 0) SQ_CUDA(cudaMemcpyAsync(q, p, keep < cap ? keep : cap, cudaMemcpyDeviceToDevice, stream));
+        if(p) { SQ_CUDA(cudaStreamSynchronize(stream)); cudaFree(p); }
+        p = q; cap = want;
+        return SQ_OK;
+    }
     int reserve(size_t bytes)
     {
         if(bytes <= cap) return SQ_OK;
@@ -91,6 +103,7 @@ struct sq_ctx {
     sq_walk_raw raw = {};
     bool have_raw = false;
     float raw_ft[SQ_NTAB], raw_pt[SQ_NTAB];
+    uint64_t raw_serial = 0, w_table_sig = 0;     // device split table: rebuilt only when its inputs change
     int64_t kernel_launches = 0;
     sq_timings tm = {};
 
@@ -134,6 +147,23 @@ struct sq_ctx {
     int slab_N = 0, slab_P = 0;
     sq_buf slab_tab, route_tmp;
     sq_buf step_tmp;                 // sq_step.cu: error counter, compaction block counts
+
+    // ---- multi-rank tree (sq_domain.cu, sq_let.cu): the reference's DomainDecomp + raw NCCL
+    void * nccl_comm = nullptr;      // ncclComm_t
+    void * loop_hub = nullptr;       // test transport: ranks as host threads of one process (sq_let.cu)
+    int comm_rank = 0, nranks = 1;
+    std::vector<sq_topnode> dom_nodes;
+    std::vector<sq_topleaf> dom_leaves;
+    std::vector<sq_task> dom_tasks;
+    bool have_domain = false;
+    int dom_maxlevel = 0;            // deepest top-node level
+    sq_buf d_leafrange;              // int2 per top leaf: (first particle, count) of a local top leaf in the sorted order
+    sq_buf d_topnodes, d_topleaves, d_treenode, t_top;   // device copies; treenode[leaf] = node of that top leaf; t_top[node] = top node index or -1
+    sq_buf let_leafdata, let_mask, let_scan_n, let_scan_p, let_roots, let_send, let_recv, let_boxes;
+    int64_t n_local_nodes = 0;       // nodes of this rank's own build (imports are appended behind them)
+    int64_t n_sources = 0;           // particles the walk can read as sources: n local + imported
+    bool let_attached = false;
+    double walk_munit = 0;           // mass unit override for the walk's FP32 tiers (0: total / count of the local tree)
 };
 
 static inline int sq_div_up(int64_t a, int64_t b) { return (int) ((a + b - 1) / b); }
@@ -200,6 +230,8 @@ int sq_exclusive_scan_u32(sq_ctx * c, uint32_t * data, int64_t n, uint32_t * tot
 int sq_gather_run(sq_ctx * c);
 int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_buf * out, int64_t * count);
 int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_info * info);
+int sq_tree_moments_top(sq_ctx * c, int ls, int le);
+void sq_comm_destroy(sq_ctx * c);
 int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order);
 int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
 int sq_pm_run(sq_ctx * c, bool paint_only);

@@ -20,10 +20,16 @@ static const unsigned char h_ph_sub[48 * 8] = SQ_PH_SUB_INIT;
 
 // [0,3072): rot2[r*64+p]   [3072,6144): sub2[r*64+p]   [6144,6528): rot1[r*8+p]   [6528,6912): sub1
 #define SQ_PHTAB_BYTES 6912
-static unsigned char * d_phtab = nullptr;
+// one copy per device (a process may drive several GPUs through several contexts), created under a lock
+#include <mutex>
+static unsigned char * d_phtab_dev[64] = {};
+static std::mutex d_phtab_lock;
+#define d_phtab (d_phtab_dev[sq_current_device()])
+static int sq_current_device() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < 64) ? d : 0; }
 
 static int sq_phtab_init()
 {
+    std::lock_guard<std::mutex> guard(d_phtab_lock);
     if(d_phtab) return SQ_OK;
     unsigned char h[SQ_PHTAB_BYTES];
     for(int r = 0; r < 48; r++)

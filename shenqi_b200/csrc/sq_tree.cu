@@ -26,8 +26,9 @@ int sq_iota(sq_ctx * c, uint32_t * v, int64_t n);
 #define CNT_ERR 2
 
 __global__ void sq_tree_root_kernel(double4 * cm, double4 * cl, int4 * lk, int * parent, unsigned char * rot, int * lvl, int * cnt,
-                                    int np, double box)
+                                    int np, double box, int * topidx)
 {
+    if(topidx) topidx[0] = 0;      // the root is top node 0 of the domain (force_tree_create_topnodes, forcetree.cpp:654-686)
     // forcetree.cpp:653-686: root cube 1.001*Box centred on Box/2; the trivial domain's single top leaf
     cl[0] = make_double4(box / 2., box / 2., box / 2., box * 1.001);
     cm[0] = make_double4(0, 0, 0, 0);
@@ -51,8 +52,15 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
                                                             const float * __restrict__ mass, double4 * __restrict__ cm,
                                                             double4 * __restrict__ cl, int4 * __restrict__ lk, int * __restrict__ parent,
                                                             unsigned char * __restrict__ rot, const int * __restrict__ lvl, int * __restrict__ cnt,
-                                                            int L, int maxnodes, const unsigned char * __restrict__ phtab)
+                                                            int L, int maxnodes, const unsigned char * __restrict__ phtab,
+                                                            const sq_topnode * __restrict__ tn, const sq_topleaf * __restrict__ tl,
+                                                            int * __restrict__ treenode, int * __restrict__ topidx, int myrank, int2 * __restrict__ leafrange)
 {
+    // With a domain (tn != NULL) the top of the tree is the domain's top tree, force_create_node_for_topnode
+    // (forcetree.cpp:868-933): a node that is an internal top node gets all 8 children whatever it holds (TopLevel,
+    // never pruned, forcetree.cpp:1033-1041), the child whose key digit is `sub` being top node Daughter + sub; a top
+    // leaf of another rank is a pseudo node (no particles here); a top leaf of this rank is built down as usual and
+    // its node number recorded (TopLeaves[].treenode).
     __shared__ unsigned char rot1[384], sub1[384];
     for(int i = threadIdx.x; i < 384; i += blockDim.x) {
         rot1[i] = phtab[6144 + i];
@@ -73,13 +81,32 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
         int4 link = make_int4(0, 0, -1, 0);
         if(live) link = lk[i];
         const int first = link.x, count = link.y;
-        const bool split = live && count > SQ_NMAXCHILD;
+        bool forced = false, pseudo = false;
+        int daughter = -1, wflags = link.w;
+        if(tn && live) {
+            const int ti = topidx[i];
+            if(ti >= 0) {
+                const sq_topnode T = tn[ti];
+                if(T.Daughter >= 0) { forced = true; daughter = T.Daughter; }
+                else {
+                    pseudo = tl[T.Leaf].Task != myrank;
+                    wflags |= pseudo ? (2 << 8) : (1 << 14);               // PSEUDO_NODE_TYPE / DependsOnLocalMass
+                    if(sl == 0) {
+                        treenode[T.Leaf] = i;
+                        leafrange[T.Leaf] = make_int2(first, pseudo ? 0 : count);
+                        if(pseudo && count > 0) atomicOr(&cnt[CNT_ERR], 4);   // a particle of another rank's top leaf
+                        lk[i] = make_int4(first, pseudo ? 0 : count, link.z, wflags);
+                    }
+                }
+            }
+        }
+        const bool split = live && !pseudo && (forced || count > SQ_NMAXCHILD);
         int nchild = 0, slot = 0, s_oct = 0, pix = 0, start = 0, ccount = 0;
         unsigned rotn = 0;
         if(live && !split) {
             // leaf: moments now (forcetree.cpp:946-952, 984-1003)
             double m = 0, mx = 0, my = 0, mz = 0;
-            if(sl < count) {
+            if(sl < count && !pseudo) {
                 const int p = first + sl;
                 m = (double) mass[p];
                 mx = m * pos[3 * (int64_t) p];
@@ -122,14 +149,15 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
             if(sl == 7) nxt = first + count;
             ccount = split && L < SQ_MAXLEVEL ? nxt - start : 0;
         }
-        if(ccount > 0) {
+        const bool exists = ccount > 0 || (forced && split && L < SQ_MAXLEVEL);
+        if(exists) {
             // octant whose key digit is sl in this orientation; reference child index = x + 2y + 4z
             #pragma unroll
             for(int p = 0; p < 8; p++)
                 if(sub1[rotn * 8 + p] == sl) pix = p;
             s_oct = ((pix >> 2) & 1) | (((pix >> 1) & 1) << 1) | ((pix & 1) << 2);
         }
-        unsigned mm = ccount > 0 ? (1u << s_oct) : 0u;
+        unsigned mm = exists ? (1u << s_oct) : 0u;
         #pragma unroll
         for(int o = 4; o >= 1; o >>= 1)
             mm |= __shfl_xor_sync(SQ_FULL, mm, o);
@@ -149,7 +177,7 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
             if(tbase + nchild > maxnodes) {
                 if(sl == 0) atomicOr(&cnt[CNT_ERR], 1);
             } else {
-                if(ccount > 0) {
+                if(exists) {
                     const int c = tbase + slot;
                     const double4 pc = cl[i];
                     const double q = 0.25 * pc.w;
@@ -157,19 +185,21 @@ __global__ void __launch_bounds__(256) sq_tree_split_kernel(const uint64_t * __r
                     cl[c] = make_double4((s_oct & 1) ? __dadd_rn(pc.x, q) : __dadd_rn(pc.x, -q),
                                          (s_oct & 2) ? __dadd_rn(pc.y, q) : __dadd_rn(pc.y, -q),
                                          (s_oct & 4) ? __dadd_rn(pc.z, q) : __dadd_rn(pc.z, -q), 0.5 * pc.w);
-                    lk[c] = make_int4(start, ccount, sib, (L + 1) | (s_oct << 16));
+                    lk[c] = make_int4(start, ccount, sib, (L + 1) | (s_oct << 16) | (forced ? (1 << 12) : 0));
                     parent[c] = i;
                     rot[c] = rot1[rotn * 8 + pix];
+                    if(topidx) topidx[c] = forced ? daughter + sl : -1;
                 }
                 if(sl == 0)
-                    lk[i] = make_int4(tbase, nchild, link.z, link.w | (1 << 8) | (int) (mm << 24));   // + which octants exist
+                    lk[i] = make_int4(tbase, nchild, link.z, wflags | (1 << 8) | (int) (mm << 24) | (forced ? (1 << 13) : 0));   // + which octants exist
             }
         }
     }
 }
 
 // Bottom-up moments of the internal nodes of one level (forcetree.cpp:1080-1100)
-__global__ void __launch_bounds__(256) sq_tree_moments_kernel(double4 * __restrict__ cm, const int4 * __restrict__ lk, int ls, int le)
+__global__ void __launch_bounds__(256) sq_tree_moments_kernel(double4 * __restrict__ cm, const int4 * __restrict__ lk, int ls, int le,
+                                                              const double4 * __restrict__ cl, int toponly)
 {
     const unsigned lane = sq_lane();
     const int sg = lane >> 3, sl = lane & 7;
@@ -179,7 +209,7 @@ __global__ void __launch_bounds__(256) sq_tree_moments_kernel(double4 * __restri
         const int i = base_node + sg;
         int4 link = make_int4(0, 0, -1, 0);
         if(i < le) link = lk[i];
-        const bool internal = (i < le) && SQ_INFO_TYPE(link.w) == 1;
+        const bool internal = (i < le) && SQ_INFO_TYPE(link.w) == 1 && (!toponly || SQ_INFO_ITOP(link.w));
         double m = 0, mx = 0, my = 0, mz = 0;
         if(internal && sl < link.y) {
             const double4 c = cm[link.x + sl];
@@ -194,6 +224,7 @@ __global__ void __launch_bounds__(256) sq_tree_moments_kernel(double4 * __restri
         }
         if(internal && sl == 0) {
             if(m > 0) cm[i] = make_double4(mx / m, my / m, mz / m, m);
+            else if(SQ_INFO_ITOP(link.w)) { const double4 c4 = cl[i]; cm[i] = make_double4(c4.x, c4.y, c4.z, 0.0); }   // forcetree.cpp:1275-1281
             else cm[i] = make_double4(0, 0, 0, 0);
         }
     }
@@ -281,6 +312,10 @@ static int sq_tree_alloc(sq_ctx * c, int64_t maxnodes)
     SQ_TRY(c->t_parent.reserve(sizeof(int) * (size_t) maxnodes));
     SQ_TRY(c->t_rot.reserve((size_t) maxnodes + 16));
     SQ_TRY(c->t_lvl.reserve(sizeof(int) * 64));
+    if(c->have_domain) {
+        SQ_TRY(c->t_top.reserve(sizeof(int) * (size_t) maxnodes));
+        SQ_TRY(c->d_leafrange.reserve(sizeof(int2) * c->dom_leaves.size()));
+    }
     return SQ_OK;
 }
 
@@ -355,25 +390,35 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
     const double * tp = c->tree_identity ? c->pos.as<double>() : c->tree_pos.as<double>();
     const float * tmass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
     double factor = c->par.TreeAllocFactor > 0 ? c->par.TreeAllocFactor : 0.9;
+    const bool dom = c->have_domain;
+    if(dom && c->geo_mismatch && c->dom_nodes.size() > 1) {
+        sq_set_error("tree build: particles exactly on a cell face under a multi-leaf domain are not supported");
+        return SQ_ERR_ARG;
+    }
+    const sq_topnode * d_tn = dom ? c->d_topnodes.as<sq_topnode>() : nullptr;
+    const sq_topleaf * d_tl = dom ? c->d_topleaves.as<sq_topleaf>() : nullptr;
+    const int ntopnodes = dom ? (int) c->dom_nodes.size() : 0;
     const unsigned char * phtab = sq_phtab_device();
     if(!phtab) return SQ_ERR_CUDA;
     int h_lvl[SQ_MAXLEVEL + 4];
     int h_cnt[4];
     for(;;) {
         // forcetree.cpp:200: maxnodes = TreeAllocFactor * NumPart + NTopNodes
-        int64_t maxnodes = (int64_t) (factor * (double) np) + 1 + 64;
+        int64_t maxnodes = (int64_t) (factor * (double) np) + 1 + 64 + ntopnodes;
         if(maxnodes > 0x5fffffff) maxnodes = 0x5fffffff;   // forcetree.cpp:1385 index limit
         SQ_TRY(sq_tree_alloc(c, maxnodes));
         int * lvl = c->t_lvl.as<int>();
         int * cnt = c->t_counters.as<int>();
         SQ_CUDA(cudaMemsetAsync(lvl, 0, sizeof(int) * 64, c->stream));
         sq_tree_root_kernel<<<1, 1, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(), c->t_parent.as<int>(),
-                c->t_rot.as<unsigned char>(), lvl, cnt, (int) np, c->par.BoxSize);
+                c->t_rot.as<unsigned char>(), lvl, cnt, (int) np, c->par.BoxSize, dom ? c->t_top.as<int>() : nullptr);
+        if(dom) SQ_CUDA(cudaMemsetAsync(c->d_treenode.p, 0xff, sizeof(int) * c->dom_leaves.size(), c->stream));
         c->kernel_launches++;
         const int grid = c->num_sms * 4;
         for(int L = 0; L <= SQ_MAXLEVEL; L++) {
             sq_tree_split_kernel<<<grid, 256, 0, c->stream>>>(tk, tp, tmass, c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
-                    c->t_parent.as<int>(), c->t_rot.as<unsigned char>(), lvl, cnt, L, (int) maxnodes, phtab);
+                    c->t_parent.as<int>(), c->t_rot.as<unsigned char>(), lvl, cnt, L, (int) maxnodes, phtab,
+                    d_tn, d_tl, dom ? c->d_treenode.as<int>() : nullptr, dom ? c->t_top.as<int>() : nullptr, c->comm_rank, dom ? c->d_leafrange.as<int2>() : nullptr);
             sq_tree_advance_kernel<<<1, 1, 0, c->stream>>>(lvl, cnt, L, (int) maxnodes);
             c->kernel_launches += 2;
         }
@@ -381,6 +426,7 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
         SQ_CUDA(cudaMemcpyAsync(h_lvl, lvl, sizeof(int) * (SQ_MAXLEVEL + 3), cudaMemcpyDeviceToHost, c->stream));
         SQ_CUDA(cudaMemcpyAsync(h_cnt, cnt, sizeof(int) * 4, cudaMemcpyDeviceToHost, c->stream));
         SQ_CUDA(cudaStreamSynchronize(c->stream));
+        if(h_cnt[CNT_ERR] & 4) { sq_set_error("tree build: a local particle lies in a top leaf that the domain assigns to another rank (exchange particles first)"); return SQ_ERR_ARG; }
         if(h_cnt[CNT_ERR] & 2) { sq_set_error("tree build: more than 8 particles share one 2^-21 cell"); return SQ_ERR_TREE_DEPTH; }
         if(h_cnt[CNT_ERR] & 1) {
             // forcetree.cpp:215-231: grow the pool by 1.15, give up above 3.0
@@ -404,7 +450,7 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
     for(int L = maxlevel - 1; L >= 0; L--) {
         const int ls = h_lvl[L], le = h_lvl[L + 1];
         const int g = grid_for(c, (int64_t) (le - ls) * 8, 256, 8);
-        sq_tree_moments_kernel<<<g, 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_lk.as<int4>(), ls, le);
+        sq_tree_moments_kernel<<<g, 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_lk.as<int4>(), ls, le, c->t_cl.as<double4>(), 0);
         c->kernel_launches++;
     }
     SQ_CUDA(cudaGetLastError());
@@ -413,6 +459,10 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
     SQ_CUDA(cudaMemcpyAsync(&h_root, c->t_cm.p, sizeof(h_root), cudaMemcpyDeviceToHost, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));
     c->tree_total_mass = h_root.w;
+    c->n_local_nodes = c->tree_numnodes;
+    c->n_sources = np;
+    c->let_attached = false;
+    c->walk_munit = 0;
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]); c->tm.tree_build_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]); c->tm.tree_moments_ms = ms;
@@ -424,6 +474,16 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
         info->maxlevel = maxlevel;
         info->geo_mismatch = c->geo_mismatch;
     }
+    return SQ_OK;
+}
+
+// internal top-level nodes of one level from their 8 children (force_treeupdate_pseudos, forcetree.cpp:1212-1282)
+int sq_tree_moments_top(sq_ctx * c, int ls, int le)
+{
+    if(le <= ls) return SQ_OK;
+    const int g = grid_for(c, (int64_t) (le - ls) * 8, 256, 8);
+    sq_tree_moments_kernel<<<g, 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_lk.as<int4>(), ls, le, c->t_cl.as<double4>(), 1);
+    c->kernel_launches++;
     return SQ_OK;
 }
 

@@ -418,7 +418,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
     const float INF = __int_as_float(0x7f800000);
 
     const long long ngroups = (ntargets + G - 1) / G;
-    unsigned long long st_int = 0, st_ent = 0, st_tst = 0, st_pair = 0, st_exact = 0;
+    unsigned long long st_int = 0, st_ent = 0, st_tst = 0, st_pair = 0, st_exact = 0, st_pseudo = 0;
 
     for(;;) {
         long long g = 0;
@@ -743,6 +743,9 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                 }
             }
             const int type = SQ_INFO_TYPE(L.w);
+            // a pseudo node some target opens: the reference exports that particle (gravshort2.hpp:400-411); here the
+            // sub-tree should have been imported below it - counted so that the caller can tell
+            if(open_mask && type == 2) st_pseudo += __popc(open_mask);
             // ---- opened internal nodes -> push children with the open mask (pseudo nodes are skipped: gravshort2.hpp:305-314)
             {
                 const unsigned cmk = SQ_INFO_CHILDMASK(L.w);
@@ -918,6 +921,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         st_tst += __shfl_xor_sync(SQ_FULL, st_tst, o);
         st_pair += __shfl_xor_sync(SQ_FULL, st_pair, o);
         st_exact += __shfl_xor_sync(SQ_FULL, st_exact, o);
+        st_pseudo += __shfl_xor_sync(SQ_FULL, st_pseudo, o);
     }
     if(lane == 0) {
         atomicAdd(&stats[0], st_int);
@@ -925,6 +929,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         atomicAdd(&stats[2], st_tst);
         atomicAdd(&stats[3], st_pair);
         atomicAdd(&stats[4], st_exact);
+        if(st_pseudo) atomicAdd(&stats[5], st_pseudo);
     }
 }
 
@@ -956,6 +961,10 @@ static const double h_sr_force[SQ_NGRAVTAB] = SQ_SHORTRANGE_FORCE_INIT;
 //   force + pot: row i = (force intercept, force slope, potential intercept, potential slope), rows 511.. = 0
 static int sq_walk_table(sq_ctx * c)
 {
+    // the device image only changes with (window type, Asmth) or a new raw table: keep it across walks (hierarchical
+    // sub-steps call the walk thousands of times per PM step)
+    const uint64_t sig = c->have_raw ? (0x8000000000000000ull | c->raw_serial) : (((uint64_t) c->par.WindowType << 56) ^ (uint64_t) llround(c->par.Asmth * 1e9));
+    if(c->w_table.p && c->w_table_sig == sig) return SQ_OK;
     float ft[SQ_NTAB], pt[SQ_NTAB];
     for(int i = 0; i < SQ_NTAB; i++) {
         const double u = h_sr_x[i] * 0.5 / c->par.Asmth;
@@ -982,8 +991,9 @@ static int sq_walk_table(sq_ctx * c)
         h.fp[i] = make_float4((float) ((double) ft[i] - (double) i * (double) fsf), fsf, (float) ((double) pt[i] - (double) i * (double) fsp), fsp);
     }
     SQ_TRY(c->w_table.reserve(sizeof(h)));
+    // pageable source: the call returns once `h` has been staged, no stream synchronisation needed
     SQ_CUDA(cudaMemcpyAsync(c->w_table.p, &h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
-    SQ_CUDA(cudaStreamSynchronize(c->stream));
+    c->w_table_sig = sig;
     return SQ_OK;
 }
 
@@ -1044,7 +1054,7 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     }
     // scaled system of the FP32 tiers: 1 length unit = one step of the split table, 1 mass unit = mean tree particle
     P.s = 1.0 / (cell * table_dx);
-    const double munit = (c->tree_total_mass > 0 && c->tree_np > 0) ? c->tree_total_mass / (double) c->tree_np : 1.0;
+    const double munit = c->walk_munit > 0 ? c->walk_munit : ((c->tree_total_mass > 0 && c->tree_np > 0) ? c->tree_total_mass / (double) c->tree_np : 1.0);
     P.minv = 1.0 / munit;
     P.Ka = P.G * munit * P.s * P.s;
     P.Kp = munit * P.s;
@@ -1105,10 +1115,11 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
         const float * smass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
         SQ_TRY(c->w_icm.reserve(sizeof(uint4) * (size_t) (c->tree_numnodes + 1)));
         SQ_TRY(c->w_icl.reserve(sizeof(uint4) * (size_t) (c->tree_numnodes + 1)));
-        SQ_TRY(c->w_ipart.reserve(sizeof(uint4) * (size_t) (c->tree_np + 1)));
+        const int64_t nsrc = c->let_attached ? c->n_sources : c->tree_np;      // local + imported particles
+        SQ_TRY(c->w_ipart.reserve(sizeof(uint4) * (size_t) (nsrc + 1)));
         sq_walk_prep_nodes_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), (long long) c->tree_numnodes,
                 c->w_icm.as<uint4>(), c->w_icl.as<uint4>(), P.qinv, P.s, P.minv);
-        sq_walk_prep_parts_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(spos, smass, (long long) c->tree_np, c->w_ipart.as<uint4>(), P.qinv, P.minv);
+        sq_walk_prep_parts_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(spos, smass, (long long) nsrc, c->w_ipart.as<uint4>(), P.qinv, P.minv);
         c->kernel_launches += 2;
         SQ_CUDA(cudaGetLastError());
         int rc;
@@ -1133,6 +1144,7 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
         stats->nodes_tested = (int64_t) h_stats[2];
         stats->pair_tests = (int64_t) h_stats[3];
         stats->exact_tests = (int64_t) h_stats[4];
+        stats->pseudo_opened = (int64_t) h_stats[5];
         stats->kernel_ms = ms;
     }
     // TreeUseBH > 1: Barnes-Hut on the first call only (gravshort-tree2.cpp:170-171)

@@ -34,6 +34,19 @@ def _setup(ng, nmesh):
     return sq, pos, mass, par, P, opar
 
 
+def reachable_nodes(nodes, firstnode):
+    """number of nodes reachable from the root (the reference's numnodes also counts unused thread-cache slots)."""
+    frontier = np.array([0], np.int64)
+    tot = 0
+    while len(frontier):
+        tot += len(frontier)
+        nd = nodes[frontier]
+        inner = nd[((nd["flags"] >> 3) & 3) == 1]
+        ch = inner["suns"].reshape(-1)
+        frontier = ch[ch >= 0].astype(np.int64) - firstnode
+    return tot
+
+
 def _assert_parity(a, r, what):
     e = rel_err(a, r)
     med, p999 = float(np.median(e)), float(np.percentile(e, 99.9))
@@ -87,7 +100,7 @@ def test_baseline_config_against_reference_build(ng, nmesh):
     # 3. topology: canonical cells + leaf membership by ID, moments 1e-12
     cells, parts, moms = canonical_tree(nodes, first, ids, box)
     rcells, rparts, rmoms = canonical_tree(rnodes, rfirst, rids, box)
-    assert info.numnodes == len(rnodes)
+    assert info.numnodes == len(rcells)          # reachable nodes (the reference's numnodes also counts unused cache slots)
     assert np.array_equal(cells, rcells) and np.array_equal(parts, rparts)
     assert (np.abs(moms - rmoms) / np.abs(rmoms).max(axis=0)).max() < 1e-12
     # 4. interaction counts: the reference's exactly, both criteria
@@ -139,7 +152,9 @@ def test_config2_full_size_sample_against_reference_build():
         R.ref_sort_particles()
         _, _, rids = r_sorted_particles()
         inv = (rids - 1).astype(np.int64)                                  # reference sorted position -> upload index
-        rnn = R.ref_tree_build(c_dbl(0.9), None)
+        rnodes, rfirst, _ = r_tree(0.9)
+        rnn = reachable_nodes(rnodes, rfirst)
+        del rnodes
         where = np.zeros(n, np.int64); where[inv] = np.arange(n)           # upload index -> reference sorted position
         ract = np.ascontiguousarray(where[act].astype(np.int32))
         racc0 = np.zeros((n, 3)); cnt0 = np.zeros(len(ract), np.int64)
