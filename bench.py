@@ -224,11 +224,32 @@ def run_reference_arm(args):
 
 
 # ---------------------------------------------------------------------------------------------- multi-GPU
+def torch_topleaf(dom, keys):
+    """domain_get_topleaf (domain.h:68-75) for a device tensor of keys (int64 view of the 63-bit keys)."""
+    import torch
+    dev = keys.device
+    start = torch.from_numpy(dom.topnodes["StartKey"].astype(np.int64)).to(dev)
+    daughter = torch.from_numpy(dom.topnodes["Daughter"].astype(np.int64)).to(dev)
+    shift = torch.from_numpy(dom.topnodes["Shift"].astype(np.int64)).to(dev)
+    leaf = torch.from_numpy(dom.topnodes["Leaf"].astype(np.int64)).to(dev)
+    no = torch.zeros_like(keys)
+    for _ in range(22):
+        d = daughter[no]
+        live = d >= 0
+        if not bool(live.any()):
+            break
+        sub = (keys - start[no]) >> (shift[no] - 3).clamp(min=0)
+        no = torch.where(live, d + sub, no)
+    return leaf[no]
+
+
 def run_dist(args, rank, local_rank, world):
-    """N > 1: ONE domain-decomposed problem (not replicas): ~256^3 particles per GPU of a global Zel'dovich box, every
-    rank owning a consecutive range of the global Peano-Hilbert order (what the reference's domain decomposition hands
-    the path).  Step = shenqi_b200.dist.DistGravity: local sort, all-gather of the sorted ranges, global tree, walk of
-    the rank's own targets; PM on x-slabs with all-to-all routing/transposes.  NCCL over NVLink."""
+    """N > 1: ONE domain-decomposed problem (not replicas): ~256^3 particles per GPU of a global box.  Partitioning = the
+    reference's: a top tree over Peano-Hilbert key ranges whose leaves are cut into one contiguous, equal-cost segment per
+    rank (sq_domain_from_histogram; cost = particle count, or the measured interaction cost with --balance cost).
+    Step = shenqi_b200.dist.DistGravity.step: local sort, tree under the domain's top nodes, top-leaf moment all-reduce,
+    import of the reachable remote sub-trees (raw NCCL inside the library), walk of the local particles; PM on x-slabs with
+    all-to-all routing / transposes on a second stream and communicator underneath the tree chain."""
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
@@ -237,40 +258,146 @@ def run_dist(args, rank, local_rank, world):
         del os.environ["NCCL_DEBUG"]
     dist.init_process_group("nccl", device_id=dev)
     import shenqi_b200 as sq
-    from shenqi_b200.ics import zeldovich_torch, rho0, G_INTERNAL
+    from shenqi_b200.ics import zeldovich_torch, clustered_torch, rho0, G_INTERNAL
     from shenqi_b200.dist import DistGravity, CudaBackend, Comm
 
     ngrid = args.ngrid if args.ngrid != 256 else DIST_NGRID.get(world, int(round(256 * world ** (1 / 3.) / 8)) * 8)
     nmesh = args.nmesh or 2 * ngrid
     W = max(args.warmup, 3)
-    box = 1000.0 * ngrid
+    clustered = args.ics == "clustered"
+    box = args.box if args.box > 0 else (50000.0 * ngrid / 512 if clustered else 1000.0 * ngrid)   # C3: 512^3 in 50 Mpc/h
     P = sq.Params.defaults(box, nmesh, (box / ngrid) / 30., G=G_INTERNAL, rho0=rho0(), TreeRcut=6.0, TreeUseBH=1)
-    B = CudaBackend(P, local_rank)
-    B.glob.set_group_width(args.group_width)
-    # the PM exchanges get their own communicator so that DistGravity.step() can run them underneath the tree's
+    # the library's own communicator: ncclGetUniqueId on rank 0, handed to the others (MPI_Bcast in the reference's host)
+    idt = torch.zeros(sq.api.NCCL_UNIQUE_ID_BYTES, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        idt.copy_(torch.from_numpy(sq.comm_unique_id()))
+    dist.broadcast(idt, 0)
+    B = CudaBackend(P, local_rank, nccl_id=idt.cpu().numpy(), rank=rank, nranks=world)
+    B.tree.set_group_width(args.group_width)
     D = DistGravity(B, Comm(), profile=False, comm_pm=Comm(dist.new_group()))
-    fp32_peak = B.glob.measure_fp32_peak()
+    fp32_peak = B.tree.measure_fp32_peak()
     hbm_peak, peak_src = read_peaks()
 
-    # ---- set-up (untimed): global ICs on every GPU, domain = equal-count range of the global PH order, shuffled
-    pos_all, mass_all = zeldovich_torch(ngrid, box, dev)
-    ntot = pos_all.shape[0]
-    srt = B.sort_local(pos_all, mass_all)
-    lo, hi = rank * ntot // world, (rank + 1) * ntot // world
-    g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
-    mine = srt["perm"][lo:hi][torch.randperm(hi - lo, device=dev, generator=g)]
-    pos = pos_all[mine].contiguous(); mass = mass_all[mine].contiguous()
-    del pos_all, mass_all, srt, mine
-    n = pos.shape[0]
-    torch.cuda.empty_cache()
+    def allmax(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    # bootstrap |a_old| with a Barnes-Hut pass + PM, as the reference starts (gravshort-tree2.cpp:170-171)
-    a0, _, _ = D.tree_force(pos, mass)
-    o4 = D.pm_force(pos, mass)
-    oldacc = ((a0 + o4[:, 1:4]).norm(dim=1) / G_INTERNAL).contiguous()
-    del a0, o4
-    P.TreeUseBH = 0
-    B.set_params(P)
+    def allmin(x):
+        return -allmax(-x)
+
+    def allsum(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- set-up (untimed): global ICs on every GPU (a base realisation, periodically tiled T^3 times for the sizes that no
+    # single GPU can generate: 1024^3 = 2^3 tiles of a 512^3 box); domain from the key histogram; every rank keeps the
+    # particles the domain gives it (what the reference's domain exchange leaves on a rank)
+    T = max(1, args.tile)
+    nbase, bbox = ngrid // T, box / T
+    if clustered:
+        base_pos, base_mass, ics_tag = clustered_torch(nbase, bbox, dev, frac=args.clustered_frac)
+    else:
+        base_pos, base_mass = zeldovich_torch(nbase, bbox, dev)
+        ics_tag = "zeldovich rms 0.2 spacings, seed 181170"
+    if T > 1:
+        ics_tag += ", %d^3 base realisation tiled %d^3 times" % (nbase, T)
+    ntot = base_pos.shape[0] * T ** 3
+    level = args.domain_level
+
+    def tiles():
+        for t in range(T ** 3):
+            off = torch.tensor([(t // (T * T)) * bbox, ((t // T) % T) * bbox, (t % T) * bbox], dtype=torch.float64, device=dev)
+            pt = base_pos if T == 1 else (base_pos + off)
+            kt = torch.empty(pt.shape[0], dtype=torch.int64, device=dev)
+            B.tree.keys_device(pt.data_ptr(), pt.shape[0], kt.data_ptr())
+            yield t, pt, kt
+
+    def make_domain(cost_tiles=None):
+        cnt = torch.zeros(8 ** level, dtype=torch.int64, device=dev)
+        cst = None if cost_tiles is None else torch.zeros(8 ** level, dtype=torch.float64, device=dev)
+        for t, pt, kt in tiles():
+            cell = kt >> (63 - 3 * level)
+            cnt += torch.bincount(cell, minlength=8 ** level)
+            if cst is not None:
+                cst += torch.bincount(cell, weights=cost_tiles[t], minlength=8 ** level)
+        return sq.domain_from_histogram(cnt.cpu().numpy(), world, args.overdecomposition, cost=None if cst is None else cst.cpu().numpy())
+
+    def take(dom):
+        task = torch.from_numpy(dom.topleaves["Task"].astype(np.int64)).to(dev)
+        sel, ps, ms = [], [], []
+        for t, pt, kt in tiles():
+            mine = torch.nonzero(task[torch_topleaf(dom, kt)] == rank).flatten()
+            sel.append(mine + t * base_pos.shape[0]); ps.append(pt[mine]); ms.append(base_mass[mine])
+        mine, pos, mass = torch.cat(sel), torch.cat(ps), torch.cat(ms)
+        g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
+        sh = torch.randperm(mine.shape[0], device=dev, generator=g)
+        return mine[sh], pos[sh].contiguous(), mass[sh].contiguous()
+
+    def bootstrap(pos, mass):
+        # |a_old| from a Barnes-Hut pass + PM, as the reference starts (gravshort-tree2.cpp:170-171)
+        P.TreeUseBH = 1
+        B.set_params(P)
+        a0, _, st0 = D.tree_force_let(pos, mass)
+        o4 = D.pm_force(pos, mass)
+        oldacc = ((a0 + o4[:, 1:4]).norm(dim=1) / G_INTERNAL).contiguous()
+        P.TreeUseBH = 0
+        B.set_params(P)
+        return a0, oldacc, st0
+
+    dom = make_domain()
+    B.set_domain(dom)
+    mine, pos, mass = take(dom)
+    a0, oldacc, st0 = bootstrap(pos, mass)
+    balance = {"by": "particle count"}
+    if args.balance == "cost":
+        # the reference balances the measured work (GravCost, domain.cpp:452-527): one relative-criterion walk, its
+        # per-particle interaction cost summed per histogram cell, new segments of equal cost, particles re-dealt
+        D.tree_force_let(pos, mass, oldacc)
+        cost_all = torch.zeros(ntot, dtype=torch.float32, device=dev)
+        cmine = torch.empty(pos.shape[0], dtype=torch.float32, device=dev)
+        B.tree.walk_particle_cost(cmine.data_ptr())
+        cost_all[mine] = cmine
+        dist.all_reduce(cost_all)
+        nb = base_pos.shape[0]
+        dom = make_domain([cost_all[t * nb:(t + 1) * nb].double() for t in range(T ** 3)])
+        B.set_domain(dom)
+        del cost_all, cmine
+        mine, pos, mass = take(dom)
+        a0, oldacc, st0 = bootstrap(pos, mass)
+        balance = {"by": "interaction cost of the previous walk"}
+    n = pos.shape[0]
+
+    # ---- parity against ONE rank on the same domain (rank 0, untimed): Barnes-Hut pass, interaction totals equal, |da|/|a|
+    verify = None
+    if args.verify and T == 1 and ntot <= 200000000:
+        pos_all, mass_all = base_pos, base_mass
+        tot_bh = allsum(float(st0.interactions))
+        if rank == 0:
+            d1 = sq.Domain(dom.topnodes.copy(), dom.topleaves.copy(), np.array([(0, dom.ntopleaves)], sq.TASK_DTYPE))
+            d1.topleaves["Task"] = 0
+            torch.cuda.synchronize()
+            c1 = sq.Context(local_rank)
+            P.TreeUseBH = 1
+            c1.set_params(P)
+            c1.upload_particles_device(pos_all.data_ptr(), mass_all.data_ptr(), ntot)
+            c1.ph_sort(); c1.domain_set(d1); c1.tree_build_dist()
+            st1 = c1.grav_short_tree_device()
+            a1 = torch.empty((ntot, 3), dtype=torch.float64, device=dev)
+            c1.download_accel_device(a1.data_ptr())
+            torch.cuda.synchronize()
+            e = ((a0 - a1[mine]).norm(dim=1) / a1[mine].norm(dim=1).clamp(min=1e-300))
+            verify = {"criterion": "Barnes-Hut pass of the bootstrap", "interactions_all_ranks": int(tot_bh), "interactions_one_rank": int(st1.interactions),
+                      "equal": bool(int(tot_bh) == int(st1.interactions)), "rank0_rel_err_median": float(e.median()), "rank0_rel_err_max": float(e.max())}
+            c1.close()
+            del a1
+            P.TreeUseBH = 0
+            assert verify["equal"], verify
+        dist.barrier()
+    del base_pos, base_mass, a0
+    pos_all = mass_all = None
+    torch.cuda.empty_cache()
 
     def step():
         return D.step(pos, mass, oldacc)
@@ -278,16 +405,6 @@ def run_dist(args, rank, local_rank, world):
     def barrier():
         dist.barrier()
         torch.cuda.synchronize()
-
-    def allmax(x):
-        t = torch.tensor([x], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def allsum(x):
-        t = torch.tensor([x], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
 
     for _ in range(W):
         step()
@@ -297,74 +414,90 @@ def run_dist(args, rank, local_rank, world):
     D.stage_ms()
     step()
     phases = {k: round(v, 3) for k, v in D.stage_ms().items()}
+    let = D.let_info
     D.profile = False
     step()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    B.loc.reset_timings(); B.glob.reset_timings()
+    B.loc.reset_timings(); B.tree.reset_timings(); B.pmc.reset_timings()
     D.comm.bytes_sent = 0
+    if D.comm_pm is not None:
+        D.comm_pm.bytes_sent = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    walk_ms, inter, entries, tb_ms = [], [], [], []
+    walk_ms, inter, entries, pseudo = [], [], [], 0
     for _ in range(args.steps):
         _, _, _, st = step()
-        walk_ms.append(st.kernel_ms); inter.append(st.interactions); entries.append(st.list_entries)
-        tg = B.glob.timings()
-        tb_ms.append(tg.tree_build_ms + tg.tree_moments_ms)
+        walk_ms.append(st.kernel_ms); inter.append(st.interactions); entries.append(st.list_entries); pseudo += st.pseudo_opened
     e1.record()
     barrier()
     dt = allmax(e0.elapsed_time(e1) * 1e-3)
-    launches = B.loc.timings().kernel_launches + B.glob.timings().kernel_launches
+    launches = B.loc.timings().kernel_launches + B.tree.timings().kernel_launches + B.pmc.timings().kernel_launches
     clocks = sampler.stop()
-    sent = D.comm.bytes_sent / args.steps
+    sent = (D.comm.bytes_sent + (D.comm_pm.bytes_sent if D.comm_pm is not None else 0)) / args.steps + let.bytes_sent
     ms_per_step = 1e3 * dt / args.steps
     total_inter = allsum(float(np.mean(inter)))
-    wms_max = allmax(float(np.mean(walk_ms)))
     wms_mine = float(np.mean(walk_ms))
+    wms_max, wms_min = allmax(wms_mine), allmin(wms_mine)
     achieved_tf = float(np.mean(inter)) * FLOP_PER_INTERACTION / (wms_mine * 1e-3) / 1e12     # rank 0's kernel against its own SMs
-    numnodes = int(D.tree_info.numnodes)
+    assert allsum(float(pseudo)) == 0, "a pseudo node was opened without an import below it"
+    mem = torch.cuda.mem_get_info(dev)
+    mem_used_max = allmax(float(mem[1] - mem[0]))
 
     # end to end: host buffers in, host buffers out, copies inside the timed region
-    hpos, hmass, hold = pos.cpu().pin_memory(), mass.cpu().pin_memory(), oldacc.cpu().pin_memory()
-    hacc = torch.empty((n, 3), dtype=torch.float64).pin_memory(); hpot = torch.empty(n, dtype=torch.float64).pin_memory()
-    hpm = torch.empty((n, 4), dtype=torch.float64).pin_memory()
+    de, e2e_steps = float("nan"), 1
+    if not args.no_e2e:
+        hpos, hmass, hold = pos.cpu().pin_memory(), mass.cpu().pin_memory(), oldacc.cpu().pin_memory()
+        hacc = torch.empty((n, 3), dtype=torch.float64).pin_memory(); hpot = torch.empty(n, dtype=torch.float64).pin_memory()
+        hpm = torch.empty((n, 4), dtype=torch.float64).pin_memory()
 
-    def e2e_step():
-        dp, dm, do = hpos.to(dev, non_blocking=True), hmass.to(dev, non_blocking=True), hold.to(dev, non_blocking=True)
-        a, p, o, st = D.step(dp, dm, do, pm_host_out=hpm)
-        hacc.copy_(a, non_blocking=True); hpot.copy_(p, non_blocking=True)
-        torch.cuda.synchronize()
+        def e2e_step():
+            dp, dm, do = hpos.to(dev, non_blocking=True), hmass.to(dev, non_blocking=True), hold.to(dev, non_blocking=True)
+            a, p, o, st = D.step(dp, dm, do, pm_host_out=hpm)
+            hacc.copy_(a, non_blocking=True); hpot.copy_(p, non_blocking=True)
+            torch.cuda.synchronize()
 
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(2, min(args.steps, 5))
-    for _ in range(e2e_steps):
         e2e_step()
-    barrier()
-    de = allmax(time.perf_counter() - t0)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(2, min(args.steps, 5))
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        de = allmax(time.perf_counter() - t0)
     ntot_all = int(allsum(float(n)))
+    n_max, n_min = int(allmax(float(n))), int(allmin(float(n)))
+    imp_p_max, imp_n_max = int(allmax(float(let.imported_particles))), int(allmax(float(let.imported_nodes)))
 
+    workload_name = ("clustered-%d^3-box%gkpc-nmesh%d (%s)" % (ngrid, box, nmesh, ics_tag)) if clustered else "zeldovich-%d^3-nmesh%d-z9" % (ngrid, nmesh)
     line = {"metric": "short-range gravity particles/s", "value": ntot_all / (dt / args.steps), "unit": "particles/s", "n_gpus": world,
             "steps": args.steps, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 pair math, f64 accumulation/tests", "data": "synthetic",
-            "config": {"workload": "zeldovich-%d^3-nmesh%d-z9 domain-decomposed over %d GPUs (%.3f x 256^3 particles per GPU)" % (ngrid, nmesh, world, n / 256. ** 3),
-                       "particles": ntot_all, "particles_per_gpu": n, "Nmesh": nmesh, "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5,
-                       "group_width": args.group_width, "parallelism": "PH-range domains, replicated global tree, x-slab PM (PM chain on a second stream + communicator underneath the tree's all-gather and build)",
-                       "l2": "inputs_exceed_l2 (particle arrays %.0f MB per GPU)" % (ntot_all * 36 / 1e6)},
+            "config": {"workload": "%s domain-decomposed over %d GPUs (%.3f x 256^3 particles per GPU)" % (workload_name, world, ntot_all / world / 256. ** 3),
+                       "particles": ntot_all, "particles_per_gpu_min_max": [n_min, n_max], "Nmesh": nmesh, "ErrTolForceAcc": 0.002, "TreeRcut": 6.0, "Asmth": 1.5,
+                       "group_width": args.group_width,
+                       "parallelism": "top tree over PH key ranges (%d top nodes, %d top leaves, %s per rank), own sub-trees + imported boundary sub-trees (raw NCCL in the library), x-slab PM on a second stream + communicator"
+                                      % (len(dom.topnodes), dom.ntopleaves, "/".join(str(int(t["EndLeaf"] - t["StartLeaf"])) for t in dom.tasks)),
+                       "balance": balance,
+                       "l2": "inputs_exceed_l2 (particle arrays %.0f MB per GPU)" % (n * 36 / 1e6)},
             "interactions_per_s": total_inter / (wms_max * 1e-3), "interactions_per_particle": total_inter / ntot_all,
             "walk_particles_per_s": ntot_all / (wms_max * 1e-3),
-            "stage_ms": {"walk_ms_max_over_ranks": wms_max, "walk_ms_rank0": wms_mine, "global_tree_build_ms_rank0": float(np.mean(tb_ms)),
-                         "other_ms (local sort, exchanges, PM)": ms_per_step - wms_max - float(np.mean(tb_ms)),
-                         "phases_rank0_ms (one untimed step run sequentially, CUDA events)": phases},
-            "exchange_bytes_sent_per_step_rank0": int(sent), "tree_nodes": numnodes,
+            "stage_ms": {"walk_ms_max_over_ranks": wms_max, "walk_ms_min_over_ranks": wms_min, "walk_max_over_min": wms_max / wms_min, "walk_ms_rank0": wms_mine,
+                         "other_ms (local sort, tree build, exchanges, PM)": ms_per_step - wms_max,
+                         "phases_rank0_ms (one untimed step run sequentially, CUDA events)": phases,
+                         "tree_build_dist_rank0_ms": {"local_build": let.build_ms, "moments_exchange": let.moments_exchange_ms, "mark+pack": let.let_mark_ms,
+                                                      "import_exchange": let.let_exchange_ms, "attach": let.let_attach_ms}},
+            "memory": {"per_gpu": "O(N/P + boundary)", "local_particles_max": n_max, "imported_particles_max": imp_p_max, "imported_nodes_max": imp_n_max,
+                       "import_fraction_max": imp_p_max / float(max(1, n_max)), "local_nodes_rank0": int(let.local_nodes), "device_bytes_in_use_max": int(mem_used_max)},
+            "exchange_bytes_sent_per_step_rank0": int(sent), "tree_nodes": int(D.tree_info.numnodes),
+            "parity_vs_one_rank": verify,
             "roofline": {"bound": "fp32", "kernel": "sq_walk_kernel", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": achieved_tf / fp32_peak if fp32_peak > 0 else None, "traffic": None, "flop_per_interaction": FLOP_PER_INTERACTION,
                          "peak_source": "FFMA microbenchmark in this run (sq_measure_fp32_peak), rank 0",
                          "lane_efficiency": float(np.mean(inter)) / float(max(1, np.mean(entries) * 32))},
-            "e2e": {"value": ntot_all / (de / e2e_steps), "unit": "particles/s", "h2d_bytes_per_step": int(n * (24 + 4 + 8)) * world,
-                    "d2h_bytes_per_step": int(n * (24 + 8 + 32)) * world, "ms_per_step": 1e3 * de / e2e_steps},
+            "e2e": None if args.no_e2e else {"value": ntot_all / (de / e2e_steps), "unit": "particles/s", "h2d_bytes_per_step": int(ntot_all * (24 + 4 + 8)),
+                    "d2h_bytes_per_step": int(ntot_all * (24 + 8 + 32)), "ms_per_step": 1e3 * de / e2e_steps},
             "gpu_launches": int(launches), "clocks": clocks}
     if rank == 0:
         print(json.dumps(line))
@@ -384,6 +517,15 @@ def main():
     ap.add_argument("--cpu-ngrid", type=int, default=64)
     ap.add_argument("--group-width", type=int, default=32)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--ics", default="zeldovich", choices=["zeldovich", "clustered"], help="N > 1: clustered = BASELINE config 3 (512^3 in a 50 Mpc/h box at N = 8)")
+    ap.add_argument("--clustered-frac", type=float, default=0.5, help="fraction of the particles in Hernquist halos (shenqi_b200.ics.clustered)")
+    ap.add_argument("--box", type=float, default=0.0, help="box size in kpc/h (default: 1 Mpc/h mean spacing; clustered: 50 Mpc/h x Ngrid / 512)")
+    ap.add_argument("--balance", default="count", choices=["count", "cost"], help="N > 1: cut the top leaves into segments of equal particle count or equal measured interaction cost")
+    ap.add_argument("--domain-level", type=int, default=5, help="N > 1: histogram level of the domain's top tree (8^level cells)")
+    ap.add_argument("--overdecomposition", type=int, default=4, help="DomainOverDecompositionFactor (gadget/params.cpp:84)")
+    ap.add_argument("--tile", type=int, default=1, help="N > 1: build the box from tile^3 periodic copies of an (ngrid / tile)^3 realisation (1024^3 = --ngrid 1024 --tile 2)")
+    ap.add_argument("--no-e2e", action="store_true", help="N > 1: skip the host-buffer leg (e.g. 1024^3: 13 GB of pinned memory per rank)")
+    ap.add_argument("--no-verify", dest="verify", action="store_false", help="N > 1: skip the one-rank parity run on rank 0")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -162,6 +162,11 @@ int sq_tree_walk(sq_ctx * ctx, const int32_t * active, int64_t nactive, double *
 /* Same, results left on the device (benchmark / chained use); fetch with sq_download_accel. */
 int sq_tree_walk_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
 int sq_download_accel(sq_ctx * ctx, double * accel, double * potential);
+/* Same into DEVICE arrays (upload order), queued on the context's stream, no host synchronisation. */
+int sq_download_accel_device(sq_ctx * ctx, double * accel, double * potential);
+/* Work estimate per particle of the last walk, upload order: interactions of its target group / group width (what the
+ * reference keeps as GravCost for the domain balance, domain.cpp:452-527).  cost: host or device float[N]. */
+int sq_walk_particle_cost(sq_ctx * ctx, float * cost);
 
 /* ---- particle mesh --------------------------------------------------------------------------- */
 /* CIC paint -> r2c FFT -> potential + 3 force transfer functions -> 4 c2r FFTs -> fused CIC readout.
@@ -269,6 +274,8 @@ int sq_domain_from_histogram(const int64_t * count, const double * cost, int lev
 /* Histogram of this rank's uploaded particles over the level-`level` cells, summed over ranks (ncclAllReduce when the
  * context is distributed); weights = per-particle cost in upload order (device or host pointer) or NULL. */
 int sq_domain_histogram(sq_ctx * ctx, int level, int64_t * count, double * cost, const float * weights);
+/* PEANO() keys (libgadget/utils/peano.h:15-21) of n positions that are already on the device; keys: device uint64[n]. */
+int sq_keys_device(sq_ctx * ctx, const double * pos, int64_t n, uint64_t * keys);
 /* Rank that owns each uploaded particle under the installed domain (domain_get_topleaf, domain.h:68-75); host array. */
 int sq_domain_owner(sq_ctx * ctx, int32_t * owner);
 /* Collective.  sq_tree_build under the installed domain: local sub-trees + top nodes, moment exchange, import of the

@@ -156,7 +156,8 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device",
            "sq_gravity_timebins_device", "sq_timebin_pushdown_device",
            "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram",
-           "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count"]
+           "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count", "sq_download_accel_device",
+           "sq_walk_particle_cost", "sq_keys_device"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
@@ -291,6 +292,10 @@ class Context:
         self._check(self.L.sq_domain_histogram(self._ctx, c_int(level), _p(count), _p(cost), _p(w)))
         return count, cost
 
+    def keys_device(self, pos_ptr, n, keys_ptr):
+        """PEANO keys of device positions into a device uint64 array (queued on the context's stream)."""
+        self._check(self.L.sq_keys_device(self._ctx, ctypes.c_void_p(pos_ptr), c_i64(n), ctypes.c_void_p(keys_ptr)))
+
     def domain_owner(self):
         owner = np.zeros(self.n, np.int32)
         self._check(self.L.sq_domain_owner(self._ctx, _p(owner)))
@@ -347,6 +352,22 @@ class Context:
         accel = np.zeros((self.n, 3)); pot = np.zeros(self.n)
         self._check(self.L.sq_download_accel(self._ctx, _p(accel), _p(pot)))
         return accel, pot
+
+    def download_accel_device(self, accel_ptr, pot_ptr=None):
+        self._check(self.L.sq_download_accel_device(self._ctx, ctypes.c_void_p(accel_ptr), ctypes.c_void_p(pot_ptr)))
+
+    def walk_particle_cost(self, out_ptr=None):
+        """per-particle work estimate of the last walk (upload order): numpy array, or written to a device pointer."""
+        if out_ptr is not None:
+            self._check(self.L.sq_walk_particle_cost(self._ctx, ctypes.c_void_p(out_ptr)))
+            return None
+        cost = np.zeros(self.n, np.float32)
+        self._check(self.L.sq_walk_particle_cost(self._ctx, _p(cost)))
+        return cost
+
+    def set_oldacc_device(self, oldacc_ptr):
+        """oldacc[i] (upload order) from a DEVICE array; call before ph_sort (the sort gathers it)."""
+        self._check(self.L.sq_set_oldacc(self._ctx, ctypes.c_void_p(oldacc_ptr)))
 
     # ---- gravpm_force
     def gravpm_force(self):

@@ -114,7 +114,7 @@ void sq_ctx_destroy(sq_ctx * c)
                        &c->w_counter, &c->w_icm, &c->w_icl, &c->w_ipart, &c->pm_real[0], &c->pm_real[1], &c->pm_real[2], &c->pm_real[3], &c->pm_cplx[0], &c->pm_cplx[1],
                        &c->pm_cplx[2], &c->pm_cplx[3], &c->pm_out, &c->slab_tab, &c->route_tmp, &c->oldacc_tmp, &c->stage_a, &c->stage_b, &c->act_tmp, &c->step_tmp,
                        &c->d_leafrange, &c->d_topnodes, &c->d_topleaves, &c->d_treenode, &c->t_top, &c->let_leafdata, &c->let_mask, &c->let_scan_n, &c->let_scan_p,
-                       &c->let_roots, &c->let_send, &c->let_recv, &c->let_boxes};
+                       &c->let_roots, &c->let_send, &c->let_recv, &c->let_boxes, &c->w_gcost};
     for(sq_buf * b : bufs) b->release();
     for(int i = 0; i < 16; i++) if(c->ev[i]) cudaEventDestroy(c->ev[i]);
     for(int i = 0; i < 4; i++) if(c->evx[i]) cudaEventDestroy(c->evx[i]);
@@ -221,7 +221,7 @@ int sq_upload_particles_aos(sq_ctx * c, const void * base, int64_t n, const sq_a
 int sq_set_oldacc(sq_ctx * c, const double * oldacc)
 {
     if(!c || !oldacc) { sq_set_error("sq_set_oldacc: null argument"); return SQ_ERR_ARG; }
-    SQ_CUDA(cudaMemcpyAsync(c->oldacc_in.p, oldacc, sizeof(double) * (size_t) c->n, cudaMemcpyHostToDevice, c->stream));
+    SQ_CUDA(cudaMemcpyAsync(c->oldacc_in.p, oldacc, sizeof(double) * (size_t) c->n, cudaMemcpyDefault, c->stream));   // host or device pointer
     SQ_CUDA(cudaStreamSynchronize(c->stream));
     if(c->sorted) SQ_TRY(sq_gather_run(c));
     return sq_sync(c);
@@ -337,6 +337,20 @@ int sq_download_accel(sq_ctx * c, double * accel, double * potential)
         SQ_CUDA(cudaMemcpyAsync(potential, c->w_out_pot.p, sizeof(double) * (size_t) n, cudaMemcpyDeviceToHost, c->stream));
     }
     return sq_sync(c);
+}
+
+// results of the last walk into the caller's DEVICE arrays, upload order (only the walked targets are written)
+int sq_download_accel_device(sq_ctx * c, double * accel, double * potential)
+{
+    if(!c || !c->walk_done) { sq_set_error("sq_download_accel_device: no walk results"); return SQ_ERR_ARG; }
+    const int64_t n = c->n;
+    const bool all = c->walk_ntargets == n;
+    const uint32_t * targets = all ? nullptr : c->w_targets.as<uint32_t>();
+    const long long m = c->walk_ntargets;
+    if(accel && m > 0) { sq_unpermute_kernel<3><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_accel.as<double>(), 3, 0, c->perm.as<uint32_t>(), targets, m, accel); c->kernel_launches++; }
+    if(potential && c->tree_full && m > 0) { sq_unpermute_kernel<1><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_pot.as<double>(), 1, 0, c->perm.as<uint32_t>(), targets, m, potential); c->kernel_launches++; }
+    SQ_CUDA(cudaGetLastError());
+    return SQ_OK;
 }
 
 int sq_tree_walk(sq_ctx * c, const int32_t * active, int64_t nactive, double * accel, double * potential, sq_walk_stats * stats)

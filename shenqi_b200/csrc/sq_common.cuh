@@ -131,6 +131,8 @@ struct sq_ctx {
 
     // ---- walk
     sq_buf w_accel, w_pot, w_stats, w_targets, w_table, w_out_accel, w_out_pot, w_counter, w_icm, w_icl, w_ipart;
+    sq_buf w_gcost;                  // interactions per target group of the last walk
+    int walk_group = 32;
     bool walk_done = false;
     int64_t walk_ntargets = 0;
 

@@ -207,3 +207,19 @@ int sq_iota(sq_ctx * c, uint32_t * v, int64_t n)
     SQ_CUDA(cudaGetLastError());
     return SQ_OK;
 }
+
+// PEANO() keys of positions that are already on the device (no context state touched except the parameter BoxSize)
+extern "C" int sq_keys_device(sq_ctx * c, const double * pos, int64_t n, uint64_t * keys)
+{
+    if(!c || !c->have_params || (n > 0 && (!pos || !keys))) { sq_set_error("sq_keys_device: bad argument (set the parameters first)"); return SQ_ERR_ARG; }
+    SQ_CUDA(cudaSetDevice(c->device));
+    SQ_TRY(sq_phtab_init());
+    if(n == 0) return SQ_OK;
+    SQ_TRY(c->t_counters.reserve(256));
+    const double box = c->par.BoxSize;
+    const double domainfac = 1.0 / (box * 1.001) * (double) (((uint64_t) 1) << 21);
+    sq_keys_kernel<false><<<sq_grid_for(c, n, 256, 8), 256, 0, c->stream>>>(pos, n, box, box / 2000, domainfac, d_phtab, keys, c->t_counters.as<int>() + 8);
+    c->kernel_launches++;
+    SQ_CUDA(cudaGetLastError());
+    return SQ_OK;
+}

@@ -275,43 +275,57 @@ __host__ __device__ __forceinline__ unsigned let_quant(double x, double qinv)
 struct let_leafdata { double cm[4]; long long lo[3], hi[3]; long long valid, pad; };     // 12 x 8 B
 static_assert(sizeof(let_leafdata) == 96, "leaf record is 12 words");
 
-__global__ void __launch_bounds__(256) let_leafdata_kernel(const sq_topleaf * __restrict__ tl, int nleaves, int myrank, const int * __restrict__ treenode,
-                                                           const int2 * __restrict__ leafrange, const double4 * __restrict__ cm, const double * __restrict__ pos,
-                                                           double qinv, let_leafdata * __restrict__ out)
+// bounding boxes: every particle finds its top leaf (the leaves' particle ranges are consecutive in the sorted order),
+// a warp reduces over the lanes that share the first lane's leaf, one set of atomics per warp and leaf
+__global__ void __launch_bounds__(256) let_leafbox_kernel(const int2 * __restrict__ leafrange, const int * __restrict__ myleaves, int nmine,
+                                                          const double * __restrict__ pos, long long n, double qinv, unsigned * __restrict__ box /* [leaf][6] */)
 {
-    __shared__ unsigned lo[3], hi[3];
-    for(int leaf = blockIdx.x; leaf < nleaves; leaf += gridDim.x) {
+    for(long long i0 = (blockIdx.x * (long long) blockDim.x + threadIdx.x) & ~31ll; i0 < n; i0 += (long long) gridDim.x * blockDim.x) {
+        const long long i = i0 + sq_lane();
+        int leaf = -1;
+        unsigned q[3] = {0, 0, 0};
+        if(i < n) {
+            // last of my leaves (sorted by first particle) whose range starts at or before i
+            int lo = 0, hi = nmine;
+            while(hi - lo > 1) { const int mid = (lo + hi) >> 1; if(leafrange[myleaves[mid]].x <= i) lo = mid; else hi = mid; }
+            leaf = myleaves[lo];
+            const int2 r = leafrange[leaf];
+            if(i < r.x || i >= (long long) r.x + r.y) leaf = -1;
+            #pragma unroll
+            for(int a = 0; a < 3; a++) q[a] = let_quant(pos[3 * i + a], qinv);
+        }
+        unsigned todo = __ballot_sync(SQ_FULL, leaf >= 0);
+        while(todo) {
+            const int lead = __ffs((int) todo) - 1;
+            const int l0 = __shfl_sync(SQ_FULL, leaf, lead);
+            const bool in = leaf == l0;
+            const unsigned grp = __ballot_sync(SQ_FULL, in);
+            #pragma unroll
+            for(int a = 0; a < 3; a++) {
+                const unsigned mn = __reduce_min_sync(SQ_FULL, in ? q[a] : 0xffffffffu), mx = __reduce_max_sync(SQ_FULL, in ? q[a] : 0u);
+                if((int) sq_lane() == lead) { atomicMin(&box[6 * l0 + a], mn); atomicMax(&box[6 * l0 + 3 + a], mx); }
+            }
+            todo &= ~grp;
+        }
+    }
+}
+
+__global__ void let_leafdata_kernel(const sq_topleaf * __restrict__ tl, int nleaves, int myrank, const int * __restrict__ treenode,
+                                    const int2 * __restrict__ leafrange, const double4 * __restrict__ cm, const unsigned * __restrict__ box,
+                                    let_leafdata * __restrict__ out)
+{
+    for(int leaf = blockIdx.x * blockDim.x + threadIdx.x; leaf < nleaves; leaf += gridDim.x * blockDim.x) {
         let_leafdata d;
         memset(&d, 0, sizeof(d));
-        const bool mine = tl[leaf].Task == myrank;
-        if(threadIdx.x < 3) { lo[threadIdx.x] = 0xffffffffu; hi[threadIdx.x] = 0u; }
-        __syncthreads();
-        int count = 0;
-        if(mine) {
-            const int2 r = leafrange[leaf];
-            count = r.y;
-            for(int k = threadIdx.x; k < r.y; k += blockDim.x) {
-                const long long p = r.x + k;
-                #pragma unroll
-                for(int a = 0; a < 3; a++) {
-                    const unsigned q = let_quant(pos[3 * p + a], qinv);
-                    atomicMin(&lo[a], q); atomicMax(&hi[a], q);
-                }
+        if(tl[leaf].Task == myrank) {
+            const double4 m = cm[treenode[leaf]];
+            d.cm[0] = m.x; d.cm[1] = m.y; d.cm[2] = m.z; d.cm[3] = m.w;
+            if(leafrange[leaf].y > 0) {
+                for(int a = 0; a < 3; a++) { d.lo[a] = box[6 * leaf + a]; d.hi[a] = box[6 * leaf + 3 + a]; }
+                d.valid = 1;
             }
         }
-        __syncthreads();
-        if(threadIdx.x == 0) {
-            if(mine) {
-                const double4 m = cm[treenode[leaf]];
-                d.cm[0] = m.x; d.cm[1] = m.y; d.cm[2] = m.z; d.cm[3] = m.w;
-                if(count > 0) {
-                    for(int a = 0; a < 3; a++) { d.lo[a] = lo[a]; d.hi[a] = hi[a]; }
-                    d.valid = 1;
-                }
-            }
-            out[leaf] = d;
-        }
-        __syncthreads();
+        out[leaf] = d;
     }
 }
 
@@ -535,9 +549,23 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
     SQ_TRY(c->let_leafdata.reserve(sizeof(let_leafdata) * (size_t) (NL + 1)));
     let_leafdata * ld = c->let_leafdata.as<let_leafdata>();
     {
-        const int g = NL < c->num_sms * 4 ? NL : c->num_sms * 4;
-        let_leafdata_kernel<<<g, 256, 0, c->stream>>>(c->d_topleaves.as<sq_topleaf>(), NL, me, c->d_treenode.as<int>(), c->d_leafrange.as<int2>(),
-                c->t_cm.as<double4>(), c->pos.as<double>(), qinv, ld);
+        // my leaves in the order of their particle ranges (= leaf order: the domain's leaves are in key order)
+        std::vector<int> mine;
+        for(int l = c->dom_tasks[me].StartLeaf; l < c->dom_tasks[me].EndLeaf; l++) mine.push_back(l);
+        sq_buf & scratch = c->let_scan_p;
+        SQ_TRY(scratch.reserve(sizeof(unsigned) * 6 * (size_t) NL + sizeof(int) * (size_t) (mine.size() + 1) + 64));
+        unsigned * d_box = scratch.as<unsigned>();
+        int * d_mine = (int *) (d_box + 6 * (size_t) NL);
+        std::vector<unsigned> init(6 * (size_t) NL);
+        for(int l = 0; l < NL; l++) for(int a = 0; a < 3; a++) { init[6 * l + a] = 0xffffffffu; init[6 * l + 3 + a] = 0u; }
+        SQ_CUDA(cudaMemcpyAsync(d_box, init.data(), sizeof(unsigned) * init.size(), cudaMemcpyHostToDevice, c->stream));
+        SQ_CUDA(cudaMemcpyAsync(d_mine, mine.data(), sizeof(int) * mine.size(), cudaMemcpyHostToDevice, c->stream));
+        if(n > 0 && !mine.empty()) {
+            let_leafbox_kernel<<<let_grid(c, n), 256, 0, c->stream>>>(c->d_leafrange.as<int2>(), d_mine, (int) mine.size(), c->pos.as<double>(), (long long) n, qinv, d_box);
+            c->kernel_launches++;
+        }
+        let_leafdata_kernel<<<let_grid(c, NL), 256, 0, c->stream>>>(c->d_topleaves.as<sq_topleaf>(), NL, me, c->d_treenode.as<int>(), c->d_leafrange.as<int2>(),
+                c->t_cm.as<double4>(), d_box, ld);
         c->kernel_launches++;
         SQ_CUDA(cudaGetLastError());
     }

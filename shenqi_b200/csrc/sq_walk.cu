@@ -391,7 +391,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
                const double * __restrict__ tpos, const float * __restrict__ tmass, const double * __restrict__ toldacc,
                const uint32_t * __restrict__ targets, long long ntargets, const float2 * __restrict__ gtab,
                double * __restrict__ accel, double * __restrict__ pot, unsigned long long * __restrict__ stats,
-               int * __restrict__ group_counter, const sq_walk_par P)
+               int * __restrict__ group_counter, unsigned * __restrict__ gcost, const sq_walk_par P)
 {
     constexpr int S = 32 / G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -426,6 +426,7 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
         g = __shfl_sync(SQ_FULL, g, 0);
         if(g >= ngroups) break;
         const long long t0 = g * G;
+        const unsigned long long st_int_before = st_int;
         const int nt = (int) ((ntargets - t0) < G ? (ntargets - t0) : G);
         const bool valid = t < nt;
         long long tidx = 0;
@@ -899,6 +900,11 @@ sq_walk_kernel(const uint4 * __restrict__ icm, const uint4 * __restrict__ icl, c
             daz += __shfl_xor_sync(SQ_FULL, daz, o);
             if(POT) dap += __shfl_xor_sync(SQ_FULL, dap, o);
         }
+        if(gcost) {
+            // interactions of this group: the work measure the domain decomposition balances (domain.cpp:452-527 uses GravCost)
+            const unsigned gi = __reduce_add_sync(SQ_FULL, (unsigned) (st_int - st_int_before));
+            if(lane == 0) gcost[g] = gi;
+        }
         if(valid && s == 0) {
             // gravshort2.hpp:88-107
             accel[3 * tidx] = dax * P.Ka;
@@ -1013,13 +1019,44 @@ static int sq_walk_launch(sq_ctx * c, const uint32_t * targets, int64_t ntargets
     sq_walk_kernel<POT, G><<<(unsigned) grid, WALK_THREADS, smem, c->stream>>>(c->w_icm.as<uint4>(), c->w_icl.as<uint4>(), c->t_lk.as<int4>(),
             c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->w_ipart.as<uint4>(), c->pos.as<double>(), c->mass.as<float>(), c->oldacc.as<double>(),
             targets, (long long) ntargets, c->w_table.as<float2>() + (POT ? TAB_ROWS + 1 : 0), c->w_accel.as<double>(), c->w_pot.as<double>(),
-            c->w_stats.as<unsigned long long>(), c->w_counter.as<int>(), P);
+            c->w_stats.as<unsigned long long>(), c->w_counter.as<int>(), c->w_gcost.as<unsigned>(), P);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
     return SQ_OK;
 }
 
 int sq_walk_group_width = 32;   // tunable: targets per warp (32, 16 or 8)
+
+// cost[upload index] = interactions of the particle's group / group width, for the targets of the last walk
+__global__ void sq_walk_cost_kernel(const unsigned * __restrict__ gcost, const uint32_t * __restrict__ targets, const uint32_t * __restrict__ perm,
+                                    long long m, int G, float * __restrict__ out)
+{
+    for(long long q = blockIdx.x * (long long) blockDim.x + threadIdx.x; q < m; q += (long long) gridDim.x * blockDim.x) {
+        const long long i = targets ? targets[q] : q;
+        out[perm[i]] = (float) gcost[q / G] / (float) G;
+    }
+}
+
+extern "C" int sq_walk_particle_cost(sq_ctx * c, float * cost)
+{
+    if(!c || !cost || !c->walk_done) { sq_set_error("sq_walk_particle_cost: no walk results"); return SQ_ERR_ARG; }
+    SQ_CUDA(cudaSetDevice(c->device));
+    const int64_t n = c->n, m = c->walk_ntargets;
+    sq_buf tmp;
+    SQ_TRY(tmp.reserve(sizeof(float) * (size_t) (n + 1)));
+    cudaError_t e = cudaMemsetAsync(tmp.p, 0, sizeof(float) * (size_t) (n + 1), c->stream);
+    if(e == cudaSuccess && m > 0) {
+        sq_walk_cost_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->w_gcost.as<unsigned>(), m == n ? nullptr : c->w_targets.as<uint32_t>(), c->perm.as<uint32_t>(),
+                (long long) m, c->walk_group, tmp.as<float>());
+        c->kernel_launches++;
+        e = cudaGetLastError();
+    }
+    if(e == cudaSuccess) e = cudaMemcpyAsync(cost, tmp.p, sizeof(float) * (size_t) n, cudaMemcpyDefault, c->stream);
+    if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    tmp.release();
+    if(e != cudaSuccess) { sq_set_error("sq_walk_particle_cost: %s", cudaGetErrorString(e)); return SQ_ERR_CUDA; }
+    return SQ_OK;
+}
 
 int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats)
 {
@@ -1104,6 +1141,8 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
     SQ_TRY(c->w_pot.reserve(sizeof(double) * (size_t) (n + 1)));
     SQ_TRY(c->w_stats.reserve(64));
     SQ_TRY(c->w_counter.reserve(64));
+    SQ_TRY(c->w_gcost.reserve(sizeof(unsigned) * (size_t) (ntargets / 8 + 2)));
+    c->walk_group = G;
     SQ_CUDA(cudaMemsetAsync(c->w_stats.p, 0, 64, c->stream));
     SQ_CUDA(cudaMemsetAsync(c->w_counter.p, 0, 64, c->stream));
     SQ_CUDA(cudaMemsetAsync(c->w_accel.p, 0, sizeof(double) * 3 * (size_t) n, c->stream));

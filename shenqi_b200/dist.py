@@ -2,7 +2,12 @@
 gloo on CPU for the tests of this host logic).  SURVEY.md section 8e.
 
 What is exchanged (and what the reference exchanges at the same place):
-  * tree: every rank sorts its own particles, the sorted (key, pos, mass) ranges are all-gathered in rank order
+  * tree, production path (`DistGravity.tree_force_let`, everything behind the C ABI with raw NCCL, sq_let.cu): the tree is
+    built under the reference's DomainDecomp - forced top-level nodes, own sub-trees, pseudo nodes - top-leaf moments are
+    all-reduced (forcetree.cpp:1155-1282) and each rank imports, once per build, the nodes and particles of remote
+    sub-trees that its particles can reach (instead of exporting boundary particles per walk, treewalk2.h:618-812);
+    memory per GPU is O(N/P + boundary).
+  * tree, replicated test mode (`tree_force`): every rank sorts its own particles, the sorted (key, pos, mass) ranges are all-gathered in rank order
     (= global Peano-Hilbert order, ranks own consecutive key ranges as after the reference's domain decomposition),
     every rank builds the whole tree and walks only its own targets.  The reference instead exchanges top-leaf
     moments (forcetree.cpp:1144-1282) and exports each boundary walk to the owner of the pseudo node and imports
@@ -207,6 +212,36 @@ class DistGravity:
         self._mark("tree:unpermute")
         return accel, pot, st
 
+    # ------------------------------------------------------------------ short-range tree force, domain-decomposed tree
+    def tree_force_let(self, pos, mass, oldacc=None, after_sort=None, before_walk=None):
+        """Like tree_force, but with the reference's partitioning: this rank's particles must be the ones the installed
+        domain (backend.set_domain) assigns to it.  Local sort, tree under the domain's top nodes, moment exchange and
+        sub-tree import (sq_tree_build_dist, NCCL inside the library), walk of the local particles.  No torch collective
+        and no host list round trip on this path."""
+        B = self.B
+        n = pos.shape[0]
+        self._mark("begin")
+        T = B.tree
+        T.upload_particles_device(pos.contiguous().data_ptr(), mass.contiguous().data_ptr(), n)
+        if oldacc is not None:
+            T.set_oldacc_device(oldacc.contiguous().data_ptr())
+        T.ph_sort()
+        self._mark("tree:local_sort")
+        self._sorted = B.sorted_views(T, n)
+        if after_sort is not None:
+            after_sort()
+        self.tree_info, self.let_info = T.tree_build_dist()
+        self._mark("tree:build+moments+import")
+        if before_walk is not None:
+            before_walk()
+        st = T.grav_short_tree_device()
+        self._mark("tree:walk")
+        accel = torch.empty((n, 3), dtype=torch.float64, device=B.device)
+        pot = torch.empty(n, dtype=torch.float64, device=B.device)
+        T.download_accel_device(accel.data_ptr(), pot.data_ptr())
+        self._mark("tree:unpermute")
+        return accel, pot, st
+
     # ------------------------------------------------------------------ particle-mesh force
     def pm_force(self, pos, mass, reuse_sorted=False, comm=None):
         """Returns out4 [n,4] = (PM potential, fx, fy, fz) for this rank's particles, in their order.
@@ -275,8 +310,9 @@ class DistGravity:
         second stream, underneath the walk.  Returns (accel, potential, out4, stats) like the two calls."""
         B = self.B
         side = getattr(B, "pm_stream", None)
+        tree_force = self.tree_force_let if getattr(B, "tree", None) is not None else self.tree_force
         if side is None or self.comm_pm is None or self.profile or self.world == 1:
-            a, p, st = self.tree_force(pos, mass, oldacc)
+            a, p, st = tree_force(pos, mass, oldacc)
             o = self.pm_force(pos, mass, reuse_sorted=True)
             if pm_host_out is not None:
                 pm_host_out.copy_(o, non_blocking=True)
@@ -299,7 +335,7 @@ class DistGravity:
             main.wait_event(box["done"])
             box["out"].record_stream(main)
 
-        a, p, st = self.tree_force(pos, mass, oldacc, after_sort=fork, before_walk=join)
+        a, p, st = tree_force(pos, mass, oldacc, after_sort=fork, before_walk=join)
         return a, p, box["out"], st
 
 
@@ -308,7 +344,9 @@ class CudaBackend:
     Two library contexts: `loc` sorts and routes this rank's own particles, `glob` holds the all-gathered set, the tree
     and the walk.  Both run on torch's current stream, so the exchanges and the kernels are ordered without host syncs."""
 
-    def __init__(self, params, device):
+    def __init__(self, params, device, nccl_id=None, rank=0, nranks=1):
+        """nccl_id (comm_unique_id() of rank 0, the same 128 bytes on every rank): also create `tree`, the context of the
+        domain-decomposed tree path, as rank `rank` of `nranks` (collective)."""
         from . import api
         self.api = api
         self.device = torch.device("cuda", device) if isinstance(device, int) else device
@@ -317,6 +355,10 @@ class CudaBackend:
         self.glob = api.Context(self.device.index)
         stream = torch.cuda.current_stream(self.device).cuda_stream
         self.loc.set_stream(stream); self.glob.set_stream(stream)
+        self.tree = None
+        if nccl_id is not None:
+            self.tree = api.Context(self.device.index, nccl_id=nccl_id, rank=rank, nranks=nranks)
+            self.tree.set_stream(stream)
         # PM kernels have their own context; DistGravity.step() moves it to `pm_stream` while the tree chain runs
         self.pmc = api.Context(self.device.index)
         self.pmc.set_stream(stream)
@@ -330,9 +372,23 @@ class CudaBackend:
         self.loc.set_params(params)
         self.glob.set_params(params)
         self.pmc.set_params(params)
+        if self.tree is not None:
+            self.tree.set_params(params)
+
+    def set_domain(self, dom):
+        self.tree.domain_set(dom)
+
+    def sorted_views(self, ctx, n):
+        A = self.api
+        # copies: the library may move its particle arrays when the imported particles are appended behind them
+        return {"pos": self._wrap(ctx.device_ptr(A.PTR_SORTED_POS)[0], (n, 3), torch.float64).clone(),
+                "mass": self._wrap(ctx.device_ptr(A.PTR_SORTED_MASS)[0], (n,), torch.float32).clone(),
+                "perm": self._wrap(ctx.device_ptr(A.PTR_SORTED_PERM)[0], (n,), torch.int32).to(torch.int64)}
 
     def close(self):
         self.loc.close(); self.glob.close(); self.pmc.close()
+        if self.tree is not None:
+            self.tree.close()
 
     def _wrap(self, ptr, shape, dtype):
         """torch view of library-owned device memory (valid until the library reallocates it)"""

@@ -118,3 +118,41 @@ def clustered(ngrid, box, halo_fraction=0.5, nhalo=None, seed=181170):
     np.mod(pos, box, out=pos)
     pos[pos >= box] = 0.0
     return pos, mass, ids
+
+
+def clustered_torch(ngrid, box, device, frac=0.5, nhalo=None, seed=181170):
+    """clustered() on a CUDA device with torch (multi-GPU benchmark set-up; torch's generator, so its own realisation):
+    Zel'dovich load with rms displacement 0.6 spacings, `frac` of the particles moved into Hernquist halos with
+    dn/dM ~ M^-1.9 centred on particles.  Returns (pos, mass, tag); tag names generator and seed for the bench line."""
+    import torch
+    pos, mass = zeldovich_torch(ngrid, box, device, rms_disp=0.6, seed=seed)
+    n = pos.shape[0]
+    g = torch.Generator(device=device)
+    g.manual_seed(seed + 1)
+    nmove = int(frac * n)
+    tag = "shenqi_b200.ics.clustered_torch: zeldovich rms 0.6 + %.2f of the particles in Hernquist halos dn/dM~M^-1.9, seed %d" % (frac, seed)
+    if nmove == 0:
+        return pos, mass, tag
+    nhalo = nhalo or max(8, n // 4096)
+    u = torch.rand(nhalo, dtype=torch.float64, device=device, generator=g)
+    mmin, mmax, al = 32.0, max(64.0, 0.02 * n), -0.9
+    hm = (mmin ** al + u * (mmax ** al - mmin ** al)) ** (1.0 / al)
+    cnt = torch.clamp(torch.floor(hm * nmove / hm.sum()), min=1).to(torch.int64)
+    cnt[-1] += nmove - int(cnt.sum())
+    if int(cnt[-1]) < 1:
+        cnt[-1] = 1
+    nmove = int(cnt.sum())
+    moved = torch.randperm(n, device=device, generator=g)[:nmove]
+    centres = pos[torch.randint(0, n, (nhalo,), device=device, generator=g)]
+    spacing = box / ngrid
+    a = 0.35 * spacing * cnt.to(torch.float64) ** (1.0 / 3)
+    hid = torch.repeat_interleave(torch.arange(nhalo, device=device), cnt)
+    q = torch.rand(nmove, dtype=torch.float64, device=device, generator=g) * 0.98
+    r = a[hid] * torch.sqrt(q) / (1.0 - torch.sqrt(q))
+    mu = 2.0 * torch.rand(nmove, dtype=torch.float64, device=device, generator=g) - 1.0
+    ph = 2.0 * np.pi * torch.rand(nmove, dtype=torch.float64, device=device, generator=g)
+    st = torch.sqrt(1.0 - mu * mu)
+    pos[moved] = centres[hid] + r[:, None] * torch.stack([st * torch.cos(ph), st * torch.sin(ph), mu], 1)
+    pos.remainder_(box)
+    pos[pos >= box] = 0.0
+    return pos, mass, tag
