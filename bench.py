@@ -302,6 +302,7 @@ def run_dist(args, rank, local_rank, world):
         base_pos, base_mass = zeldovich_torch(nbase, bbox, dev)
         ics_tag = "zeldovich rms 0.2 spacings, seed 181170"
     if T > 1:
+        base_pos.clamp_(min=bbox * 1e-9)      # no coordinate exactly on a tile boundary (= a cell face of the top levels)
         ics_tag += ", %d^3 base realisation tiled %d^3 times" % (nbase, T)
     ntot = base_pos.shape[0] * T ** 3
     level = args.domain_level

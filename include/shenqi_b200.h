@@ -151,6 +151,11 @@ int sq_tree_build(sq_ctx * ctx, const int32_t * active, int64_t nactive, sq_tree
 /* Write the tree as the reference's NODE[numnodes] image (120 B each), node numbers starting at
  * firstnode, particle numbers = sorted positions (or upload indices if upload_order != 0). */
 int sq_tree_export_nodes(sq_ctx * ctx, void * nodes, int64_t firstnode, int upload_order);
+/* Same with the caller's lastnode (= firstnode + maxnodes of its pool): the top leaves of other ranks are written as
+ * PSEUDO nodes whose suns[0] = lastnode + leaf, as force_create_node_for_topnode leaves them (forcetree.cpp:903-906). */
+int sq_tree_export_nodes_ex(sq_ctx * ctx, void * nodes, int64_t firstnode, int64_t lastnode, int upload_order);
+/* nodes of this rank's own build (what the host image holds; sub-trees imported from other ranks come on top on the device) */
+int sq_tree_local_nodes(sq_ctx * ctx, int64_t * n);
 
 /* ---- short-range walk -------------------------------------------------------------------------- */
 /* accel: N x 3 host doubles in upload order (already x G), written for active particles only.

@@ -34,6 +34,7 @@
 #include <libgadget/timestep.h>
 #include <libgadget/drift.h>
 #include <libgadget/gravshort2.hpp>
+#include <libgadget/cosmology.h>
 
 /* ---- symbols the path references but which live in reference files we do not build ---- */
 /* libgadget/timestep.cpp:78 : forward to the particle manager, no list */
@@ -387,6 +388,50 @@ double ref_grav_short_pair(int Nmesh, double Asmth, double G, double Rcut, doubl
                 accel[3 * i + j] = PartManager->Base[i].FullTreeGravAccel[j];
     }
     return dt;
+}
+
+#ifdef REF_HAVE_GRAVPM
+/* gravpm_init_periodic + gravpm_force (gravity.h:71, 86) on the loaded particles; only in builds that link a gravpm
+ * implementation (tests/dropin: shenqi_b200/host/gravpm_b200.cpp; the reference's own needs FFTW + heFFTe). */
+void ref_gravpm_force(int Nmesh, double Asmth, double G)
+{
+    static PetaPM pm;
+    gravpm_init_periodic(&pm, PartManager->BoxSize, Asmth, Nmesh, G);
+    Cosmology CP;
+    memset(&CP, 0, sizeof(CP));
+    CP.Omega0 = 0.3; CP.OmegaLambda = 0.7; CP.HubbleParam = 0.7;
+    gravpm_force(&pm, &RefDomain, &CP, 0.1, 3.085678e21, std::string("."), 0.01);
+}
+#endif
+void ref_set_potential(const double * pot)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        PartManager->Base[i].Potential = pot[i];
+}
+void ref_get_gravpm(double * gravpm)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        for(int j = 0; j < 3; j++)
+            gravpm[3 * i + j] = PartManager->Base[i].GravPM[j];
+}
+void ref_set_flags(const unsigned char * flags, const unsigned char * types)
+{
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++) {
+        PartManager->Base[i].IsGarbage = flags[i] & 1;
+        PartManager->Base[i].Swallowed = (flags[i] >> 1) & 1;
+        if(types) PartManager->Base[i].Type = types[i];
+    }
+}
+int64_t ref_tree_numparticles2(void) { return RefTree.NumParticles; }
+int ref_tree_flags(void) { return RefTree.moments_computed_flag | (RefTree.full_particle_tree_flag << 1) | ((RefTree.Father != NULL) << 2); }
+/* Father[i] - firstnode for every loaded particle (needs a tree built with alloc_father) */
+void ref_tree_fathers(int * out)
+{
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        out[i] = RefTree.Father ? RefTree.Father[i] - (int) RefTree.firstnode : -1;
 }
 
 double ref_force_softening(void) { return FORCE_SOFTENING(); }

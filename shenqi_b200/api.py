@@ -157,7 +157,7 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_gravity_timebins_device", "sq_timebin_pushdown_device",
            "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram",
            "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count", "sq_download_accel_device",
-           "sq_walk_particle_cost", "sq_keys_device"]
+           "sq_walk_particle_cost", "sq_keys_device", "sq_tree_export_nodes_ex", "sq_tree_local_nodes"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 

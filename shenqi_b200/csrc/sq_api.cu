@@ -45,7 +45,8 @@ __global__ void sq_oldacc_kernel(const double * __restrict__ a, const double * _
 
 // unpack the caller's array-of-structs records (struct particle_data, partmanager.h:9-71)
 __global__ void sq_unpack_aos_kernel(const unsigned char * __restrict__ base, long long n, sq_aos_layout lay, double G,
-                                     double * __restrict__ pos, float * __restrict__ mass, double * __restrict__ oldacc)
+                                     double * __restrict__ pos, float * __restrict__ mass, double * __restrict__ oldacc,
+                                     unsigned char * __restrict__ skip, int * __restrict__ nskip)
 {
     for(long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         const unsigned char * p = base + (size_t) i * lay.stride;
@@ -57,6 +58,12 @@ __global__ void sq_unpack_aos_kernel(const unsigned char * __restrict__ base, lo
         double s = 0;
         for(int j = 0; j < 3; j++) { const double ax = A[j] + B[j]; s += ax * ax; }
         oldacc[i] = sqrt(s) / G;
+        // partmanager.h:18-31: bit 0 IsGarbage, bit 1 Swallowed, byte + 3 Type.  Garbage and swallowed black holes are not in
+        // the tree (forcetree.cpp:805) and sort behind everything else (TypeKey 255, slotsmanager.cpp:428-432)
+        const unsigned char fl = p[lay.off_flags], type = p[lay.off_flags + 3];
+        const bool sk = (fl & 1u) || ((fl & 2u) && type == 5);
+        skip[i] = sk ? 1 : 0;
+        if(sk) atomicAdd(nskip, 1);
     }
 }
 
@@ -171,6 +178,7 @@ static int sq_reset_particles(sq_ctx * c, int64_t n)
     if(n < 0 || n >= ((int64_t) 1 << 31)) { sq_set_error("particle count %lld out of range (MaxPart < 2^31, partmanager.c:22)", (long long) n); return SQ_ERR_ARG; }
     c->n = n;
     c->sorted = false; c->tree_built = false; c->walk_done = false; c->pm_done = false;
+    c->have_skip = false; c->n_valid = n;
     SQ_TRY(c->pos_in.reserve(sizeof(double) * 3 * (size_t) (n + 1)));
     SQ_TRY(c->mass_in.reserve(sizeof(float) * (size_t) (n + 1)));
     SQ_TRY(c->oldacc_in.reserve(sizeof(double) * (size_t) (n + 1)));
@@ -200,21 +208,36 @@ int sq_upload_particles_aos(sq_ctx * c, const void * base, int64_t n, const sq_a
     if(lay_in) lay = *lay_in; else sq_default_aos_layout(&lay);
     SQ_TRY(sq_reset_particles(c, n));
     // stage the records on the device, unpack there (the AoS is 160 B/particle; 64 B of it are read)
+    if(lay.stride < 40 || lay.off_flags + 4 > lay.stride || lay.off_pos + 24 > lay.stride || lay.off_gravpm + 24 > lay.stride ||
+       lay.off_fulltreegravaccel + 24 > lay.stride || lay.off_mass + 4 > lay.stride) {
+        sq_set_error("sq_upload_particles_aos: field offsets do not fit the record stride %zu", lay.stride);
+        return SQ_ERR_ARG;
+    }
     sq_buf stage;
     const size_t chunk = 1 << 22;
     SQ_TRY(stage.reserve(lay.stride * (size_t) (n < (int64_t) chunk ? n + 1 : chunk)));
+    SQ_TRY(c->skip_in.reserve((size_t) n + 64));
+    int * d_nskip = (int *) (c->skip_in.as<unsigned char>() + (((size_t) n + 15) & ~(size_t) 15));
+    SQ_CUDA(cudaMemsetAsync(d_nskip, 0, 4, c->stream));
     int rc = SQ_OK;
     for(int64_t i0 = 0; i0 < n; i0 += (int64_t) chunk) {
         const int64_t m = (n - i0) < (int64_t) chunk ? (n - i0) : (int64_t) chunk;
         cudaError_t e = cudaMemcpyAsync(stage.p, (const unsigned char *) base + (size_t) i0 * lay.stride, lay.stride * (size_t) m, cudaMemcpyHostToDevice, c->stream);
         if(e != cudaSuccess) { sq_set_error("sq_upload_particles_aos: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
         sq_unpack_aos_kernel<<<api_grid(c, m), 256, 0, c->stream>>>(stage.as<unsigned char>(), m, lay, c->par.G, c->pos_in.as<double>() + 3 * i0,
-                c->mass_in.as<float>() + i0, c->oldacc_in.as<double>() + i0);
+                c->mass_in.as<float>() + i0, c->oldacc_in.as<double>() + i0, c->skip_in.as<unsigned char>() + i0, d_nskip);
         c->kernel_launches++;
         e = cudaStreamSynchronize(c->stream);
         if(e != cudaSuccess) { sq_set_error("sq_upload_particles_aos: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
     }
     stage.release();
+    if(rc == SQ_OK) {
+        int h_nskip = 0;
+        SQ_CUDA(cudaMemcpyAsync(&h_nskip, d_nskip, 4, cudaMemcpyDeviceToHost, c->stream));
+        SQ_CUDA(cudaStreamSynchronize(c->stream));
+        c->have_skip = h_nskip > 0;
+        c->n_valid = n - h_nskip;
+    }
     return rc;
 }
 
@@ -300,7 +323,20 @@ int sq_tree_build(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_i
 int sq_tree_export_nodes(sq_ctx * c, void * nodes, int64_t firstnode, int upload_order)
 {
     if(!c || !nodes) return SQ_ERR_ARG;
-    return sq_tree_export(c, nodes, firstnode, upload_order);
+    return sq_tree_export(c, nodes, firstnode, upload_order, -1);
+}
+
+int sq_tree_export_nodes_ex(sq_ctx * c, void * nodes, int64_t firstnode, int64_t lastnode, int upload_order)
+{
+    if(!c || !nodes) return SQ_ERR_ARG;
+    return sq_tree_export(c, nodes, firstnode, upload_order, lastnode);
+}
+
+int sq_tree_local_nodes(sq_ctx * c, int64_t * n)
+{
+    if(!c || !n || !c->tree_built) { sq_set_error("sq_tree_local_nodes: no tree"); return SQ_ERR_ARG; }
+    *n = c->n_local_nodes;
+    return SQ_OK;
 }
 
 int sq_tree_walk_device(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats)
@@ -314,8 +350,8 @@ int sq_download_accel(sq_ctx * c, double * accel, double * potential)
     if(!c || !c->walk_done) { sq_set_error("sq_download_accel: no walk results"); return SQ_ERR_ARG; }
     const int64_t n = c->n;
     // only the walked targets are written, as the reference's reduce does (gravshort2.hpp:136-146)
-    const bool all = c->walk_ntargets == n;
-    const uint32_t * targets = all ? nullptr : c->w_targets.as<uint32_t>();
+    const bool all = c->walk_all && c->n_valid == n;
+    const uint32_t * targets = c->walk_all ? nullptr : c->w_targets.as<uint32_t>();
     const long long m = c->walk_ntargets;
     if(accel) {
         SQ_TRY(c->w_out_accel.reserve(sizeof(double) * 3 * (size_t) (n + 1)));
@@ -343,9 +379,7 @@ int sq_download_accel(sq_ctx * c, double * accel, double * potential)
 int sq_download_accel_device(sq_ctx * c, double * accel, double * potential)
 {
     if(!c || !c->walk_done) { sq_set_error("sq_download_accel_device: no walk results"); return SQ_ERR_ARG; }
-    const int64_t n = c->n;
-    const bool all = c->walk_ntargets == n;
-    const uint32_t * targets = all ? nullptr : c->w_targets.as<uint32_t>();
+    const uint32_t * targets = c->walk_all ? nullptr : c->w_targets.as<uint32_t>();
     const long long m = c->walk_ntargets;
     if(accel && m > 0) { sq_unpermute_kernel<3><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_accel.as<double>(), 3, 0, c->perm.as<uint32_t>(), targets, m, accel); c->kernel_launches++; }
     if(potential && c->tree_full && m > 0) { sq_unpermute_kernel<1><<<api_grid(c, m), 256, 0, c->stream>>>(c->w_pot.as<double>(), 1, 0, c->perm.as<uint32_t>(), targets, m, potential); c->kernel_launches++; }

@@ -111,6 +111,12 @@ struct sq_ctx {
     int64_t n = 0;
     sq_buf pos_in, mass_in, id_in, type_in, oldacc_in, keys_in, oldacc_tmp, stage_a, stage_b;
     bool have_types = false;
+    // IsGarbage || (Swallowed && Type == 5) per uploaded particle (forcetree.cpp:805, slotsmanager.cpp:428-432): such
+    // particles get the largest key, sort behind every valid one and stay out of the tree, the walk and the mesh
+    sq_buf skip_in;
+    bool have_skip = false;
+    int64_t n_valid = 0;             // particles in front of the garbage after the sort
+    bool walk_all = false;           // the last walk had no explicit target list
     // ---- particles, PH-sorted order
     sq_buf pos, mass, oldacc, keys, perm, rank;   // perm[sorted] = upload idx; rank[upload] = sorted pos
     sq_buf sort_tmp_keys, sort_tmp_vals, sort_hist, scan_tmp, flag_tmp;
@@ -234,7 +240,7 @@ int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_
 int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_info * info);
 int sq_tree_moments_top(sq_ctx * c, int ls, int le);
 void sq_comm_destroy(sq_ctx * c);
-int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order);
+int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order, int64_t lastnode);
 int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_stats * stats);
 int sq_pm_run(sq_ctx * c, bool paint_only);
 void sq_pm_destroy(sq_ctx * c);

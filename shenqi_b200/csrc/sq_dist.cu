@@ -359,6 +359,7 @@ int sq_upload_particles_device(sq_ctx * c, const double * pos, const float * mas
     if(!c || (n > 0 && (!pos || !mass))) { sq_set_error("sq_upload_particles_device: null argument"); return SQ_ERR_ARG; }
     if(n < 0 || n >= ((int64_t) 1 << 31)) { sq_set_error("particle count %lld out of range (MaxPart < 2^31, partmanager.c:22)", (long long) n); return SQ_ERR_ARG; }
     c->n = n;
+    c->n_valid = n; c->have_skip = false;
     c->sorted = false; c->tree_built = false; c->walk_done = false; c->pm_done = false;
     SQ_TRY(c->pos_in.reserve(sizeof(double) * 3 * (size_t) (n + 1)));
     SQ_TRY(c->mass_in.reserve(sizeof(float) * (size_t) (n + 1)));
@@ -384,6 +385,7 @@ int sq_set_sorted_device(sq_ctx * c, const uint64_t * keys, const double * pos, 
     if(n < 0 || n >= ((int64_t) 1 << 31)) { sq_set_error("particle count %lld out of range (MaxPart < 2^31, partmanager.c:22)", (long long) n); return SQ_ERR_ARG; }
     if(n > 0 && (!keys || !pos || !mass)) { sq_set_error("sq_set_sorted_device: null argument"); return SQ_ERR_ARG; }
     c->n = n;
+    c->n_valid = n; c->have_skip = false;
     c->sorted = false; c->tree_built = false; c->walk_done = false; c->pm_done = false;
     SQ_TRY(c->keys.reserve(sizeof(uint64_t) * (size_t) (n + 1)));
     SQ_TRY(c->pos.reserve(sizeof(double) * 3 * (size_t) (n + 1)));

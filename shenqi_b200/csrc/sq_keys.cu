@@ -112,13 +112,20 @@ __global__ void __launch_bounds__(256) sq_keys_kernel(const double * __restrict_
         atomicOr(flags, 1);
 }
 
+// garbage / swallowed particles: the largest key, so that they sort behind every valid particle
+__global__ void sq_keys_skip_kernel(const unsigned char * __restrict__ skip, int64_t n, uint64_t * __restrict__ keys)
+{
+    for(int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x)
+        if(skip[i]) keys[i] = ~0ull;
+}
+
 // perm[i] = upload index of the particle at sorted position i
 __global__ void __launch_bounds__(256) sq_gather_kernel(const uint32_t * __restrict__ perm, int64_t n,
                                                         const double * __restrict__ pos_in, const float * __restrict__ mass_in,
                                                         const double * __restrict__ oldacc_in,
                                                         double * __restrict__ pos, float * __restrict__ mass,
                                                         double * __restrict__ oldacc, uint32_t * __restrict__ rank,
-                                                        int * __restrict__ flags)
+                                                        int * __restrict__ flags, int64_t nvalid)
 {
     int bad = 0;
     for(int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
@@ -128,7 +135,7 @@ __global__ void __launch_bounds__(256) sq_gather_kernel(const uint32_t * __restr
         pos[3 * i + 2] = pos_in[3 * (int64_t) j + 2];
         const float m = mass_in[j];
         mass[i] = m;
-        bad |= !(m > 0.f);
+        bad |= (i < nvalid) && !(m > 0.f);
         oldacc[i] = oldacc_in ? oldacc_in[j] : 0.0;
         rank[j] = (uint32_t) i;
     }
@@ -177,6 +184,10 @@ int sq_keys_run(sq_ctx * c)
     sq_keys_kernel<false><<<sq_grid_for(c, n, 256, 8), 256, 0, c->stream>>>(c->pos_in.as<double>(), n, box, box2000, domainfac,
                                                                              d_phtab, c->keys_in.as<uint64_t>(), c->t_counters.as<int>());
     c->kernel_launches++;
+    if(c->have_skip) {
+        sq_keys_skip_kernel<<<sq_grid_for(c, n, 256, 8), 256, 0, c->stream>>>(c->skip_in.as<unsigned char>(), n, c->keys_in.as<uint64_t>());
+        c->kernel_launches++;
+    }
     SQ_CUDA(cudaGetLastError());
     SQ_CUDA(cudaEventRecord(c->ev[1], c->stream));
     return SQ_OK;
@@ -193,7 +204,7 @@ int sq_gather_run(sq_ctx * c)
     if(n == 0) return SQ_OK;
     sq_gather_kernel<<<sq_grid_for(c, n, 256, 8), 256, 0, c->stream>>>(c->perm.as<uint32_t>(), n, c->pos_in.as<double>(),
             c->mass_in.as<float>(), c->oldacc_in.p ? c->oldacc_in.as<double>() : nullptr, c->pos.as<double>(), c->mass.as<float>(),
-            c->oldacc.as<double>(), c->rank.as<uint32_t>(), c->t_counters.as<int>());
+            c->oldacc.as<double>(), c->rank.as<uint32_t>(), c->t_counters.as<int>(), c->n_valid);
     c->kernel_launches++;
     SQ_CUDA(cudaGetLastError());
     return SQ_OK;

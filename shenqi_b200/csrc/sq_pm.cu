@@ -237,7 +237,7 @@ int sq_pm_run(sq_ctx * c, bool paint_only)
     if(!c->sorted) { sq_set_error("sq_pm_force: call sq_ph_sort first"); return SQ_ERR_ARG; }
     const int N = c->par.Nmesh;
     if(N < 2 || (N & 1)) { sq_set_error("sq_pm_force: Nmesh must be even and >= 2"); return SQ_ERR_ARG; }
-    const long long n = c->n;
+    const long long n = c->n_valid, nall = c->n;       // garbage particles neither paint nor read out
     const size_t nreal = (size_t) N * N * N;
     const size_t ncplx = (size_t) N * N * (N / 2 + 1);
     const double cell = c->par.BoxSize / N;
@@ -257,7 +257,8 @@ int sq_pm_run(sq_ctx * c, bool paint_only)
     }
     SQ_TRY(c->pm_cplx[0].reserve(sizeof(double2) * ncplx));
     for(int f = 1; f < 4; f++) SQ_TRY(c->pm_real[f].reserve(sizeof(double) * nreal));
-    SQ_TRY(c->pm_out.reserve(sizeof(double) * 4 * (size_t) (n + 1) + sizeof(double) * 2 * (size_t) N));
+    SQ_TRY(c->pm_out.reserve(sizeof(double) * 4 * (size_t) (nall + 1) + sizeof(double) * 2 * (size_t) N));
+    if(nall > n) SQ_CUDA(cudaMemsetAsync(c->pm_out.as<double>() + 4 * (size_t) n, 0, sizeof(double) * 4 * (size_t) (nall - n), c->stream));
     if(c->plan_nmesh != N) {
         sq_pm_destroy(c);
         SQ_CUFFT(cufftPlan3d(&c->plan_r2c, N, N, N, CUFFT_D2Z));
@@ -276,7 +277,7 @@ int sq_pm_run(sq_ctx * c, bool paint_only)
         const double w = k * (2 * M_PI / N);
         tab[N + i] = -1 * (1 / 6.0 * (8 * sin(w) - sin(2 * w))) * (N / c->par.BoxSize);
     }
-    double * d_tab = c->pm_out.as<double>() + 4 * (size_t) (n + 1);
+    double * d_tab = c->pm_out.as<double>() + 4 * (size_t) (nall + 1);
     SQ_CUDA(cudaMemcpyAsync(d_tab, tab.data(), sizeof(double) * 2 * (size_t) N, cudaMemcpyHostToDevice, c->stream));
     SQ_CUDA(cudaStreamSynchronize(c->stream));     // tab is a host temporary
     SQ_CUFFT(cufftExecD2Z(c->plan_r2c, c->pm_real[0].as<double>(), c->pm_cplx[0].as<cufftDoubleComplex>()));

@@ -231,10 +231,15 @@ __global__ void __launch_bounds__(256) sq_tree_moments_kernel(double4 * __restri
 }
 
 // flags[sorted position] = 1 for active particles; then compacted to an ascending list
-__global__ void sq_mark_active_kernel(const int32_t * __restrict__ active, int64_t nactive, const uint32_t * __restrict__ rank, uint32_t * __restrict__ flags)
+__global__ void sq_mark_active_kernel(const int32_t * __restrict__ active, int64_t nactive, const uint32_t * __restrict__ rank, uint32_t * __restrict__ flags,
+                                      int64_t n, int64_t nvalid, int * __restrict__ bad)
 {
-    for(int64_t k = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; k < nactive; k += (int64_t) gridDim.x * blockDim.x)
-        flags[rank[active[k]]] = 1u;
+    for(int64_t k = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; k < nactive; k += (int64_t) gridDim.x * blockDim.x) {
+        const int32_t a = active[k];
+        if(a < 0 || a >= n) { atomicOr(bad, 1); continue; }          // an index outside the particle table
+        const uint32_t r = rank[a];
+        if(r < nvalid) flags[r] = 1u;                                // garbage / swallowed particles have no work (and are not in the tree)
+    }
 }
 __global__ void sq_compact_kernel(const uint32_t * __restrict__ scanned, const uint32_t * __restrict__ flags_total, int64_t n, uint32_t * __restrict__ out)
 {
@@ -286,7 +291,7 @@ int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_
         if(e == cudaSuccess) e = cudaMemsetAsync(flags, 0, sizeof(uint32_t) * (size_t) (n + 4), c->stream);
         if(e != cudaSuccess) { sq_set_error("active list upload: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
         if(nactive > 0) {
-            sq_mark_active_kernel<<<grid_for(c, nactive, 256, 8), 256, 0, c->stream>>>(d_act.as<int32_t>(), nactive, c->rank.as<uint32_t>(), flags);
+            sq_mark_active_kernel<<<grid_for(c, nactive, 256, 8), 256, 0, c->stream>>>(d_act.as<int32_t>(), nactive, c->rank.as<uint32_t>(), flags, n, c->n_valid, (int *) (flags + n + 2));
             c->kernel_launches++;
         }
         uint32_t * total = flags + n + 1;
@@ -295,9 +300,12 @@ int sq_active_to_sorted(sq_ctx * c, const int32_t * active, int64_t nactive, sq_
             sq_compact_kernel<<<grid_for(c, n, 256, 8), 256, 0, c->stream>>>(flags, total, n, out->as<uint32_t>());
             c->kernel_launches++;
         }
-        e = cudaMemcpyAsync(&h_total, total, 4, cudaMemcpyDeviceToHost, c->stream);
+        uint32_t h_two[2] = {0, 0};
+        e = cudaMemcpyAsync(h_two, total, 8, cudaMemcpyDeviceToHost, c->stream);
         if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if(e != cudaSuccess) { sq_set_error("active list compaction: %s", cudaGetErrorString(e)); rc = SQ_ERR_CUDA; break; }
+        h_total = h_two[0];
+        if(h_two[1]) { sq_set_error("active list: an index lies outside [0, %lld)", (long long) n); rc = SQ_ERR_ARG; break; }
     } while(0);
     *count = h_total;
     return rc;
@@ -326,7 +334,7 @@ static int sq_tree_prepare_set(sq_ctx * c, const int32_t * active, int64_t nacti
     const int64_t n = c->n;
     c->tree_identity = true;
     c->tree_full = (active == nullptr);
-    c->tree_np = n;
+    c->tree_np = c->n_valid;         // garbage sorts behind the valid particles and stays out of the tree (forcetree.cpp:805)
     uint32_t * order = nullptr;    // tree position -> sorted position, when not identity
     if(active) {
         int64_t h_total = 0;
@@ -500,11 +508,21 @@ static_assert(sizeof(sq_ref_node) == 120, "NODE image must be 120 bytes");
 
 __global__ void sq_tree_export_kernel(const double4 * __restrict__ cm, const double4 * __restrict__ cl, const int4 * __restrict__ lk,
                                       const int * __restrict__ parent, int numnodes, long long firstnode,
-                                      const uint32_t * __restrict__ tree_order, const uint32_t * __restrict__ perm, sq_ref_node * __restrict__ out)
+                                      const uint32_t * __restrict__ tree_order, const uint32_t * __restrict__ perm, sq_ref_node * __restrict__ out,
+                                      const int * __restrict__ topidx, const sq_topnode * __restrict__ tn, const sq_topleaf * __restrict__ tl, int myrank,
+                                      long long lastnode)
 {
     for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < numnodes; i += gridDim.x * blockDim.x) {
-        const int4 l = lk[i];
+        int4 l = lk[i];
         const double4 c = cl[i], m = cm[i];
+        // a top leaf of another rank is a pseudo node in the reference's image, whatever was imported below it on the device:
+        // ChildType PSEUDO, suns[0] = lastnode + leaf (force_create_node_for_topnode, forcetree.cpp:903-906)
+        int pseudo_leaf = -1;
+        if(topidx && topidx[i] >= 0) {
+            const sq_topnode T = tn[topidx[i]];
+            if(T.Daughter < 0 && tl[T.Leaf].Task != myrank) pseudo_leaf = T.Leaf;
+        }
+        if(pseudo_leaf >= 0) l = make_int4(0, 0, l.z, (l.w & ~(3 << 8)) | (2 << 8));
         sq_ref_node nd;
         nd.sibling = l.z >= 0 ? (int) (firstnode + l.z) : -1;
         nd.father = parent[i] >= 0 ? (int) (firstnode + parent[i]) : -1;
@@ -524,21 +542,25 @@ __global__ void sq_tree_export_kernel(const double4 * __restrict__ cm, const dou
             }
             nd.suns[j] = v;
         }
+        if(pseudo_leaf >= 0) nd.suns[0] = (int) (lastnode + pseudo_leaf);
         nd.noccupied = type == 1 ? SQ_NODEFULL : l.y;
         nd.flags = (unsigned) SQ_INFO_ITOP(l.w) | ((unsigned) SQ_INFO_TOP(l.w) << 1) | ((unsigned) SQ_INFO_LOCAL(l.w) << 2) | ((unsigned) type << 3);
         out[i] = nd;
     }
 }
 
-int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order)
+int sq_tree_export(sq_ctx * c, void * host_nodes, int64_t firstnode, int upload_order, int64_t lastnode)
 {
     if(!c->tree_built) { sq_set_error("sq_tree_export_nodes: no tree"); return SQ_ERR_ARG; }
-    const int nn = (int) c->tree_numnodes;
+    const int nn = (int) c->n_local_nodes;          // imported sub-trees are not part of the host image
+    if(lastnode < 0) lastnode = firstnode + nn;
     sq_buf img;
     SQ_TRY(img.reserve(sizeof(sq_ref_node) * (size_t) nn));
     sq_tree_export_kernel<<<grid_for(c, nn, 256, 8), 256, 0, c->stream>>>(c->t_cm.as<double4>(), c->t_cl.as<double4>(), c->t_lk.as<int4>(),
             c->t_parent.as<int>(), nn, (long long) firstnode, c->tree_identity ? nullptr : c->tree_order.as<uint32_t>(),
-            upload_order ? c->perm.as<uint32_t>() : nullptr, img.as<sq_ref_node>());
+            upload_order ? c->perm.as<uint32_t>() : nullptr, img.as<sq_ref_node>(),
+            c->have_domain ? c->t_top.as<int>() : nullptr, c->have_domain ? c->d_topnodes.as<sq_topnode>() : nullptr,
+            c->have_domain ? c->d_topleaves.as<sq_topleaf>() : nullptr, c->comm_rank, (long long) lastnode);
     c->kernel_launches++;
     cudaError_t e = cudaMemcpyAsync(host_nodes, img.p, sizeof(sq_ref_node) * (size_t) nn, cudaMemcpyDeviceToHost, c->stream);
     if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);

@@ -1046,7 +1046,7 @@ extern "C" int sq_walk_particle_cost(sq_ctx * c, float * cost)
     SQ_TRY(tmp.reserve(sizeof(float) * (size_t) (n + 1)));
     cudaError_t e = cudaMemsetAsync(tmp.p, 0, sizeof(float) * (size_t) (n + 1), c->stream);
     if(e == cudaSuccess && m > 0) {
-        sq_walk_cost_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->w_gcost.as<unsigned>(), m == n ? nullptr : c->w_targets.as<uint32_t>(), c->perm.as<uint32_t>(),
+        sq_walk_cost_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->w_gcost.as<unsigned>(), c->walk_all ? nullptr : c->w_targets.as<uint32_t>(), c->perm.as<uint32_t>(),
                 (long long) m, c->walk_group, tmp.as<float>());
         c->kernel_launches++;
         e = cudaGetLastError();
@@ -1126,7 +1126,8 @@ int sq_walk_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_walk_sta
 
     const int64_t n = c->n;
     const uint32_t * targets = nullptr;
-    int64_t ntargets = n;
+    int64_t ntargets = c->n_valid;
+    c->walk_all = !active && c->range_count < 0;
     if(active) {
         SQ_TRY(sq_active_to_sorted(c, active, nactive, &c->w_targets, &ntargets));
         targets = c->w_targets.as<uint32_t>();

@@ -18,9 +18,9 @@
 //           parts[i].FullTreeGravAccel and parts[i].Potential (= tree potential with the self terms of
 //           GravTreeOutput::postprocess, gravshort2.hpp:88-107; the primary reduce ASSIGNS the potential)
 //   errors  endrun() (abort), like every reference module; there is no CPU fallback.
-// The device tree is rebuilt from the particles (they are in Peano-Hilbert order after domain_decompose,
-// so the sort is the identity); tree->Nodes of the host tree is not read.
-// Single rank per GPU: comm is used only for its size (multi-rank export/import: DESIGN.md section 6).
+// With forcetree_b200.cpp linked, the device tree built by force_tree_full / force_tree_active_moments for this host
+// tree is walked as it is (also for NTask > 1: domain top nodes, exchanged moments, imported sub-trees); otherwise the
+// device tree is rebuilt from the particles (single rank), tree->Nodes of the host tree is not read.
 #include <mpi.h>
 #include <math.h>
 #include <stdlib.h>
@@ -29,28 +29,24 @@
 
 #include "gravshort2.hpp"
 #include "utils/endrun.h"
-#include "../../include/shenqi_b200.h"
+#include "b200_host.h"
 
-static sq_ctx * B200Ctx = NULL;
 static sq_walk_stats B200LastStats;
 
 extern "C" const sq_walk_stats * shenqi_b200_last_walk_stats(void) { return &B200LastStats; }
-
-static void b200_check(int rc, const char * what)
-{
-    if(rc != SQ_OK)
-        endrun(5, "shenqi_b200: %s failed (%d): %s\n", what, rc, sq_last_error());
-}
 
 void
 grav_short_tree_cuda(const ActiveParticles * act, ForceTree * tree, GravTreeParams * priv, GravTreeOutput * output, particle_data * const parts, const size_t MaxExportBufferBytes, MPI_Comm comm)
 {
     int NTask = 1;
     MPI_Comm_size(comm, &NTask);
-    if(NTask > 1)
-        endrun(5, "shenqi_b200: this hook serves one rank per GPU with a rank-local tree; NTask = %d\n", NTask);
-    if(!B200Ctx)
-        b200_check(sq_ctx_create(&B200Ctx, 0), "sq_ctx_create");
+    sq_ctx * B200Ctx = b200_context(comm);
+    /* The device tree that forcetree_b200.cpp's force_tree_full / force_tree_active_moments built for THIS host tree is
+     * walked as it is (top nodes of the domain, moments exchanged, remote sub-trees imported when NTask > 1): no second
+     * upload, sort or build.  A host tree from the reference's own forcetree.cpp is rebuilt on the device from the particles. */
+    const bool cached = b200_tree_is_cached(tree) != 0;
+    if(NTask > 1 && !cached)
+        endrun(5, "shenqi_b200: with NTask = %d the tree must come from forcetree_b200.cpp (it carries the domain's top nodes and the imported sub-trees)\n", NTask);
 
     const int64_t NumPart = PartManager->NumPart;
     /* GravShortTable keeps its tables private; apply_short_range_window() at the knots returns them exactly
@@ -90,21 +86,37 @@ grav_short_tree_cuda(const ActiveParticles * act, ForceTree * tree, GravTreePara
     raw.ntab = NGRAVTAB; raw.force_table = ftab.data(); raw.pot_table = ptab.data(); raw.table_dx = table_dx;
     b200_check(sq_set_walk_raw(B200Ctx, &raw), "sq_set_walk_raw");
 
-    /* particle_data is read in place (160-B records); |a_old| = |FullTreeGravAccel + GravPM| / G is formed on the device */
-    b200_check(sq_upload_particles_aos(B200Ctx, parts, NumPart, NULL), "sq_upload_particles_aos");
-    b200_check(sq_ph_sort(B200Ctx), "sq_ph_sort");
     const int * active = act->ActiveParticle;
     const int64_t nactive = act->NumActiveParticle;
     const bool all = (active == NULL && nactive == NumPart);
-    /* the tree holds what the host tree holds: every particle on a full-particle tree (PM steps), else the active set */
     sq_tree_info info;
-    if(tree->full_particle_tree_flag)
-        b200_check(sq_tree_build(B200Ctx, NULL, 0, &info), "sq_tree_build");
-    else {
-        std::vector<int32_t> idx;
-        const int32_t * lst = active;
-        if(!lst) { idx.resize(nactive); for(int64_t i = 0; i < nactive; i++) idx[i] = (int32_t) i; lst = idx.data(); }
-        b200_check(sq_tree_build(B200Ctx, lst, nactive, &info), "sq_tree_build");
+    memset(&info, 0, sizeof(info));
+    if(cached) {
+        /* only |a_old| = |FullTreeGravAccel + GravPM| / G may have changed since the build (gravshort2.hpp:111-121): 8 bytes per particle */
+        std::vector<double> oldacc((size_t) NumPart + 1);
+        #pragma omp parallel for
+        for(int64_t i = 0; i < NumPart; i++) {
+            double s = 0;
+            for(int d = 0; d < 3; d++) { const double ax = parts[i].FullTreeGravAccel[d] + parts[i].GravPM[d]; s += ax * ax; }
+            oldacc[i] = sqrt(s) / priv->G;
+        }
+        b200_check(sq_set_oldacc(B200Ctx, oldacc.data()), "sq_set_oldacc");
+        info.numnodes = tree->numnodes;
+    } else {
+        /* particle_data is read in place (layout from the reference's own struct); |a_old| is formed on the device */
+        const sq_aos_layout lay = b200_particle_layout();
+        b200_check(sq_upload_particles_aos(B200Ctx, parts, NumPart, &lay), "sq_upload_particles_aos");
+        b200_check(sq_ph_sort(B200Ctx), "sq_ph_sort");
+        b200_check(sq_domain_set(B200Ctx, NULL, 0, NULL, 0, NULL, 0), "sq_domain_set");
+        /* the tree holds what the host tree holds: every particle on a full-particle tree (PM steps), else the active set */
+        if(tree->full_particle_tree_flag)
+            b200_check(sq_tree_build(B200Ctx, NULL, 0, &info), "sq_tree_build");
+        else {
+            std::vector<int32_t> idx;
+            const int32_t * lst = active;
+            if(!lst) { idx.resize(nactive); for(int64_t i = 0; i < nactive; i++) idx[i] = (int32_t) i; lst = idx.data(); }
+            b200_check(sq_tree_build(B200Ctx, lst, nactive, &info), "sq_tree_build");
+        }
     }
     std::vector<double> accel((size_t) NumPart * 3), pot;
     /* inactive entries must keep the caller's values */
