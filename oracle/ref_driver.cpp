@@ -65,11 +65,17 @@ static void ref_trivial_domain(DomainDecomp * ddecomp)
     ddecomp->NTopNodes = 1;
     ddecomp->NTopLeaves = 1;
     ddecomp->TopNodes = (struct topnode_data *) calloc(1, sizeof(struct topnode_data));
+#ifdef REF_USE_MANAGED
+    /* TopLeaves are dereferenced by the reference's toptree kernels */
+    ddecomp->TopLeaves = mymanagedmalloc("TopLeaves", struct topleaf_data, 1);
+    memset(ddecomp->TopLeaves, 0, sizeof(struct topleaf_data));
+#else
+    ddecomp->TopLeaves = (struct topleaf_data *) calloc(1, sizeof(struct topleaf_data));
+#endif
     ddecomp->TopNodes[0].Daughter = -1;
     ddecomp->TopNodes[0].Leaf = 0;
     ddecomp->TopNodes[0].StartKey = 0;
     ddecomp->TopNodes[0].Shift = BITS_PER_DIMENSION * 3;
-    ddecomp->TopLeaves = (struct topleaf_data *) calloc(1, sizeof(struct topleaf_data));
     ddecomp->TopLeaves[0].Task = 0;
     ddecomp->Tasks = (struct task_data *) calloc(1, sizeof(struct task_data));
     ddecomp->Tasks[0].StartLeaf = 0;
@@ -85,8 +91,14 @@ int ref_init(void)
     int thr;
     MPI_Init_thread(NULL, NULL, MPI_THREAD_FUNNELED, &thr);
     init_endrun(0);
+#ifdef REF_USE_MANAGED
+    /* the reference's own GPU walk (tests/dropin libshenqi_refgpu.so) reads particles, nodes and parameters from managed memory */
+    allocator_malloc_init(A_MAIN, "MAIN", 1);
+    allocator_malloc_init(A_TEMP, "TEMP", 1);
+#else
     allocator_malloc_init(A_MAIN, "MAIN", 0);
     allocator_malloc_init(A_TEMP, "TEMP", 0);
+#endif
     walltime_init(&RefClocks);
     memset(PartManager, 0, sizeof(PartManager[0]));
     memset(SlotsManager, 0, sizeof(SlotsManager[0]));
