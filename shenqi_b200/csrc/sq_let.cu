@@ -538,7 +538,10 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
     SQ_TRY(sq_tree_run(c, nullptr, 0, info));
     SQ_CUDA(cudaEventRecord(ev[11], c->stream));
     const int NL = (int) c->dom_leaves.size(), R = c->nranks, me = c->comm_rank;
-    const int64_t n = c->n, nn0 = c->tree_numnodes;
+    // particles in tree order: the sorted arrays, or their geometric re-ordering when some particle lies on a cell face
+    sq_buf & SP = c->tree_identity ? c->pos : c->tree_pos;
+    sq_buf & SM = c->tree_identity ? c->mass : c->tree_mass;
+    const int64_t n = c->tree_np, nn0 = c->tree_numnodes;
     LI.local_nodes = nn0; LI.local_particles = n;
     const double qinv = 4294967296.0 / c->par.BoxSize;
     sq_buf & d_tasks = c->let_boxes;          // task table on the device
@@ -561,7 +564,7 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
         SQ_CUDA(cudaMemcpyAsync(d_box, init.data(), sizeof(unsigned) * init.size(), cudaMemcpyHostToDevice, c->stream));
         SQ_CUDA(cudaMemcpyAsync(d_mine, mine.data(), sizeof(int) * mine.size(), cudaMemcpyHostToDevice, c->stream));
         if(n > 0 && !mine.empty()) {
-            let_leafbox_kernel<<<let_grid(c, n), 256, 0, c->stream>>>(c->d_leafrange.as<int2>(), d_mine, (int) mine.size(), c->pos.as<double>(), (long long) n, qinv, d_box);
+            let_leafbox_kernel<<<let_grid(c, n), 256, 0, c->stream>>>(c->d_leafrange.as<int2>(), d_mine, (int) mine.size(), SP.as<double>(), (long long) n, qinv, d_box);
             c->kernel_launches++;
         }
         let_leafdata_kernel<<<let_grid(c, NL), 256, 0, c->stream>>>(c->d_topleaves.as<sq_topleaf>(), NL, me, c->d_treenode.as<int>(), c->d_leafrange.as<int2>(),
@@ -663,7 +666,7 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
         double4 * pcm, * pcl; int4 * plk; double * ppos; float * pmass; int * proot;
         sect(c->let_send.as<unsigned char>() + soff[r], snn[r], snp[r], pcm, pcl, plk, ppos, pmass, proot);
         let_pack_kernel<<<let_grid(c, nn0), 256, 0, c->stream>>>(c->let_mask.as<unsigned>(), r, c->t_lk.as<int4>(), c->t_cm.as<double4>(), c->t_cl.as<double4>(),
-                c->pos.as<double>(), c->mass.as<float>(), (int) nn0, fn, fp, pcm, pcl, plk, ppos, pmass);
+                SP.as<double>(), SM.as<float>(), (int) nn0, fn, fp, pcm, pcl, plk, ppos, pmass);
         let_roots_kernel<<<let_grid(c, NL), 256, 0, c->stream>>>(c->d_topleaves.as<sq_topleaf>(), NL, me, c->d_treenode.as<int>(), c->let_mask.as<unsigned>(), r, fn, proot);
         c->kernel_launches += 3;
         LI.exported_nodes += snn[r]; LI.exported_particles += snp[r];
@@ -712,8 +715,8 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
     SQ_TRY(c->t_cm.grow_keep(sizeof(double4) * ntotn, sizeof(double4) * (size_t) nn0, c->stream));
     SQ_TRY(c->t_cl.grow_keep(sizeof(double4) * ntotn, sizeof(double4) * (size_t) nn0, c->stream));
     SQ_TRY(c->t_lk.grow_keep(sizeof(int4) * ntotn, sizeof(int4) * (size_t) nn0, c->stream));
-    SQ_TRY(c->pos.grow_keep(sizeof(double) * 3 * ntotp, sizeof(double) * 3 * (size_t) n, c->stream));
-    SQ_TRY(c->mass.grow_keep(sizeof(float) * ntotp, sizeof(float) * (size_t) n, c->stream));
+    SQ_TRY(SP.grow_keep(sizeof(double) * 3 * ntotp, sizeof(double) * 3 * (size_t) n, c->stream));
+    SQ_TRY(SM.grow_keep(sizeof(float) * ntotp, sizeof(float) * (size_t) n, c->stream));
     int64_t noff = nn0, poff = n;
     for(int s = 0; s < R; s++) {
         if(s == me) continue;
@@ -725,8 +728,8 @@ extern "C" int sq_tree_build_dist(sq_ctx * c, sq_tree_info * info, sq_let_info *
             SQ_CUDA(cudaMemcpyAsync(c->t_lk.as<int4>() + noff, plk, sizeof(int4) * (size_t) rnn[s], cudaMemcpyDeviceToDevice, c->stream));
         }
         if(rnp[s] > 0) {
-            SQ_CUDA(cudaMemcpyAsync(c->pos.as<double>() + 3 * poff, ppos, sizeof(double) * 3 * (size_t) rnp[s], cudaMemcpyDeviceToDevice, c->stream));
-            SQ_CUDA(cudaMemcpyAsync(c->mass.as<float>() + poff, pmass, sizeof(float) * (size_t) rnp[s], cudaMemcpyDeviceToDevice, c->stream));
+            SQ_CUDA(cudaMemcpyAsync(SP.as<double>() + 3 * poff, ppos, sizeof(double) * 3 * (size_t) rnp[s], cudaMemcpyDeviceToDevice, c->stream));
+            SQ_CUDA(cudaMemcpyAsync(SM.as<float>() + poff, pmass, sizeof(float) * (size_t) rnp[s], cudaMemcpyDeviceToDevice, c->stream));
         }
         if(rnn[s] > 0) {
             let_relocate_kernel<<<let_grid(c, rnn[s]), 256, 0, c->stream>>>(c->t_lk.as<int4>(), noff, rnn[s], poff);

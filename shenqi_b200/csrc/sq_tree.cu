@@ -260,6 +260,11 @@ __global__ void sq_tree_gather_kernel(const uint32_t * __restrict__ idx, int64_t
         omass[j] = mass[s];
     }
 }
+__global__ void sq_topbits_kernel(const uint64_t * __restrict__ a, const uint64_t * __restrict__ b, int64_t m, int shift, int * __restrict__ flag)
+{
+    for(int64_t j = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; j < m; j += (int64_t) gridDim.x * blockDim.x)
+        if((a[j] ^ b[j]) >> shift) atomicOr(flag, 1);
+}
 __global__ void sq_compose_kernel(const uint32_t * __restrict__ outer, const uint32_t * __restrict__ inner, int64_t m, uint32_t * __restrict__ out)
 {
     for(int64_t j = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; j < m; j += (int64_t) gridDim.x * blockDim.x)
@@ -368,6 +373,13 @@ static int sq_tree_prepare_set(sq_ctx * c, const int32_t * active, int64_t nacti
             if((rc = nmass.reserve(sizeof(float) * (size_t) m))) break;
             if((rc = nord.reserve(sizeof(uint32_t) * (size_t) m))) break;
             if((rc = sq_geokeys_run(c, spos, m, gk.as<uint64_t>()))) break;
+            if(c->have_domain && c->dom_maxlevel > 0) {
+                // under a domain the re-ordering must stay inside the top leaves: a particle exactly on a face of a TOP-LEVEL cell
+                // would change its top leaf (and owner); faces of the finer cells are free
+                const uint64_t * pk = c->tree_identity ? c->keys.as<uint64_t>() : c->tree_keys.as<uint64_t>();
+                sq_topbits_kernel<<<grid_for(c, m, 256, 8), 256, 0, c->stream>>>(gk.as<uint64_t>(), pk, m, 63 - 3 * c->dom_maxlevel, c->t_counters.as<int>() + 4);
+                c->kernel_launches++;
+            }
             if((rc = sq_iota(c, gv.as<uint32_t>(), m))) break;
             if((rc = sq_sort_pairs(c, gk.as<uint64_t>(), gv.as<uint32_t>(), m, 0, 64))) break;
             sq_tree_gather_kernel<<<grid_for(c, m, 256, 8), 256, 0, c->stream>>>(gv.as<uint32_t>(), m, nullptr, spos, smass, nullptr,
@@ -375,7 +387,10 @@ static int sq_tree_prepare_set(sq_ctx * c, const int32_t * active, int64_t nacti
             sq_compose_kernel<<<grid_for(c, m, 256, 8), 256, 0, c->stream>>>(gv.as<uint32_t>(), c->tree_identity ? nullptr : c->tree_order.as<uint32_t>(),
                     m, nord.as<uint32_t>());
             c->kernel_launches += 2;
+            int h_top = 0;
+            if(c->have_domain && c->dom_maxlevel > 0) cudaMemcpyAsync(&h_top, c->t_counters.as<int>() + 4, 4, cudaMemcpyDeviceToHost, c->stream);
             if(cudaStreamSynchronize(c->stream) != cudaSuccess) { sq_set_error("geometric re-order failed"); rc = SQ_ERR_CUDA; break; }
+            if(h_top) { sq_set_error("tree build: a particle lies exactly on a face of a top-level cell of the domain"); rc = SQ_ERR_ARG; break; }
         } while(0);
         if(rc != SQ_OK) { gk.release(); gv.release(); npos.release(); nmass.release(); nord.release(); return rc; }
         // adopt the re-ordered buffers
@@ -399,10 +414,6 @@ int sq_tree_run(sq_ctx * c, const int32_t * active, int64_t nactive, sq_tree_inf
     const float * tmass = c->tree_identity ? c->mass.as<float>() : c->tree_mass.as<float>();
     double factor = c->par.TreeAllocFactor > 0 ? c->par.TreeAllocFactor : 0.9;
     const bool dom = c->have_domain;
-    if(dom && c->geo_mismatch && c->dom_nodes.size() > 1) {
-        sq_set_error("tree build: particles exactly on a cell face under a multi-leaf domain are not supported");
-        return SQ_ERR_ARG;
-    }
     const sq_topnode * d_tn = dom ? c->d_topnodes.as<sq_topnode>() : nullptr;
     const sq_topleaf * d_tl = dom ? c->d_topleaves.as<sq_topleaf>() : nullptr;
     const int ntopnodes = dom ? (int) c->dom_nodes.size() : 0;

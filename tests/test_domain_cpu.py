@@ -1,0 +1,136 @@
+"""CPU tests (no GPU) of the host logic of the domain-decomposed tree path: the domain builder of the C ABI
+(sq_domain_from_histogram is pure host code: libgadget/domain.cpp's top-tree refinement and balanced leaf assignment),
+the topnode_data / topleaf_data / task_data layouts, domain_get_topleaf, and - with world_size 2 over gloo - the flow the
+multi-GPU bench follows: every rank histograms its own particles, the histograms are all-reduced, every rank derives
+the SAME domain, and the owners partition the particle set."""
+import os
+import socket
+import sys
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
+from helpers import o_keys, random_clustered, ref
+
+
+def _hist(keys, level):
+    return np.bincount((keys >> np.uint64(63 - 3 * level)).astype(np.int64), minlength=8 ** level)
+
+
+def _check_domain(D, nranks, keys, level):
+    T, L, K = D.topnodes, D.topleaves, D.tasks
+    assert T["Shift"][0] == 63 and T["StartKey"][0] == 0                       # root = the whole key space (domain.cpp:1076)
+    inner = np.flatnonzero(T["Daughter"] >= 0)
+    for i in inner:                                                              # domain.cpp:849-868: 8 daughters, key order
+        d = T["Daughter"][i]
+        assert np.all(T["Shift"][d:d + 8] == T["Shift"][i] - 3)
+        assert np.array_equal(T["StartKey"][d:d + 8], T["StartKey"][i] + (np.arange(8, dtype=np.uint64) << np.uint64(T["Shift"][i] - 3)))
+    leaves = np.flatnonzero(T["Daughter"] < 0)
+    assert len(leaves) == len(L) and sorted(T["Leaf"][leaves]) == list(range(len(L)))
+    assert np.array_equal(L["topnode"][T["Leaf"][leaves]], leaves)
+    # leaves in key order, cut into nranks contiguous segments (domain_assign_topleaves_balanced)
+    sk = T["StartKey"][L["topnode"]].astype(np.float64)
+    assert np.all(np.diff(sk) > 0)
+    assert K["StartLeaf"][0] == 0 and K["EndLeaf"][-1] == len(L) and np.array_equal(K["StartLeaf"][1:], K["EndLeaf"][:-1])
+    for t in range(nranks):
+        assert K["EndLeaf"][t] > K["StartLeaf"][t]
+        assert np.all(L["Task"][K["StartLeaf"][t]:K["EndLeaf"][t]] == t)
+    # every key falls into exactly the leaf whose key range holds it
+    leaf = D.topleaf_of(keys)
+    tn = L["topnode"][leaf]
+    assert np.all(keys >= T["StartKey"][tn]) and np.all((keys - T["StartKey"][tn]) >> T["Shift"][tn].astype(np.uint64) == 0)
+    return L["Task"][leaf]
+
+
+@pytest.mark.parametrize("nranks,level,over", [(1, 2, 2), (2, 3, 4), (8, 3, 4), (8, 4, 4), (5, 3, 8)])
+def test_domain_from_histogram(nranks, level, over):
+    import shenqi_b200 as sq
+    box = 8.0
+    pos = random_clustered(100000, box, 7)
+    keys = o_keys(pos, box)
+    cnt = _hist(keys, level)
+    D = sq.domain_from_histogram(cnt, nranks, over)
+    owner = _check_domain(D, nranks, keys, level)
+    load = np.bincount(owner, minlength=nranks)
+    assert load.sum() == len(pos) and load.min() > 0
+    # no leaf above the refinement limit unless it sits at the histogram's own resolution
+    lim = len(pos) / (over * nranks)
+    T = D.topnodes[D.topleaves["topnode"]]
+    per_leaf = np.bincount(D.topleaf_of(keys), minlength=D.ntopleaves)
+    assert np.all((per_leaf <= lim) | (T["Shift"] == 63 - 3 * level))
+    # cost-weighted: segments of equal cost, not equal count
+    cost = cnt.astype(np.float64) ** 1.5
+    Dc = sq.domain_from_histogram(cnt, nranks, over, cost=cost)
+    oc = _check_domain(Dc, nranks, keys, level)
+    cell = (keys >> np.uint64(63 - 3 * level)).astype(np.int64)
+    w = (cost / np.maximum(cnt, 1))[cell]
+    if nranks > 1:
+        # a greedy cut is never further from the mean than the heaviest leaf
+        per_rank = np.bincount(oc, weights=w, minlength=nranks)
+        heaviest = np.bincount(Dc.topleaf_of(keys), weights=w, minlength=Dc.ntopleaves).max()
+        assert np.abs(per_rank - w.sum() / nranks).max() <= heaviest * (1 + 1e-9)
+
+
+def test_domain_struct_layouts_match_reference():
+    import shenqi_b200 as sq
+    assert sq.TOPNODE_DTYPE.itemsize == 24 and sq.TOPLEAF_DTYPE.itemsize == 12 and sq.TASK_DTYPE.itemsize == 8     # domain.h:12-31
+    if ref() is not None:
+        assert ref().ref_sizeof_topnode() == 24 and ref().ref_sizeof_topleaf() == 12
+
+
+def test_domain_errors():
+    import shenqi_b200 as sq
+    with pytest.raises(sq.ShenqiError):
+        sq.domain_from_histogram(np.array([5], np.int64), 2, 1)          # one cell, two ranks: "Number of Topleaves is less than NTask"
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import shenqi_b200 as sq
+        box, level = 8.0, 3
+        pos = random_clustered(60000, box, 11)
+        keys = o_keys(pos, box)
+        mine = np.arange(rank, len(pos), world)                         # before the exchange: particles anywhere
+        h = torch.from_numpy(_hist(keys[mine], level))
+        dist.all_reduce(h)                                               # MPI_Allreduce of the local top-tree counts (domain.cpp:1160-1230)
+        D = sq.domain_from_histogram(h.numpy(), world, 4)
+        owner = D.topleaves["Task"][D.topleaf_of(keys[mine])]
+        # what the particle exchange would move: counts to every rank, all-to-all of the counts must be consistent
+        send = torch.from_numpy(np.bincount(owner, minlength=world))
+        recv = [torch.zeros_like(send) for _ in range(world)]
+        dist.all_gather(recv, send)
+        q.put((rank, [D.topnodes[f].tolist() for f in D.topnodes.dtype.names], D.topleaves.tobytes(), D.tasks.tobytes(), h.numpy().sum(), torch.stack(recv).numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world2_gloo_same_domain_on_every_rank():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = {}
+    for _ in range(world):
+        r, a, b, c, tot, table = q.get(timeout=300)
+        out[r] = (a, b, c, tot, table)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert out[0][:3] == out[1][:3]                                      # the same DomainDecomp on both ranks, field for field
+    assert out[0][3] == out[1][3] == 60000
+    table = out[0][4]                                                    # table[s][d] = particles rank s sends to rank d
+    assert table.sum() == 60000 and np.all(table.sum(axis=0) > 0)

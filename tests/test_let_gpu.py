@@ -23,10 +23,26 @@ from helpers import (ref, ptr, c_i64, c_dbl, c_int, quiet_stdout, canonical_tree
 pytestmark = pytest.mark.gpu
 
 
-def _problem(n=60000, seed=11, nmesh=48):
+def _face_coordinate(box, depth, rng):
+    """a coordinate exactly on a face between two level-(depth + 1) cells: the centre of a level-`depth` cell, by the
+    reference's own recurrence centre +- len / 4 (forcetree.cpp:277-283, 304-319)"""
+    c, q = box / 2., 0.25 * (box * 1.001)
+    for _ in range(depth):
+        c = c + q if rng.random() < 0.5 else c - q
+        q *= 0.5
+    return c
+
+
+def _problem(n=60000, seed=11, nmesh=48, onface=0):
     import shenqi_b200 as sq
     box = 8.0
     pos = random_clustered(n, box, seed)
+    if onface:
+        # particles exactly on faces of cells BELOW the domain's top levels: key digits and geometric octants disagree there,
+        # the tree is ordered by geometric keys (the reference descends by `Pos > centre`)
+        rng = np.random.default_rng(seed + 1)
+        for i in rng.choice(n, onface, replace=False):
+            pos[i, rng.integers(3)] = _face_coordinate(box, int(rng.integers(6, 14)), rng)
     mass = (1.0 + 0.25 * (np.arange(n) % 3)).astype(np.float32)
     P = sq.Params.defaults(box, nmesh, (box / n ** (1 / 3.)) / 30., TreeUseBH=1, TreeRcut=6.0)
     return box, pos, mass, P
@@ -155,16 +171,16 @@ def _check_ranks(out, R, pos, ref_acc, ref_pot, ref_inter, keys):
         assert L["imported_nodes"] > 0 and L["exported_nodes"] > 0
 
 
-@pytest.mark.parametrize("R,relative", [(2, False), (2, True), (4, True)])
-def test_let_ranks_as_threads_on_one_gpu(R, relative):
+@pytest.mark.parametrize("R,relative,onface", [(2, False, 0), (2, True, 0), (4, True, 0), (2, True, 40)])
+def test_let_ranks_as_threads_on_one_gpu(R, relative, onface):
     import shenqi_b200 as sq
-    box, pos, mass, P = _problem()
+    box, pos, mass, P = _problem(onface=onface)
     dom, keys = _domain(pos, box, R, 3, 4)
     # |a_old| for the relative criterion from a Barnes-Hut pass (as the reference bootstraps)
     a_bh, _, _, _, _, _, _ = _single_rank_with_domain(pos, mass, P, dom)
     P1 = sq.Params.defaults(P.BoxSize, P.Nmesh, P.GravitySoftening, TreeUseBH=0 if relative else 1, TreeRcut=P.TreeRcut)
     ref_acc, ref_pot, st, _, _, _, _ = _single_rank_with_domain(pos, mass, P1, dom, oldacc_from=a_bh if relative else None)
-    nid = sq.comm_loopback_id(1000 + 10 * R + int(relative))
+    nid = sq.comm_loopback_id(1000 + 10 * R + int(relative) + 100 * int(onface > 0))
     out = {}
     th = [threading.Thread(target=_rank_body, args=(r, R, nid, 0, pos, mass, P, dom, keys, a_bh, out, relative), daemon=True) for r in range(R)]
     for t in th:
