@@ -37,18 +37,7 @@
 #include <libgadget/cosmology.h>
 
 /* ---- symbols the path references but which live in reference files we do not build ---- */
-/* libgadget/timestep.cpp:78 : forward to the particle manager, no list */
-ActiveParticles init_empty_active_particles(struct part_manager_type * pman)
-{
-    ActiveParticles act;
-    memset(&act, 0, sizeof(act));
-    act.ActiveParticle = NULL;
-    act.NumActiveParticle = pman->NumPart;
-    act.Particles = pman->Base;
-    return act;
-}
-/* libgadget/timebinmgr.cpp: only consulted for gas/BH hmax; DM-only path never reaches it */
-int is_timebin_active(int bin, inttime_t current_ti) { (void) bin; (void) current_ti; return 1; }
+/* (init_empty_active_particles and is_timebin_active now come from the reference's own timestep.cpp, compiled through oracle/ref_timestep.cpp) */
 
 /* libgadget/bhdynfric.h:22, consulted by drift.cpp:32 for Type 5 only; black holes are not built here */
 int BHGetRepositionEnabled(void) { return 0; }

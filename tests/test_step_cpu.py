@@ -5,7 +5,7 @@ made by tests/golden/make_golden_step.py), and the literal semantics of libgadge
 import os
 import numpy as np
 import pytest
-from helpers import ROOT, oracle, ref, o_drift, o_kick, o_active_sublist, r_drift, o_gravity_timebins, timebin_params, c_i64, c_int, ptr
+from helpers import ROOT, oracle, ref, o_drift, o_kick, o_active_sublist, r_drift, o_gravity_timebins, timebin_params, c_i64, c_int, c_dbl, ptr
 
 needs_ref = pytest.mark.skipif(ref() is None, reason="oracle/_ref was not built (no /root/reference at build time)")
 GOLD = np.load(os.path.join(ROOT, "tests", "golden", "step_ref.npz"))
@@ -172,3 +172,99 @@ def test_pushdown_rule_host_equals_oracle():
             exp = L.sqo_pushdown_bin(ptr(c2), c_int(40), c_int(isPM))
             got, c3 = sq.pushdown_bin(counts.tolist(), 40, isPM)
             assert got == exp and c3 == c2.tolist()
+
+
+# ------------------------------------------------------------------------------------------ pins to the reference's own timestep.cpp
+needs_ref = pytest.mark.skipif(ref() is None, reason="reference build (oracle/_ref) not present")
+
+
+def _ref_load_for_timestep(n, gravpm, flags, seed=3):
+    """n particles in the reference's particle table with the given GravPM and IsGarbage / Swallowed flags."""
+    from helpers import r_load, quiet_stdout
+    rng = np.random.default_rng(seed)
+    pos = rng.random((n, 3)) * 8.0
+    with quiet_stdout():
+        r_load(pos, np.ones(n, np.float32), 8.0)
+        ref().ref_set_accels(None, ptr(np.ascontiguousarray(gravpm)))
+        ref().ref_set_flags(ptr(np.ascontiguousarray(flags)), None)
+
+
+@needs_ref
+def test_timebins_equal_reference_timestep_cpp():
+    """The bin loop of hierarchical_gravity_accelerations (timestep.cpp:351-377) run with the reference's OWN static
+    functions (oracle/ref_timestep.cpp includes timestep.cpp where it lies): get_timestep_gravity_dloga,
+    convert_timestep_to_ti -> TimeBinMgr::dti_from_dloga, round_down_power_of_two, get_timestep_bin.  The restatement
+    (and with it the GPU kernel, tests/test_step_gpu.py) must give the same bin for every particle and the same counts."""
+    from helpers import quiet_stdout
+    import math
+    R = ref()
+    rng = np.random.default_rng(8)
+    n = 40000
+    acc = rng.standard_normal((n, 3)) * 10.0 ** rng.uniform(-2, 6, (n, 1))
+    pm = rng.standard_normal((n, 3)) * 10.0
+    acc[:3] = 0; pm[:3] = 0
+    flags = np.where(rng.random(n) < 0.05, rng.integers(1, 3, n), 0).astype(np.uint8)      # IsGarbage (1) or Swallowed (2)
+    skip = (flags != 0).astype(np.uint8)
+    _ref_load_for_timestep(n, pm, flags)
+    sync = np.array([math.log(0.1), math.log(0.111), math.log(0.125)])
+    R.ref_ts_gravity_timebins.restype = c_i64
+    R.ref_ts_loga_from_ti.restype = c_dbl
+    soft = 1.0 / 30
+    for kw in (dict(), dict(Ti_Current=(1 << 45) + (1 << 30)), dict(largest_active=33), dict(dti_max=1 << 31), dict(MinSizeTimestep=1e-4),
+               dict(nsync=2), dict(dti_max=0)):
+        nsync = kw.pop("nsync", 3)
+        Ti = kw.get("Ti_Current", 0)
+        with quiet_stdout():
+            R.ref_ts_setup(c_dbl(0.02), c_dbl(kw.get("MinSizeTimestep", 0.0)), ptr(sync), c_int(nsync))
+            R.ref_ts_set_softening(c_dbl(soft))
+        loga = R.ref_ts_loga_from_ti(c_i64(Ti))
+        P = timebin_params(loga=loga, can_advance=1 if nsync == 3 else 0, softening=soft, **kw)
+        rtb = np.zeros(n, np.uint8); rcounts = np.zeros(47, np.int64)
+        with quiet_stdout():
+            R.ref_ts_set_timebins(ptr(np.full(n, 255, np.uint8)))
+            rbad = R.ref_ts_gravity_timebins(ptr(acc), None, c_i64(n), c_dbl(P.atime), c_dbl(P.hubble), c_i64(P.Ti_Current), c_i64(P.dti_max),
+                                             c_int(P.largest_active), ptr(rtb), ptr(rcounts))
+        tb, counts, nbad = o_gravity_timebins(P, acc, pm, None, skip, n)
+        assert np.array_equal(tb, rtb), kw
+        assert np.array_equal(counts, rcounts) and nbad == rbad, kw
+    # an active list
+    act = np.sort(rng.choice(n, n // 4, replace=False)).astype(np.int32)
+    with quiet_stdout():
+        R.ref_ts_setup(c_dbl(0.02), c_dbl(0.0), ptr(sync), c_int(3))
+        R.ref_ts_set_timebins(ptr(np.full(n, 255, np.uint8)))
+        P = timebin_params(loga=R.ref_ts_loga_from_ti(c_i64(0)), softening=soft)
+        rtb = np.zeros(n, np.uint8); rcounts = np.zeros(47, np.int64)
+        R.ref_ts_gravity_timebins(ptr(acc), ptr(act), c_i64(len(act)), c_dbl(P.atime), c_dbl(P.hubble), c_i64(0), c_i64(P.dti_max), c_int(P.largest_active), ptr(rtb), ptr(rcounts))
+    tb, counts, _ = o_gravity_timebins(P, acc, pm, act, skip, n)
+    assert np.array_equal(tb, rtb) and np.array_equal(counts, rcounts)
+
+
+@needs_ref
+@pytest.mark.parametrize("with_list", [False, True])
+def test_active_sublist_and_kick_equal_reference_timestep_cpp(with_list):
+    """build_active_sublist (timestep.cpp:1375-1397, std::copy_if with SubActivePredicate) and the kick loop of
+    apply_hierarchical_grav_kick (:270-279, do_grav_short_range_kick :962-968), the reference's own code."""
+    from helpers import quiet_stdout
+    R = ref()
+    rng = np.random.default_rng(7)
+    n = 30000
+    timebin = rng.integers(0, 12, n).astype(np.uint8)
+    flags = np.where(rng.random(n) < 0.05, rng.integers(1, 3, n), 0).astype(np.uint8)
+    skip = (flags != 0).astype(np.uint8)
+    _ref_load_for_timestep(n, np.zeros((n, 3)), flags)
+    R.ref_ts_active_sublist.restype = c_i64
+    with quiet_stdout():
+        R.ref_ts_set_timebins(ptr(timebin))
+    act = np.sort(rng.choice(n, n // 2, replace=False)).astype(np.int32) if with_list else None
+    na = n if act is None else len(act)
+    for ti in (0, 1 << 5, 3 << 4, 1 << 11, (1 << 11) + 64):
+        for mtb in (0, 3, 6, 46):
+            out = np.zeros(na, np.int32)
+            with quiet_stdout():
+                m = R.ref_ts_active_sublist(ptr(act), c_i64(na), c_int(mtb), c_i64(ti), ptr(out))
+            assert np.array_equal(o_active_sublist(act, na, timebin, skip, mtb, ti), out[:m]), (ti, mtb)
+    vel = rng.standard_normal((n, 3)); acc = rng.standard_normal((n, 3)) * 100
+    rvel = vel.copy()
+    with quiet_stdout():
+        R.ref_ts_hierarchical_kick(ptr(rvel), ptr(acc), ptr(act), c_i64(na), c_dbl(0.0371))
+    assert np.array_equal(o_kick(vel, acc, act, skip, 0.0371), rvel)
