@@ -96,23 +96,16 @@ __global__ void __launch_bounds__(256) sq_keys_kernel(const double * __restrict_
     int bad = 0;
     for(int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const double px = pos[3 * i], py = pos[3 * i + 1], pz = pos[3 * i + 2];
+        const unsigned gx = sq_geo_bits(px, box), gy = sq_geo_bits(py, box), gz = sq_geo_bits(pz, box);
         if(GEO) {
-            keys[i] = sq_ph_from_ints(tab, sq_geo_bits(px, box), sq_geo_bits(py, box), sq_geo_bits(pz, box));
+            keys[i] = sq_ph_from_ints(tab, gx, gy, gz);
         } else {
             // peano.h:18-20: no contraction, truncation toward zero
-            const double tx = __dmul_rn(__dadd_rn(px, box2000), domainfac), ty = __dmul_rn(__dadd_rn(py, box2000), domainfac), tz = __dmul_rn(__dadd_rn(pz, box2000), domainfac);
-            const unsigned ix = (unsigned) __double2int_rz(tx), iy = (unsigned) __double2int_rz(ty), iz = (unsigned) __double2int_rz(tz);
+            const unsigned ix = (unsigned) __double2int_rz(__dmul_rn(__dadd_rn(px, box2000), domainfac));
+            const unsigned iy = (unsigned) __double2int_rz(__dmul_rn(__dadd_rn(py, box2000), domainfac));
+            const unsigned iz = (unsigned) __double2int_rz(__dmul_rn(__dadd_rn(pz, box2000), domainfac));
             keys[i] = sq_ph_from_ints(tab, ix, iy, iz);
-            // The geometric descent (`Pos > centre` with the FP64 centre recurrence) and the truncated key can only disagree
-            // for a coordinate within rounding (a few 1e-16 Box = 1e-9 of a finest cell) of a cell face, i.e. when the
-            // fractional part of the scaled coordinate is that close to 0 or 1: only then is the 21-level recurrence run
-            // (threshold 1e-6 of a finest cell: 500 times the bound).
-            const double fx = tx - (double) ix, fy = ty - (double) iy, fz = tz - (double) iz;
-            const double lo = 1e-6, hi = 1.0 - 1e-6;
-            if(fx < lo || fx > hi || fy < lo || fy > hi || fz < lo || fz > hi) {
-                const unsigned gx = sq_geo_bits(px, box), gy = sq_geo_bits(py, box), gz = sq_geo_bits(pz, box);
-                bad |= (ix != gx) | (iy != gy) | (iz != gz);
-            }
+            bad |= (ix != gx) | (iy != gy) | (iz != gz);
         }
     }
     if(!GEO && __any_sync(SQ_FULL, bad) && sq_lane() == 0)
