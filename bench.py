@@ -256,7 +256,13 @@ def run_dist(args, rank, local_rank, world):
     dev = torch.device("cuda", local_rank)
     if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":              # NCCL prints its banner on stdout: keep it to the one JSON line
         del os.environ["NCCL_DEBUG"]
-    dist.init_process_group("nccl", device_id=dev)
+    # a rank that dies (e.g. out of memory) leaves the others waiting inside a collective: give up after --deadline seconds
+    # instead of holding 8 GPUs until somebody's timeout (a 1024^3 attempt of round 2 did exactly that for 15 minutes)
+    import signal
+    import datetime
+    signal.signal(signal.SIGALRM, signal.SIG_DFL)       # default action = the kernel ends the process, even inside a CUDA / NCCL call
+    signal.alarm(max(60, int(args.deadline)))
+    dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=max(60, int(args.deadline))))
     import shenqi_b200 as sq
     from shenqi_b200.ics import zeldovich_torch, clustered_torch, rho0, G_INTERNAL
     from shenqi_b200.dist import DistGravity, CudaBackend, Comm
@@ -525,6 +531,7 @@ def main():
     ap.add_argument("--domain-level", type=int, default=5, help="N > 1: histogram level of the domain's top tree (8^level cells)")
     ap.add_argument("--overdecomposition", type=int, default=4, help="DomainOverDecompositionFactor (gadget/params.cpp:84)")
     ap.add_argument("--tile", type=int, default=1, help="N > 1: build the box from tile^3 periodic copies of an (ngrid / tile)^3 realisation (1024^3 = --ngrid 1024 --tile 2)")
+    ap.add_argument("--deadline", type=float, default=420.0, help="N > 1: seconds after which every rank is ended by SIGALRM whatever it is waiting for")
     ap.add_argument("--no-e2e", action="store_true", help="N > 1: skip the host-buffer leg (e.g. 1024^3: 13 GB of pinned memory per rank)")
     ap.add_argument("--no-verify", dest="verify", action="store_false", help="N > 1: skip the one-rank parity run on rank 0")
     args = ap.parse_args()
