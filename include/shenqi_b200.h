@@ -345,6 +345,19 @@ int sq_gravity_timebins_device(sq_ctx * ctx, const sq_timebin_params * par, cons
 /* timestep.cpp:399-407: TimeBinGravity = min(TimeBinGravity, push_down_bin) over the active list. */
 int sq_timebin_pushdown_device(sq_ctx * ctx, const int32_t * active, int64_t nactive, unsigned char * timebin, int push_down_bin);
 
+/* ---- bigfile snapshot / IC reader (host code; petaio.cpp:590-700, 908-1035 over depends/bigfile) ----------
+ * <file>/<block>/header ("DTYPE: .. NMEMB: .. NFILE: .." + one "%06X: rows : checksum : sysvsum" line per physical file),
+ * raw little-endian rows in <file>/<block>/%06X, attributes in <file>/<block>/attr-v2.  Checksums (byte sum mod 2^32) are
+ * verified for every physical file read in full. */
+int sq_bigfile_block_info(const char * path, const char * block, char * dtype8, int * nmemb, int64_t * nrows, int * nfile);
+/* rows [first, first + count) converted to `want` = "f8" | "f4" | "u8" | "i8" | "u4" | "i4" | "u1"; out: count x nmemb values */
+int sq_bigfile_read_block(const char * path, const char * block, int64_t first, int64_t count, void * out, const char * want);
+/* a numeric attribute as doubles: at most maxn values written, *n = its length */
+int sq_bigfile_read_attr(const char * path, const char * block, const char * name, double * values, int maxn, int * n);
+/* "<ptype>/Position" + "<ptype>/Mass" (or Header.MassTable[ptype] when non-zero) of rows [first, first + count) (count < 0:
+ * to the end) into the context (sq_upload_particles_soa); *boxsize = Header.BoxSize if wanted */
+int sq_upload_particles_bigfile(sq_ctx * ctx, const char * path, int ptype, int64_t first, int64_t count, double * boxsize);
+
 /* ---- timing of the last device stages (CUDA events on the launching stream), milliseconds ------ */
 typedef struct sq_timings {
     double keys_ms, sort_ms, gather_ms, tree_build_ms, tree_moments_ms, walk_ms;

@@ -6,8 +6,8 @@ checked), creating a Context does not.
 """
 from .api import (Context, Params, WalkStats, TreeInfo, Timings, ShenqiError, load_library, library_path,
                   NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin, Domain, LetInfo, domain_from_histogram,
-                  comm_unique_id, comm_loopback_id, TOPNODE_DTYPE, TOPLEAF_DTYPE, TASK_DTYPE)
+                  comm_unique_id, comm_loopback_id, bigfile_block_info, bigfile_read_block, bigfile_read_attr, TOPNODE_DTYPE, TOPLEAF_DTYPE, TASK_DTYPE)
 
 __all__ = ["Context", "Params", "WalkStats", "TreeInfo", "Timings", "ShenqiError", "load_library", "library_path",
            "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin", "Domain", "LetInfo", "domain_from_histogram",
-           "comm_unique_id", "comm_loopback_id", "TOPNODE_DTYPE", "TOPLEAF_DTYPE", "TASK_DTYPE"]
+           "comm_unique_id", "comm_loopback_id", "bigfile_block_info", "bigfile_read_block", "bigfile_read_attr", "TOPNODE_DTYPE", "TOPLEAF_DTYPE", "TASK_DTYPE"]

@@ -115,6 +115,37 @@ def domain_from_histogram(count, nranks, overdecomposition=4, cost=None, max_top
     return Domain(tn[:ntn.value].copy(), tl[:ntl.value].copy(), tk)
 
 
+def bigfile_block_info(path, block):
+    """(dtype, nmemb, nrows, nfile) of a bigfile block (sq_bigfile_block_info; host code, no GPU needed)."""
+    L = load_library()
+    dt = ctypes.create_string_buffer(8); nm, nf, nr = c_int(), c_int(), c_i64()
+    rc = L.sq_bigfile_block_info(path.encode(), block.encode(), dt, ctypes.byref(nm), ctypes.byref(nr), ctypes.byref(nf))
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return dt.value.decode(), nm.value, nr.value, nf.value
+
+
+def bigfile_read_block(path, block, first=0, count=None, want="f8"):
+    """rows [first, first + count) of a bigfile block as a numpy array [count, nmemb] of `want`."""
+    L = load_library()
+    _, nmemb, nrows, _ = bigfile_block_info(path, block)
+    count = nrows - first if count is None else count
+    out = np.zeros((count, nmemb), {"f8": np.float64, "f4": np.float32, "u8": np.uint64, "i8": np.int64, "u4": np.uint32, "i4": np.int32, "u1": np.uint8}[want])
+    rc = L.sq_bigfile_read_block(path.encode(), block.encode(), c_i64(first), c_i64(count), _p(out), want.encode())
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return out
+
+
+def bigfile_read_attr(path, block, name, maxn=64):
+    L = load_library()
+    v = np.zeros(maxn); n = c_int()
+    rc = L.sq_bigfile_read_attr(path.encode(), block.encode(), name.encode(), _p(v), c_int(maxn), ctypes.byref(n))
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return v[:min(n.value, maxn)].copy()
+
+
 def comm_unique_id():
     """ncclGetUniqueId as 128 bytes (numpy uint8): create on one rank, broadcast to all."""
     L = load_library()
@@ -157,7 +188,8 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_gravity_timebins_device", "sq_timebin_pushdown_device",
            "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram",
            "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count", "sq_download_accel_device",
-           "sq_walk_particle_cost", "sq_keys_device", "sq_tree_export_nodes_ex", "sq_tree_local_nodes"]
+           "sq_walk_particle_cost", "sq_keys_device", "sq_tree_export_nodes_ex", "sq_tree_local_nodes",
+           "sq_bigfile_block_info", "sq_bigfile_read_block", "sq_bigfile_read_attr", "sq_upload_particles_bigfile"]
 
 PTR_SORTED_KEYS, PTR_SORTED_POS, PTR_SORTED_MASS, PTR_SORTED_PERM, PTR_WALK_ACCEL, PTR_WALK_POT, PTR_PM_OUT = range(7)
 
@@ -236,6 +268,15 @@ class Context:
         assert parts.dtype.itemsize == 160 and parts.flags.c_contiguous
         self.n = len(parts)
         self._check(self.L.sq_upload_particles_aos(self._ctx, _p(parts), c_i64(self.n), None))
+
+    def upload_particles_bigfile(self, path, ptype=1, first=0, count=-1):
+        """particles of one type of a bigfile snapshot / IC file (petaio's "<type>/Position", "<type>/Mass" or Header.MassTable);
+        returns Header.BoxSize."""
+        box = c_dbl()
+        self._check(self.L.sq_upload_particles_bigfile(self._ctx, path.encode(), c_int(ptype), c_i64(first), c_i64(count), ctypes.byref(box)))
+        _, _, nrows, _ = bigfile_block_info(path, "%d/Position" % ptype)
+        self.n = (nrows - first) if count < 0 else count
+        return box.value
 
     def set_old_accel(self, fulltreegravaccel=None, gravpm=None):
         a = None if fulltreegravaccel is None else np.ascontiguousarray(fulltreegravaccel, np.float64)
