@@ -22,6 +22,15 @@
  *   sq_active_sublist_device build_active_sublist (libgadget/timestep.cpp:111, 1373)
  *   sq_gravity_timebins_device / sq_timebin_pushdown_device
  *                            the bin loop and push-down of hierarchical_gravity_accelerations (libgadget/timestep.cpp:351-407)
+ *   sq_ctx_create_dist       one rank per GPU (README.rst:67): the MPI_COMM_WORLD of the tree path as an NCCL communicator
+ *   sq_domain_set            struct DomainDecomp: topnode_data / topleaf_data / task_data (libgadget/domain.h:12-43)
+ *   sq_domain_from_histogram domain_determine_global_toptree + domain_assign_topleaves_balanced (libgadget/domain.cpp:620-800, 1040-1160)
+ *   sq_tree_build_dist       force_tree_create_topnodes (forcetree.cpp:654-686, 868-933), force_exchange_pseudodata /
+ *                            force_treeupdate_pseudos (:1155-1282), and - as a once-per-build import of remote sub-trees -
+ *                            the export / ghost-walk / reduce cycle of TreeWalk::run_on_queue (treewalk2.h:282-373, 618-812)
+ *   sq_toptree_export_count  GravTopTreeWalk::toptree_visit<TOPTREE_COUNT> (libgadget/gravshort2.hpp:362-438)
+ *   sq_bigfile_*             petaio_read_block over depends/bigfile (libgadget/petaio.cpp:590-700, 908-1035)
+ * The compiled reference-side bindings that call these live in shenqi_b200/host/ (INTEGRATION.md).
  */
 #ifndef SHENQI_B200_H
 #define SHENQI_B200_H
@@ -134,7 +143,9 @@ int sq_set_old_accel(sq_ctx * ctx, const double * fulltreegravaccel, const doubl
 int sq_set_oldacc(sq_ctx * ctx, const double * oldacc);
 
 /* ---- Peano-Hilbert keys + sort (slots_gc_sorted) --------------------------------------------- */
-/* Keys, stable radix sort by (TypeKey, Key), gather into PH order on the device. */
+/* Keys, stable radix sort by Key, gather into PH order on the device.  Collisionless particles of one type only (the
+ * reference sorts by (TypeKey, Key), slotsmanager.cpp:395-412); garbage / swallowed particles uploaded through
+ * sq_upload_particles_aos get the largest key and sort behind every valid particle (its TypeKey 255, :428-432). */
 int sq_ph_sort(sq_ctx * ctx);
 /* keys in upload order (before sort) */
 int sq_get_keys(sq_ctx * ctx, uint64_t * keys);

@@ -6,7 +6,8 @@
 //   * tree side: install a globally PH-sorted particle set that arrived by all-gather (sq_set_sorted_device), walk
 //     only this rank's range of it (sq_tree_walk_range).  Stands where the reference merges the top tree and
 //     exports/imports walks (forcetree.cpp:1144-1282, treewalk2.h:282-373, 742-812): here every rank holds the whole
-//     (fixed-point) tree, which fits 180 GB up to 1024^3 particles, and no walk ever leaves the GPU.
+//     (fixed-point) tree.  TEST MODE since round 2: memory and traffic are O(N_total) per GPU (512^3 fits, 1024^3 does
+//     not); the production tree path is the domain-decomposed one of sq_let.cu (O(N/P + boundary)).
 //   * PM side: x-slab decomposition of the mesh.  Particles are routed to the owner of their x-plane
 //     (sq_pm_slab_route; the reference moves painted cells instead, petapm.cpp:692-1107), painted into the slab plus
 //     one ghost plane (sq_pm_slab_paint; petapm.cpp:1132-1183, 1304-1310), transformed as 2-D r2c per plane ->

@@ -12,7 +12,7 @@ What is exchanged (and what the reference exchanges at the same place):
     every rank builds the whole tree and walks only its own targets.  The reference instead exchanges top-leaf
     moments (forcetree.cpp:1144-1282) and exports each boundary walk to the owner of the pseudo node and imports
     the partial result (treewalk2.h:282-373, 742-812); results are identical because the global tree is the same
-    oct-tree.  The replicated fixed-point tree costs 16 B per particle + 48 B per node per GPU: 1024^3 particles fit.
+    oct-tree.  The replicated tree costs O(N_total) memory and all-gather traffic per GPU (512^3 fits, 1024^3 does not).
   * PM: x-slabs.  Particles go to the owner of their x-plane (all-to-all of 32-byte records), are painted there,
     the one ghost plane goes to the next rank; the 3-D FFT is 2-D per plane, one all-to-all transpose, 1-D along x
     (forward once, backward for the potential and the three force components); results return by the reverse
