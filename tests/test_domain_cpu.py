@@ -134,3 +134,17 @@ def test_world2_gloo_same_domain_on_every_rank():
     assert out[0][3] == out[1][3] == 60000
     table = out[0][4]                                                    # table[s][d] = particles rank s sends to rank d
     assert table.sum() == 60000 and np.all(table.sum(axis=0) > 0)
+
+
+def test_bench_topleaf_lookup_equals_domain_get_topleaf():
+    """bench.py's device-side owner lookup (torch ops) is domain_get_topleaf (domain.h:68-75): checked on CPU tensors."""
+    import sys
+    sys.path.insert(0, os.path.dirname(HERE))
+    import bench
+    import shenqi_b200 as sq
+    box = 8.0
+    pos = random_clustered(50000, box, 3)
+    keys = o_keys(pos, box)
+    D = sq.domain_from_histogram(_hist(keys, 4), 8, 4)
+    got = bench.torch_topleaf(D, torch.from_numpy(keys.astype(np.int64))).numpy()
+    assert np.array_equal(got, D.topleaf_of(keys))
