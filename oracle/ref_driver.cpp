@@ -392,16 +392,91 @@ double ref_grav_short_pair(int Nmesh, double Asmth, double G, double Rcut, doubl
 }
 
 #ifdef REF_HAVE_GRAVPM
-/* gravpm_init_periodic + gravpm_force (gravity.h:71, 86) on the loaded particles; only in builds that link a gravpm
- * implementation (tests/dropin: shenqi_b200/host/gravpm_b200.cpp; the reference's own needs FFTW + heFFTe). */
+/* gravpm_init_periodic + gravpm_force (gravity.h:71, 86) on the loaded particles.  Two builds link a gravpm
+ * implementation: tests/dropin (shenqi_b200/host/gravpm_b200.cpp behind the reference's symbols) and, with
+ * REF_REFERENCE_PM, oracle/_ref itself: the reference's OWN gravpm.cpp + petapm.cpp + powerspectrum.cpp, unmodified,
+ * with only the FFT library behind heFFTe replaced (ref_shim/heffte.h).  The power spectrum file
+ * (powerspectrum_save, powerspectrum.cpp:90-118) goes to the directory set with ref_set_power_dir. */
+static std::string RefPowerDir(".");
+#ifdef REF_REFERENCE_PM
+static void ref_pm_module_init(void);
+#endif
+void ref_set_power_dir(const char * dir) { RefPowerDir = dir ? dir : "."; }
 void ref_gravpm_force(int Nmesh, double Asmth, double G)
 {
     static PetaPM pm;
+#ifdef REF_REFERENCE_PM
+    ref_pm_module_init();
+    /* what run.cpp:257 and the domain decomposition leave behind before gravpm_force builds its tree (gravpm.cpp:97) */
+    init_forcetree_params(0.9);
+    #pragma omp parallel for
+    for(int64_t i = 0; i < PartManager->NumPart; i++)
+        PartManager->Base[i].TopLeaf = domain_get_topleaf(PEANO(PartManager->Base[i].Pos, PartManager->BoxSize), RefDomain.TopNodes);
+#endif
     gravpm_init_periodic(&pm, PartManager->BoxSize, Asmth, Nmesh, G);
     Cosmology CP;
     memset(&CP, 0, sizeof(CP));
     CP.Omega0 = 0.3; CP.OmegaLambda = 0.7; CP.HubbleParam = 0.7;
-    gravpm_force(&pm, &RefDomain, &CP, 0.1, 3.085678e21, std::string("."), 0.01);
+    gravpm_force(&pm, &RefDomain, &CP, 0.1, 3.085678e21, RefPowerDir, 0.01);
+#ifdef REF_REFERENCE_PM
+    petapm_destroy(&pm);
+#endif
+}
+#endif
+#ifdef REF_REFERENCE_PM
+static void ref_pm_module_init(void)
+{
+    static int done = 0;
+    if(!done) { petapm_module_init(omp_get_max_threads(), 0); done = 1; }
+}
+/* petapm_init + petapm_fft_r2c + petapm_fft_c2r (petapm.h:141-146, petapm.cpp:49-71, 197-332) on a caller-supplied mesh:
+ * real_in[x][y][z] (z fastest: the real-space region's strides) -> cplx_out in the fourier region's own order, indexed
+ * (y, z, x) with x fastest (petapm.cpp:265-272), Nmesh^2 (Nmesh/2+1) complex numbers; real_back = c2r(cplx_out), unscaled.
+ * Also returns the two regions' sizes and strides (6 + 6 entries) as petapm_init left them. */
+void ref_petapm_fft(int Nmesh, const double * real_in, double * cplx_out, double * real_back, int64_t * regions)
+{
+    ref_init();
+    ref_pm_module_init();
+    static PetaPM pm;
+    petapm_init(&pm, 1.0, 1.25, Nmesh, 1.0, MPI_COMM_WORLD);
+    const int64_t nreal = (int64_t) Nmesh * Nmesh * Nmesh, ncplx = (int64_t) Nmesh * Nmesh * (Nmesh / 2 + 1);
+    double * real = mymalloc("fftreal", double, pm.priv->fftsize);
+    petapm_complex * cplx = (petapm_complex *) mymalloc("fftcplx", double, pm.priv->fftsize);
+    memcpy(real, real_in, sizeof(double) * nreal);
+    petapm_fft_r2c(&pm, real, cplx);
+    memcpy(cplx_out, cplx, sizeof(double) * 2 * ncplx);
+    petapm_fft_c2r(&pm, cplx, real);
+    memcpy(real_back, real, sizeof(double) * nreal);
+    PetaPMRegion * rr = petapm_get_real_region(&pm), * fr = petapm_get_fourier_region(&pm);
+    for(int k = 0; k < 3; k++) {
+        regions[k] = rr->size[k]; regions[3 + k] = rr->strides[k];
+        regions[6 + k] = fr->size[k]; regions[9 + k] = fr->strides[k];
+    }
+    myfree(cplx);
+    myfree(real);
+    petapm_destroy(&pm);
+}
+/* powerspectrum_add_mode (gravpm.cpp:325-356) + powerspectrum_sum (powerspectrum.cpp:52-88) on caller-supplied modes:
+ * kpos[m][3] signed mesh wave numbers, value[m][2].  Returns the number of non-empty bins; kk / power / nmodes hold
+ * Nmesh entries each. */
+int ref_powerspectrum_bin(int Nmesh, double BoxSize_in_cm, int64_t nmodes_in, const int * kpos, const double * value, const double * invwindow,
+                          double * kk, double * power, int64_t * nmodes, double * norm)
+{
+    Power ps;
+    memset((void *) &ps, 0, sizeof(ps));
+    powerspectrum_alloc(&ps, Nmesh, 1, 0, BoxSize_in_cm);
+    for(int64_t m = 0; m < nmodes_in; m++) {
+        const int * kp = kpos + 3 * m;
+        const int64_t k2 = (int64_t) kp[0] * kp[0] + (int64_t) kp[1] * kp[1] + (int64_t) kp[2] * kp[2];
+        petapm_complex v = {value[2 * m], value[2 * m + 1]};
+        powerspectrum_add_mode(&ps, k2, kp, &v, invwindow ? invwindow[m] : 1.0, Nmesh);
+    }
+    powerspectrum_sum(&ps);
+    for(int i = 0; i < ps.nonzero; i++) { kk[i] = ps.kk[i]; power[i] = ps.Power[i]; nmodes[i] = ps.Nmodes[i]; }
+    *norm = ps.Norm;
+    const int nz = ps.nonzero;
+    powerspectrum_free(&ps);
+    return nz;
 }
 #endif
 void ref_set_potential(const double * pot)

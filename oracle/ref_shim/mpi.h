@@ -87,6 +87,13 @@ static inline int MPI_Abort(MPI_Comm comm, int code) { (void) comm; fprintf(stde
 static inline int MPI_Comm_rank(MPI_Comm comm, int * rank) { (void) comm; *rank = 0; return MPI_SUCCESS; }
 static inline int MPI_Comm_size(MPI_Comm comm, int * size) { (void) comm; *size = 1; return MPI_SUCCESS; }
 static inline int MPI_Barrier(MPI_Comm comm) { (void) comm; return MPI_SUCCESS; }
+/* the 1 x 1 cartesian task grid of the PM (petapm.cpp:233-238, 338, 1220) */
+static inline int MPI_Cart_create(MPI_Comm comm, int ndims, const int * dims, const int * periods, int reorder, MPI_Comm * cart)
+{ (void) periods; (void) reorder; for(int i = 0; i < ndims; i++) if(dims[i] != 1) shim_mpi_unreachable("MPI_Cart_create with more than one task"); *cart = comm; return MPI_SUCCESS; }
+static inline int MPI_Cart_get(MPI_Comm comm, int maxdims, int * dims, int * periods, int * coords)
+{ (void) comm; for(int i = 0; i < maxdims; i++) { dims[i] = 1; periods[i] = 1; coords[i] = 0; } return MPI_SUCCESS; }
+static inline int MPI_Cart_rank(MPI_Comm comm, const int * coords, int * rank) { (void) comm; (void) coords; *rank = 0; return MPI_SUCCESS; }
+static inline int MPI_Comm_free(MPI_Comm * comm) { *comm = MPI_COMM_NULL; return MPI_SUCCESS; }
 static inline double MPI_Wtime(void)
 {
     struct timespec ts;

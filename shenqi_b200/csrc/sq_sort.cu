@@ -172,14 +172,15 @@ __global__ void __launch_bounds__(SORT_THREADS) sq_sort_scatter_kernel(const uin
             const unsigned peers = sq_match8(valid, d);
             const int leader = __ffs(peers) - 1;
             uint32_t b = 0;
-            // one shared-memory atomic per digit group: the rounds do not wait for each other (the atomics of one warp
-            // are applied in issue order, which keeps the sort stable), so the 12 rounds pipeline
+            // one shared-memory atomic per digit group
             if((int) lane == leader) b = atomicAdd(&s.warp_hist[w][d], (uint32_t) __popc(peers));
             b = __shfl_sync(peers, b, leader);
             rnk[r] = b + (uint32_t) __popc(peers & sq_lanemask_lt());
         }
+        // stability needs round r's atomics applied before round r + 1's (different leader lanes may hit the same
+        // digit): the barrier orders the warp's shared-memory accesses explicitly instead of relying on issue order
+        __syncwarp();
     }
-    __syncwarp();
     __syncthreads();
     // thread d: exclusive scan of bin d over warps, then block-wide exclusive scan over bins
     {

@@ -76,6 +76,22 @@ def test_sort_ties_and_edges(ctx):
     assert np.array_equal(perm.astype(np.int64), o_sort(o_keys(pos, 8.0)))
 
 
+def test_sort_stable_with_many_ties_large(ctx):
+    """3 M particles on 125 distinct positions: in every radix pass long runs of equal digits are ranked by different
+    lanes, rounds, warps and tiles; the permutation must be the stable one (ties stay in upload order), as the oracle's."""
+    n = 3_000_000
+    rng = np.random.default_rng(17)
+    pos = np.floor(rng.random((n, 3)) * 5) * (8.0 / 5) + 0.01
+    ctx.set_params(make_params(8.0, 32, n))
+    ctx.upload_particles(pos, np.ones(n, np.float32))
+    ctx.ph_sort()
+    sk, perm = ctx.sorted_keys_perm()
+    k = o_keys(pos, 8.0)
+    operm = o_sort(k)
+    assert np.array_equal(sk, k[operm])
+    assert np.array_equal(perm.astype(np.int64), operm)
+
+
 def test_empty(ctx):
     ctx.set_params(make_params(8.0, 16, 8))
     ctx.upload_particles(np.zeros((0, 3)), np.zeros(0, np.float32))
