@@ -345,6 +345,43 @@ def r_pair(par, meansep):
     return acc, secs
 
 
+# ----------------------------------------------------------------------------- the reference's own PM
+def has_reference_pm():
+    R = ref()
+    return R is not None and hasattr(R, "ref_petapm_fft")
+
+
+REF_SCRATCH = os.path.join(ROOT, "oracle", "_ref", "scratch")
+UNIT_CM = 3.085678e21
+
+
+def r_gravpm_force(pos, mass, box, nmesh, asmth, G, flags=None, types=None, dom=None, pot0=None):
+    """gravpm_init_periodic + gravpm_force of the reference on (pos, mass); returns (Potential, GravPM, P(k) file rows)."""
+    R = ref()
+    n = len(pos)
+    os.makedirs(REF_SCRATCH, exist_ok=True)
+    out = os.path.join(REF_SCRATCH, "powerspectrum-0.1000.txt")
+    if os.path.exists(out):
+        os.remove(out)
+    with quiet_stdout():
+        r_load(pos, mass, box)
+        if flags is not None:
+            R.ref_set_flags(ptr(np.ascontiguousarray(flags, np.uint8)), ptr(None if types is None else np.ascontiguousarray(types, np.uint8)))
+        R.ref_set_potential(ptr(np.zeros(n) if pot0 is None else np.ascontiguousarray(pot0, np.float64)))
+        if dom is not None:
+            R.ref_set_domain(ptr(dom.topnodes), c_int(len(dom.topnodes)), ptr(dom.topleaves), c_int(dom.ntopleaves))
+        R.ref_set_power_dir(REF_SCRATCH.encode())
+        try:
+            R.ref_gravpm_force(c_int(nmesh), c_dbl(asmth), c_dbl(G))
+        finally:
+            if dom is not None:
+                R.ref_set_domain(None, c_int(0), None, c_int(0))
+    g = np.zeros((n, 3)); pot = np.zeros(n)
+    R.ref_get_gravpm(ptr(g))
+    R.ref_get_particles(None, None, None, None, ptr(pot))
+    return pot, g, np.loadtxt(out, ndmin=2)
+
+
 # ----------------------------------------------------------------------------- canonical tree form
 def canonical_tree(nodes, firstnode, ids, box):
     """Node numbering and leaf-slot order are not canonical in the reference (thread caches, merge order),

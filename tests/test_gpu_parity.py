@@ -324,6 +324,25 @@ def test_pm_force(ctx):
     assert np.abs(pot - opot).max() < 1e-10 * np.abs(opot).max()
 
 
+def test_pm_force_against_reference_gravpm_force(ctx):
+    """the GPU PM against gravpm_force of the reference ITSELF (gravpm.cpp + petapm.cpp compiled unmodified into
+    oracle/_ref, only FFTW/heFFTe replaced by a stand-in header; tests/test_reference_pm_cpu.py): accelerations and
+    potentials of clustered particles of unequal mass, in input order."""
+    from helpers import has_reference_pm, r_gravpm_force
+    if not has_reference_pm():
+        pytest.skip("oracle/_ref was built without the reference's PM")
+    box = 8.0; n = 20000; nmesh = 48
+    pos = random_clustered(n, box, 7)
+    mass = (1.0 + 0.25 * (np.arange(n) % 3)).astype(np.float32)
+    P = make_params(box, nmesh, n)
+    ctx.set_params(P)
+    ctx.upload_particles(pos, mass); ctx.ph_sort()
+    gpm, pot = ctx.gravpm_force()
+    rpot, rg, _ = r_gravpm_force(pos, mass, box, nmesh, P.Asmth, P.G)
+    assert np.abs(gpm - rg).max() < 1e-10 * np.abs(rg).max()
+    assert np.abs(pot - rpot).max() < 1e-10 * np.abs(rpot).max()
+
+
 @pytest.mark.parametrize("case", [0, 1, 2, 3])
 def test_reference_gravity_test_bounds(ctx, case):
     """libgadget/tests/test_gravity.cpp on the GPU path, the reference's OWN particle sets, metric and bounds (this is the

@@ -20,45 +20,11 @@ import numpy as np
 import pytest
 
 from helpers import (ROOT, ref, ptr, c_i64, c_dbl, c_int, quiet_stdout, random_clustered, default_params, o_keys, o_pm_force, o_cic_paint,
-                     o_direct27, r_load, r_tree, r_walk, reference_gravity_test_samples, reference_gravity_test_metric)
-
-
-def has_reference_pm():
-    R = ref()
-    return R is not None and hasattr(R, "ref_petapm_fft")
+                     o_direct27, r_load, r_tree, r_walk, reference_gravity_test_samples, reference_gravity_test_metric, has_reference_pm,
+                     r_gravpm_force, UNIT_CM)
 
 
 pytestmark = pytest.mark.skipif(not has_reference_pm(), reason="oracle/_ref was built without the reference's PM")
-
-SCRATCH = os.path.join(ROOT, "oracle", "_ref", "scratch")
-UNIT_CM = 3.085678e21
-
-
-def r_gravpm_force(pos, mass, box, nmesh, asmth, G, flags=None, types=None, dom=None, pot0=None):
-    """gravpm_init_periodic + gravpm_force of the reference on (pos, mass); returns (Potential, GravPM, P(k) file rows)."""
-    R = ref()
-    n = len(pos)
-    os.makedirs(SCRATCH, exist_ok=True)
-    out = os.path.join(SCRATCH, "powerspectrum-0.1000.txt")
-    if os.path.exists(out):
-        os.remove(out)
-    with quiet_stdout():
-        r_load(pos, mass, box)
-        if flags is not None:
-            R.ref_set_flags(ptr(np.ascontiguousarray(flags, np.uint8)), ptr(None if types is None else np.ascontiguousarray(types, np.uint8)))
-        R.ref_set_potential(ptr(np.zeros(n) if pot0 is None else np.ascontiguousarray(pot0, np.float64)))
-        if dom is not None:
-            R.ref_set_domain(ptr(dom.topnodes), c_int(len(dom.topnodes)), ptr(dom.topleaves), c_int(dom.ntopleaves))
-        R.ref_set_power_dir(SCRATCH.encode())
-        try:
-            R.ref_gravpm_force(c_int(nmesh), c_dbl(asmth), c_dbl(G))
-        finally:
-            if dom is not None:
-                R.ref_set_domain(None, c_int(0), None, c_int(0))
-    g = np.zeros((n, 3)); pot = np.zeros(n)
-    R.ref_get_gravpm(ptr(g))
-    R.ref_get_particles(None, None, None, None, ptr(pot))
-    return pot, g, np.loadtxt(out, ndmin=2)
 
 
 def close(a, b, tol):
