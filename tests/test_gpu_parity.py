@@ -325,22 +325,19 @@ def test_pm_force(ctx):
 
 
 def test_pm_force_against_reference_gravpm_force(ctx):
-    """the GPU PM against gravpm_force of the reference ITSELF (gravpm.cpp + petapm.cpp compiled unmodified into
-    oracle/_ref, only FFTW/heFFTe replaced by a stand-in header; tests/test_reference_pm_cpu.py): accelerations and
-    potentials of clustered particles of unequal mass, in input order."""
-    from helpers import has_reference_pm, r_gravpm_force
-    if not has_reference_pm():
-        pytest.skip("oracle/_ref was built without the reference's PM")
-    box = 8.0; n = 20000; nmesh = 48
-    pos = random_clustered(n, box, 7)
-    mass = (1.0 + 0.25 * (np.arange(n) % 3)).astype(np.float32)
-    P = make_params(box, nmesh, n)
+    """the GPU PM against gravpm_force of the reference ITSELF: tests/golden/pm_ref.npz holds what the reference's own
+    gravpm.cpp + petapm.cpp (compiled unmodified into oracle/_ref, only FFTW / heFFTe replaced by a stand-in header;
+    tests/golden/make_golden_pm.py, tests/test_reference_pm_cpu.py) leave in GravPM and add to Potential for 4096 clustered
+    particles of unequal mass at Nmesh 48, in input order."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pm_ref.npz"))
+    pos, mass, box, nmesh = g["pos"], g["mass"], float(g["box"]), int(g["nmesh"])
+    P = make_params(box, nmesh, len(pos), Asmth=float(g["asmth"]), G=float(g["G"]))
     ctx.set_params(P)
     ctx.upload_particles(pos, mass); ctx.ph_sort()
     gpm, pot = ctx.gravpm_force()
-    rpot, rg, _ = r_gravpm_force(pos, mass, box, nmesh, P.Asmth, P.G)
-    assert np.abs(gpm - rg).max() < 1e-10 * np.abs(rg).max()
-    assert np.abs(pot - rpot).max() < 1e-10 * np.abs(rpot).max()
+    assert np.abs(gpm - g["gravpm"]).max() < 1e-10 * np.abs(g["gravpm"]).max()
+    assert np.abs(pot - g["potential"]).max() < 1e-10 * np.abs(g["potential"]).max()
 
 
 @pytest.mark.parametrize("case", [0, 1, 2, 3])

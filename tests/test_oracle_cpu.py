@@ -267,6 +267,16 @@ def test_oracle_cic_conserves_mass_and_reads_back():
     assert np.allclose(o_cic_readout(xs, pos, box, nmesh)[inner], pos[inner, 0], rtol=1e-10, atol=1e-10)
 
 
+def test_oracle_pm_equals_reference_golden():
+    """the PM restatement against tests/golden/pm_ref.npz = outputs of the reference's OWN gravpm_force (gravpm.cpp +
+    petapm.cpp compiled unmodified, tests/golden/make_golden_pm.py): the code-level pin of rows a19-a22 that travels
+    without /root/reference and without oracle/_ref (tests/test_reference_pm_cpu.py is the live version)."""
+    g = np.load(os.path.join(GOLDEN, "pm_ref.npz"))
+    opot, oacc = o_pm_force(g["pos"], g["mass"], float(g["box"]), int(g["nmesh"]), float(g["asmth"]), float(g["G"]))
+    assert np.abs(oacc - g["gravpm"]).max() < 1e-12 * np.abs(g["gravpm"]).max()
+    assert np.abs(opot - g["potential"]).max() < 1e-12 * np.abs(g["potential"]).max()
+
+
 def oracle_reference_gravity_test(pos, box=8.0, nmesh=48):
     """do_force_test of libgadget/tests/test_gravity.cpp:197-247 by the CPU restatement: gravpm_force, force_tree_full,
     then grav_short_tree twice - Barnes-Hut (TreeUseBH = 2, angle 0.175) and then the relative criterion with the
