@@ -278,6 +278,11 @@ int sq_comm_loopback_id(void * id128, int key);
  * the tree then carries the forced top-level nodes of the domain, as the reference's does. */
 int sq_domain_set(sq_ctx * ctx, const sq_topnode * topnodes, int ntopnodes, const sq_topleaf * topleaves, int ntopleaves,
                   const sq_task * tasks, int ntasks);
+/* Pure host code: the consistency checks sq_domain_set applies to a DomainDecomp (daughters in key order with
+ * StartKey / Shift as domain.cpp:849-868, every leaf numbered once, tasks own contiguous leaf ranges); *maxlevel = depth
+ * of the deepest top node.  SQ_OK if the domain would be accepted. */
+int sq_domain_validate(const sq_topnode * topnodes, int ntopnodes, const sq_topleaf * topleaves, int ntopleaves,
+                       const sq_task * tasks, int ntasks, int * maxlevel);
 int sq_domain_get_treenodes(sq_ctx * ctx, int32_t * treenode /* [ntopleaves], node numbers relative to the first node */);
 /* Pure host code, no CUDA device needed: a top tree from a histogram of the particles' Peano-Hilbert keys over the
  * 8^level cells of level `level` (cell = key >> (63 - 3 level)), refined until no leaf holds more than
@@ -287,6 +292,12 @@ int sq_domain_get_treenodes(sq_ctx * ctx, int32_t * treenode /* [ntopleaves], no
 int sq_domain_from_histogram(const int64_t * count, const double * cost, int level, int nranks, int overdecomposition,
                              sq_topnode * topnodes, sq_topleaf * topleaves, sq_task * tasks, int max_topnodes,
                              int * ntopnodes, int * ntopleaves);
+/* Pure host code: the reference's own assignment of top leaves to tasks (domain_assign_topleaves_balanced,
+ * domain.cpp:620-778), leaf for leaf: cost[k] = integer cost of the k-th top leaf in Peano-Hilbert key order,
+ * task[k] = its task.  With nsegment_per_task = 1 (what the reference calls it with: domain_balance,
+ * domain.cpp:506-526) the tasks are contiguous in key order.  Fails if there are fewer leaves than
+ * nranks * nsegment_per_task. */
+int sq_domain_assign_balanced(const int64_t * cost, int ntopleaves, int nranks, int nsegment_per_task, int32_t * task);
 /* Histogram of this rank's uploaded particles over the level-`level` cells, summed over ranks (ncclAllReduce when the
  * context is distributed); weights = per-particle cost in upload order (device or host pointer) or NULL. */
 int sq_domain_histogram(sq_ctx * ctx, int level, int64_t * count, double * cost, const float * weights);

@@ -3,8 +3,8 @@
  * The reference (MP-Gadget/shenqi) needs MPI to compile; MPI is not installed in
  * this image.  This header lets the reference's own, unmodified sources for the
  * short-range gravity path compile into oracle/_ref/ as a one-rank program.
- * Every collective degenerates to a local copy; point-to-point calls are never
- * reached with one rank (there is nobody to export to) and abort if they are.
+ * Every collective degenerates to a local copy; point-to-point calls work only
+ * from rank 0 to itself and abort for any other partner.
  *
  * Nothing in the product (shenqi_b200/) includes this file.
  */
@@ -85,7 +85,11 @@ static inline int MPI_Finalize(void) { return MPI_SUCCESS; }
 static inline int MPI_Initialized(int * flag) { *flag = 1; return MPI_SUCCESS; }
 static inline int MPI_Abort(MPI_Comm comm, int code) { (void) comm; fprintf(stderr, "MPI_Abort(%d)\n", code); abort(); return 0; }
 static inline int MPI_Comm_rank(MPI_Comm comm, int * rank) { (void) comm; *rank = 0; return MPI_SUCCESS; }
-static inline int MPI_Comm_size(MPI_Comm comm, int * size) { (void) comm; *size = 1; return MPI_SUCCESS; }
+/* One rank - except that a translation unit may set shim_mpi_fake_size to drive PURELY LOCAL functions of the reference that
+ * only read the task count (domain_assign_topleaves_balanced, domain.cpp:620-778) for more than one task; no communication
+ * works at such a size (every collective is still a local copy). */
+static int shim_mpi_fake_size = 0;
+static inline int MPI_Comm_size(MPI_Comm comm, int * size) { (void) comm; *size = shim_mpi_fake_size > 0 ? shim_mpi_fake_size : 1; return MPI_SUCCESS; }
 static inline int MPI_Barrier(MPI_Comm comm) { (void) comm; return MPI_SUCCESS; }
 /* the 1 x 1 cartesian task grid of the PM (petapm.cpp:233-238, 338, 1220) */
 static inline int MPI_Cart_create(MPI_Comm comm, int ndims, const int * dims, const int * periods, int reorder, MPI_Comm * cart)
@@ -138,10 +142,78 @@ static inline int MPI_Allgatherv(const void * sendbuf, int sendcount, MPI_Dataty
 static inline int MPI_Gather(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, int recvcount, MPI_Datatype recvtype, int root, MPI_Comm comm)
 { (void) recvcount; (void) recvtype; (void) root; (void) comm; return shim_mpi_copy(sendbuf, recvbuf, sendcount, sendtype); }
 
-static inline int MPI_Isend(const void * buf, int count, MPI_Datatype type, int dest, int tag, MPI_Comm comm, MPI_Request * req)
-{ (void) buf; (void) count; (void) type; (void) dest; (void) tag; (void) comm; (void) req; shim_mpi_unreachable("MPI_Isend"); return 0; }
+static inline int MPI_Gatherv(const void * sendbuf, int sendcount, MPI_Datatype sendtype, void * recvbuf, const int * recvcounts, const int * displs, MPI_Datatype recvtype, int root, MPI_Comm comm)
+{
+    (void) recvcounts; (void) root; (void) comm;
+    if(sendbuf == MPI_IN_PLACE) return MPI_SUCCESS;
+    memmove((char *) recvbuf + (size_t) displs[0] * recvtype, sendbuf, (size_t) sendcount * sendtype);
+    return MPI_SUCCESS;
+}
+static inline int MPI_Scatterv(const void * sendbuf, const int * sendcounts, const int * displs, MPI_Datatype sendtype, void * recvbuf, int recvcount, MPI_Datatype recvtype, int root, MPI_Comm comm)
+{
+    (void) recvcount; (void) recvtype; (void) root; (void) comm;
+    if(recvbuf == MPI_IN_PLACE) return MPI_SUCCESS;
+    memmove(recvbuf, (const char *) sendbuf + (size_t) displs[0] * sendtype, (size_t) sendcounts[0] * sendtype);
+    return MPI_SUCCESS;
+}
+/* the only partner of rank 0 is rank 0 */
+static inline int MPI_Sendrecv(const void * sendbuf, int sendcount, MPI_Datatype sendtype, int dest, int sendtag, void * recvbuf, int recvcount, MPI_Datatype recvtype,
+        int source, int recvtag, MPI_Comm comm, MPI_Status * st)
+{
+    (void) sendtag; (void) recvcount; (void) recvtype; (void) recvtag; (void) comm; (void) st;
+    if(dest != 0 || source != 0) shim_mpi_unreachable("MPI_Sendrecv with another rank");
+    return shim_mpi_copy(sendbuf, recvbuf, sendcount, sendtype);
+}
+static inline int MPI_Comm_split(MPI_Comm comm, int color, int key, MPI_Comm * newcomm) { (void) color; (void) key; *newcomm = comm; return MPI_SUCCESS; }
+
+/* Point-to-point with oneself (rank 0 -> rank 0), as MPI_Alltoallv_sparse (utils/system.cpp:264-325) does even on one
+ * rank: a receive is posted and the matching send (same tag, same translation unit) copies into it, or the other way
+ * round through a buffered copy.  Any other partner aborts. */
+typedef struct { void * buf; size_t bytes; int tag; int live; } shim_mpi_post;
+static shim_mpi_post shim_mpi_recvs[64], shim_mpi_sends[64];
 static inline int MPI_Irecv(void * buf, int count, MPI_Datatype type, int src, int tag, MPI_Comm comm, MPI_Request * req)
-{ (void) buf; (void) count; (void) type; (void) src; (void) tag; (void) comm; (void) req; shim_mpi_unreachable("MPI_Irecv"); return 0; }
+{
+    (void) comm;
+    if(src != 0 && src != MPI_ANY_SOURCE) shim_mpi_unreachable("MPI_Irecv from another rank");
+    const size_t bytes = (size_t) count * (size_t) type;
+    if(req) *req = 0;
+    for(int i = 0; i < 64; i++)
+        if(shim_mpi_sends[i].live && (tag == MPI_ANY_TAG || shim_mpi_sends[i].tag == tag)) {
+            memcpy(buf, shim_mpi_sends[i].buf, bytes < shim_mpi_sends[i].bytes ? bytes : shim_mpi_sends[i].bytes);
+            free(shim_mpi_sends[i].buf);
+            shim_mpi_sends[i].live = 0;
+            return MPI_SUCCESS;
+        }
+    for(int i = 0; i < 64; i++)
+        if(!shim_mpi_recvs[i].live) {
+            shim_mpi_recvs[i].buf = buf; shim_mpi_recvs[i].bytes = bytes; shim_mpi_recvs[i].tag = tag; shim_mpi_recvs[i].live = 1;
+            return MPI_SUCCESS;
+        }
+    shim_mpi_unreachable("MPI_Irecv: more than 64 receives posted");
+    return 0;
+}
+static inline int MPI_Isend(const void * buf, int count, MPI_Datatype type, int dest, int tag, MPI_Comm comm, MPI_Request * req)
+{
+    (void) comm;
+    if(dest != 0) shim_mpi_unreachable("MPI_Isend to another rank");
+    const size_t bytes = (size_t) count * (size_t) type;
+    if(req) *req = 0;
+    for(int i = 0; i < 64; i++)
+        if(shim_mpi_recvs[i].live && (shim_mpi_recvs[i].tag == MPI_ANY_TAG || shim_mpi_recvs[i].tag == tag)) {
+            memcpy(shim_mpi_recvs[i].buf, buf, bytes < shim_mpi_recvs[i].bytes ? bytes : shim_mpi_recvs[i].bytes);
+            shim_mpi_recvs[i].live = 0;
+            return MPI_SUCCESS;
+        }
+    for(int i = 0; i < 64; i++)
+        if(!shim_mpi_sends[i].live) {
+            shim_mpi_sends[i].buf = malloc(bytes ? bytes : 1);
+            memcpy(shim_mpi_sends[i].buf, buf, bytes);
+            shim_mpi_sends[i].bytes = bytes; shim_mpi_sends[i].tag = tag; shim_mpi_sends[i].live = 1;
+            return MPI_SUCCESS;
+        }
+    shim_mpi_unreachable("MPI_Isend: more than 64 sends pending");
+    return 0;
+}
 static inline int MPI_Send(const void * buf, int count, MPI_Datatype type, int dest, int tag, MPI_Comm comm)
 { (void) buf; (void) count; (void) type; (void) dest; (void) tag; (void) comm; shim_mpi_unreachable("MPI_Send"); return 0; }
 static inline int MPI_Recv(void * buf, int count, MPI_Datatype type, int src, int tag, MPI_Comm comm, MPI_Status * st)

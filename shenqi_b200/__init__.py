@@ -5,9 +5,9 @@ of include/shenqi_b200.h).  There is no CPU fallback: importing works without a 
 checked), creating a Context does not.
 """
 from .api import (Context, Params, WalkStats, TreeInfo, Timings, ShenqiError, load_library, library_path,
-                  NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin, Domain, LetInfo, domain_from_histogram,
+                  NODE_DTYPE, PARTICLE_DTYPE, TimebinParams, pushdown_bin, Domain, LetInfo, domain_from_histogram, domain_assign_balanced,
                   comm_unique_id, comm_loopback_id, bigfile_block_info, bigfile_read_block, bigfile_read_attr, TOPNODE_DTYPE, TOPLEAF_DTYPE, TASK_DTYPE)
 
 __all__ = ["Context", "Params", "WalkStats", "TreeInfo", "Timings", "ShenqiError", "load_library", "library_path",
-           "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin", "Domain", "LetInfo", "domain_from_histogram",
+           "NODE_DTYPE", "PARTICLE_DTYPE", "TimebinParams", "pushdown_bin", "Domain", "LetInfo", "domain_from_histogram", "domain_assign_balanced",
            "comm_unique_id", "comm_loopback_id", "bigfile_block_info", "bigfile_read_block", "bigfile_read_attr", "TOPNODE_DTYPE", "TOPLEAF_DTYPE", "TASK_DTYPE"]

@@ -82,6 +82,17 @@ class Domain:
     def ntopleaves(self):
         return len(self.topleaves)
 
+    def validate(self):
+        """sq_domain_validate (pure host code): raises if sq_domain_set would refuse this domain; returns the depth of
+        the deepest top node."""
+        L = load_library()
+        ml = c_int()
+        rc = L.sq_domain_validate(_p(self.topnodes), c_int(len(self.topnodes)), _p(self.topleaves), c_int(len(self.topleaves)),
+                                  _p(self.tasks), c_int(len(self.tasks)), ctypes.byref(ml))
+        if rc != 0:
+            raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+        return ml.value
+
     def topleaf_of(self, keys):
         """domain_get_topleaf (domain.h:68-75), vectorised."""
         keys = np.asarray(keys, np.uint64)
@@ -97,9 +108,44 @@ class Domain:
         return T["Leaf"][no]
 
 
-def domain_from_histogram(count, nranks, overdecomposition=4, cost=None, max_topnodes=None):
+def domain_assign_balanced(cost, nranks, nsegment_per_task=1):
+    """sq_domain_assign_balanced (pure host code): the reference's own assignment of top leaves to tasks
+    (domain_assign_topleaves_balanced, libgadget/domain.cpp:620-778); cost = integer cost per top leaf in key order;
+    returns the task of every leaf."""
+    L = load_library()
+    cost = np.ascontiguousarray(cost, np.int64)
+    task = np.zeros(len(cost), np.int32)
+    rc = L.sq_domain_assign_balanced(_p(cost), c_int(len(cost)), c_int(nranks), c_int(nsegment_per_task), _p(task))
+    if rc != 0:
+        raise ShenqiError("shenqi_b200 error %d: %s" % (rc, L.sq_last_error().decode()))
+    return task
+
+
+def domain_from_histogram(count, nranks, overdecomposition=4, cost=None, max_topnodes=None, assign="bisect"):
     """sq_domain_from_histogram (pure host code, no GPU needed): a Domain from a Peano-Hilbert key histogram over the
-    8^level cells of one level."""
+    8^level cells of one level.  assign = "bisect": segments cut where the running cost crosses k / nranks of the total;
+    "reference": the leaves of the same top tree assigned by the reference's own greedy rule (domain_assign_balanced;
+    costs rounded to integers, as the reference's are)."""
+    D = _domain_from_histogram(count, nranks, overdecomposition, cost, max_topnodes)
+    if assign == "bisect":
+        return D
+    assert assign == "reference", assign
+    count = np.ascontiguousarray(count, np.int64)
+    w = count if cost is None else np.rint(np.ascontiguousarray(cost, np.float64)).astype(np.int64)
+    level = int(round(np.log2(len(count)) / 3))
+    T = D.topnodes[D.topleaves["topnode"]]                   # leaves are in key order
+    a = (T["StartKey"] >> np.uint64(63 - 3 * level)).astype(np.int64)
+    b = a + (np.int64(1) << (T["Shift"].astype(np.int64) - (63 - 3 * level)))
+    pre = np.concatenate([[0], np.cumsum(w)])
+    task = domain_assign_balanced(pre[b] - pre[a], nranks)
+    D.topleaves["Task"] = task
+    for t in range(nranks):
+        mine = np.flatnonzero(task == t)
+        D.tasks[t] = (mine[0], mine[-1] + 1)
+    return D
+
+
+def _domain_from_histogram(count, nranks, overdecomposition=4, cost=None, max_topnodes=None):
     L = load_library()
     count = np.ascontiguousarray(count, np.int64)
     level = int(round(np.log2(len(count)) / 3))
@@ -186,7 +232,7 @@ EXPORTS = ["sq_last_error", "sq_version", "sq_ctx_create", "sq_ctx_destroy", "sq
            "sq_pm_slab_route", "sq_pm_slab_unroute", "sq_pm_slab_paint", "sq_pm_slab_fft_fwd", "sq_pm_slab_fft_x", "sq_pm_slab_transfer", "sq_pm_slab_transfer_phi", "sq_pm_slab_gradient",
            "sq_pm_slab_fft_inv", "sq_pm_slab_readout", "sq_drift_device", "sq_kick_device", "sq_active_sublist_device",
            "sq_gravity_timebins_device", "sq_timebin_pushdown_device",
-           "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram",
+           "sq_comm_unique_id", "sq_comm_loopback_id", "sq_ctx_create_dist", "sq_comm_rank", "sq_domain_set", "sq_domain_get_treenodes", "sq_domain_from_histogram", "sq_domain_assign_balanced", "sq_domain_validate",
            "sq_domain_histogram", "sq_domain_owner", "sq_tree_build_dist", "sq_toptree_export_count", "sq_download_accel_device",
            "sq_walk_particle_cost", "sq_keys_device", "sq_tree_export_nodes_ex", "sq_tree_local_nodes",
            "sq_bigfile_block_info", "sq_bigfile_read_block", "sq_bigfile_read_attr", "sq_upload_particles_bigfile"]

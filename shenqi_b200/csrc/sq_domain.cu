@@ -101,6 +101,63 @@ extern "C" int sq_domain_from_histogram(const int64_t * count, const double * co
     return SQ_OK;
 }
 
+// ------------------------------------------------------------------------------------ host: the reference's leaf assignment
+// domain_assign_topleaves_balanced (domain.cpp:620-778) restated: the top leaves, in Peano-Hilbert key order with their
+// integer costs, are cut greedily into nranks * nsegment_per_task contiguous segments whose running total follows the
+// mean (a leaf joins the open segment while less than half of it would overshoot; a segment is never empty; the last
+// leaves are kept back so that every segment gets one), and consecutive segments fill one task after the other until
+// the task holds its share; when every task has been served and leaves remain, the means are recomputed from what is
+// left and the tasks are served again.  task[k] = task of leaf k.  Pinned against the reference's own function for
+// random costs and task counts (oracle/ref_domain.cpp, tests/test_domain_cpu.py): equal for every leaf.
+extern "C" int sq_domain_assign_balanced(const int64_t * cost, int ntopleaves, int nranks, int nsegment_per_task, int32_t * task)
+{
+    if(!cost || !task || ntopleaves < 1 || nranks < 1 || nsegment_per_task < 1) { sq_set_error("sq_domain_assign_balanced: bad argument"); return SQ_ERR_ARG; }
+    const int nseg = nranks * nsegment_per_task;
+    if(ntopleaves < nseg) { sq_set_error("sq_domain_assign_balanced: %d top leaves cannot fill %d segments", ntopleaves, nseg); return SQ_ERR_ARG; }
+    int64_t total = 0;
+    for(int k = 0; k < ntopleaves; k++) {
+        if(cost[k] < 0) { sq_set_error("sq_domain_assign_balanced: negative cost"); return SQ_ERR_ARG; }
+        total += cost[k];
+    }
+    int64_t unassigned = total;              // cost of the leaves behind the closed segments
+    double seg_share = 1.0 * total / nseg;   // what a segment / a task should hold in this pass over the tasks
+    double task_share = 1.0 * total / nranks;
+    int leaf = 0, seg = 0, t = 0, passes = 0;
+    int64_t open = 0, task_load = 0;         // cost in the open segment / in the task being filled
+    while(passes < ntopleaves) {
+        bool take, close;
+        if(leaf == ntopleaves) { take = false; close = true; }
+        else if(ntopleaves - leaf == nseg - seg) { take = true; close = true; }     // one leaf per segment still to come
+        else {
+            const int64_t done = (total - unassigned) + open;
+            take = (seg_share * (seg + 1) - done > 0.5 * cost[leaf]) || open == 0;
+            close = !take;
+        }
+        if(take) {
+            open += cost[leaf];
+            task[leaf++] = t;
+        }
+        if(!close) continue;
+        task_load += open;
+        if((task_share - task_load < 0.5 * seg_share) || (nseg - seg <= nranks - t)) {
+            task_load = 0;
+            t++;
+        }
+        unassigned -= open;
+        open = 0;
+        seg++;
+        if(t == nranks) {
+            t = 0;
+            seg_share = 1.0 * unassigned / nseg;
+            task_share = 1.0 * unassigned / nranks;
+            passes++;
+        }
+        if(leaf == ntopleaves) break;
+    }
+    if(seg < nseg || unassigned != 0) { sq_set_error("sq_domain_assign_balanced: %d of %d segments, %lld cost left", seg, nseg, (long long) unassigned); return SQ_ERR_ARG; }
+    return SQ_OK;
+}
+
 // ------------------------------------------------------------------------------------ install / query
 static int sq_domain_check(const sq_topnode * tn, int ntn, const sq_topleaf * tl, int ntl, const sq_task * tk, int ntk, int * maxlevel)
 {
@@ -133,6 +190,18 @@ static int sq_domain_check(const sq_topnode * tn, int ntn, const sq_topleaf * tl
     }
     *maxlevel = ml;
     return 0;
+}
+
+// the consistency checks sq_domain_set applies, without a context (pure host code): 0 = accepted, else the failed check
+extern "C" int sq_domain_validate(const sq_topnode * topnodes, int ntopnodes, const sq_topleaf * topleaves, int ntopleaves,
+                                  const sq_task * tasks, int ntasks, int * maxlevel)
+{
+    if(!topnodes || !topleaves || !tasks) { sq_set_error("sq_domain_validate: null argument"); return SQ_ERR_ARG; }
+    int ml = 0;
+    const int bad = sq_domain_check(topnodes, ntopnodes, topleaves, ntopleaves, tasks, ntasks, &ml);
+    if(bad) { sq_set_error("inconsistent DomainDecomp (check %d)", bad); return SQ_ERR_ARG; }
+    if(maxlevel) *maxlevel = ml;
+    return SQ_OK;
 }
 
 extern "C" int sq_domain_set(sq_ctx * c, const sq_topnode * topnodes, int ntopnodes, const sq_topleaf * topleaves, int ntopleaves,

@@ -148,3 +148,63 @@ def test_bench_topleaf_lookup_equals_domain_get_topleaf():
     D = sq.domain_from_histogram(_hist(keys, 4), 8, 4)
     got = bench.torch_topleaf(D, torch.from_numpy(keys.astype(np.int64))).numpy()
     assert np.array_equal(got, D.topleaf_of(keys))
+
+
+# ------------------------------------------------------------------------------------------ pinned to the reference's domain.cpp
+def _has_ref_domain():
+    R = ref()
+    return R is not None and hasattr(R, "ref_domain_assign_balanced")
+
+
+needs_ref_domain = pytest.mark.skipif(not _has_ref_domain(), reason="oracle/_ref was built without the reference's domain.cpp")
+
+
+def _ref_assign(cost, ntask, nspt, rng):
+    """domain_assign_topleaves_balanced + domain_set_task_leafs of the reference itself (oracle/ref_domain.cpp) on leaves
+    handed over in scrambled order; returns (task of every leaf in key order, tasks table)."""
+    import ctypes
+    import shenqi_b200 as sq
+    from helpers import ptr, quiet_stdout
+    nl = len(cost)
+    tn = np.zeros(nl + 1, sq.TOPNODE_DTYPE)                     # a root and one top node per leaf, StartKey ascending
+    tn["StartKey"][1:] = np.arange(nl, dtype=np.uint64) * np.uint64(8)
+    tn["Daughter"] = -1; tn["Shift"] = 3
+    perm = rng.permutation(nl)
+    leaf_topnode = (1 + perm).astype(np.int32)
+    task = np.zeros(nl, np.int32); topn = np.zeros(nl, np.int32); tasks = np.zeros(2 * ntask, np.int32)
+    with quiet_stdout():
+        ref().ref_domain_assign_balanced(ctypes.c_int(ntask), ctypes.c_int(nspt), ctypes.c_int(nl + 1), ptr(tn), ctypes.c_int(nl), ptr(leaf_topnode),
+                                         ptr(np.ascontiguousarray(cost[perm])), ptr(task), ptr(topn), ptr(tasks))
+    by_key = np.zeros(nl, np.int32)
+    by_key[topn - 1] = task                                     # the reference returns the leaves sorted by (Task, Key)
+    return by_key, tasks.reshape(ntask, 2)
+
+
+@needs_ref_domain
+def test_assign_balanced_equals_reference_domain_cpp():
+    """sq_domain_assign_balanced against the reference's OWN domain_assign_topleaves_balanced (domain.cpp:620-778): the
+    same task for EVERY leaf, for 300 random (task count, segments per task, leaf count, cost distribution) draws -
+    uniform, heavy-tailed (a few leaves hold most of the cost), constant, and mostly-zero costs."""
+    import shenqi_b200 as sq
+    rng = np.random.default_rng(0)
+    for trial in range(300):
+        ntask = int(rng.integers(1, 17)); nspt = int(rng.choice([1, 1, 1, 2, 4]))
+        nl = int(rng.integers(ntask * nspt, ntask * nspt * 12 + 2))
+        kind = trial % 4
+        if kind == 0:
+            cost = rng.integers(0, 1000, nl)
+        elif kind == 1:
+            cost = (rng.pareto(1.2, nl) * 100).astype(np.int64)
+        elif kind == 2:
+            cost = np.full(nl, 7)
+        else:
+            cost = rng.integers(0, 3, nl) * rng.integers(1, 10 ** 6, nl)
+        cost = cost.astype(np.int64)
+        want, tasks = _ref_assign(cost, ntask, nspt, rng)
+        got = sq.domain_assign_balanced(cost, ntask, nspt)
+        assert np.array_equal(got, want), (trial, ntask, nspt, nl, kind)
+        if nspt == 1:                                           # one segment per task: contiguous, every task served
+            assert np.all(np.diff(got) >= 0) and len(np.unique(got)) == ntask
+            for t in range(ntask):
+                mine = np.flatnonzero(got == t)
+                assert (tasks[t, 0], tasks[t, 1]) == (mine[0], mine[-1] + 1)
