@@ -25,6 +25,7 @@
  *   sq_ctx_create_dist       one rank per GPU (README.rst:67): the MPI_COMM_WORLD of the tree path as an NCCL communicator
  *   sq_domain_set            struct DomainDecomp: topnode_data / topleaf_data / task_data (libgadget/domain.h:12-43)
  *   sq_domain_from_histogram domain_determine_global_toptree + domain_assign_topleaves_balanced (libgadget/domain.cpp:620-800, 1040-1160)
+ *   sq_domain_assign_balanced domain_assign_topleaves_balanced, leaf for leaf (libgadget/domain.cpp:620-778)
  *   sq_tree_build_dist       force_tree_create_topnodes (forcetree.cpp:654-686, 868-933), force_exchange_pseudodata /
  *                            force_treeupdate_pseudos (:1155-1282), and - as a once-per-build import of remote sub-trees -
  *                            the export / ghost-walk / reduce cycle of TreeWalk::run_on_queue (treewalk2.h:282-373, 618-812)

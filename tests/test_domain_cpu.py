@@ -208,3 +208,79 @@ def test_assign_balanced_equals_reference_domain_cpp():
             for t in range(ntask):
                 mine = np.flatnonzero(got == t)
                 assert (tasks[t, 0], tasks[t, 1]) == (mine[0], mine[-1] + 1)
+
+
+def _ref_decompose(pos, box, over):
+    """domain_decompose_full (domain.cpp:174-277) of the reference on one rank; returns (Domain, Part[].TopLeaf in the
+    reference's sorted order, sorted positions)."""
+    import ctypes
+    import shenqi_b200 as sq
+    from helpers import ptr, quiet_stdout, r_load, r_sorted_particles
+    R = ref()
+    n = len(pos)
+    tn = np.zeros(200000, sq.TOPNODE_DTYPE); tl = np.zeros(200000, sq.TOPLEAF_DTYPE); ntl = ctypes.c_int()
+    with quiet_stdout():
+        r_load(pos, np.ones(n, np.float32), box, ids=np.arange(1, n + 1, dtype=np.uint64))
+        nn = R.ref_domain_decompose_full(ctypes.c_int(over), ctypes.c_double(0.5), ptr(tn), ctypes.c_int(len(tn)), ptr(tl), ctypes.c_int(len(tl)),
+                                         ctypes.byref(ntl))
+    D = sq.Domain(tn[:nn].copy(), tl[:ntl.value].copy(), np.array([(0, ntl.value)], sq.TASK_DTYPE))
+    topleaf = np.zeros(n, np.int32)
+    R.ref_domain_get_topleaf(ptr(topleaf))
+    spos, _, _ = r_sorted_particles()
+    return D, topleaf, spos
+
+
+@needs_ref_domain
+@pytest.mark.parametrize("over,seed", [(4, 21), (16, 22), (64, 23)])
+def test_domain_of_reference_domain_decompose_full_is_accepted(over, seed):
+    """a DomainDecomp the reference ITSELF builds (domain_decompose_full on clustered particles: subsampled top tree,
+    refinement, truncation, leaves of unequal depth) passes the checks sq_domain_set applies (sq_domain_validate), and
+    the host-side domain_get_topleaf restatement (Domain.topleaf_of) gives Part[i].TopLeaf for every particle."""
+    box = 8.0
+    pos = random_clustered(60000, box, seed)
+    D, topleaf, spos = _ref_decompose(pos, box, over)
+    assert D.ntopleaves >= over
+    maxlevel = D.validate()
+    lv = (63 - D.topnodes["Shift"]) // 3
+    assert maxlevel == lv.max() and len(np.unique(lv[D.topnodes["Daughter"] < 0])) > 1          # leaves of unequal depth
+    assert np.array_equal(D.topleaf_of(o_keys(spos, box)), topleaf)
+    # slots_gc_sorted at the end of domain_decompose_full leaves the particles in key order: leaves are then contiguous
+    assert np.all(np.diff(topleaf) >= 0)
+
+
+def test_domain_validate_refuses_broken_domains():
+    import shenqi_b200 as sq
+    keys = o_keys(random_clustered(20000, 8.0, 1), 8.0)
+    D = sq.domain_from_histogram(_hist(keys, 3), 4, 4)
+    assert D.validate() >= 1
+    for breaker in ("startkey", "leaf", "task", "range"):
+        B = sq.Domain(D.topnodes.copy(), D.topleaves.copy(), D.tasks.copy())
+        if breaker == "startkey":
+            B.topnodes["StartKey"][B.topnodes["Daughter"][0] + 3] += np.uint64(1)
+        elif breaker == "leaf":
+            B.topnodes["Leaf"][np.flatnonzero(B.topnodes["Daughter"] < 0)[0]] = B.ntopleaves
+        elif breaker == "task":
+            B.topleaves["Task"][0] = 4
+        else:
+            B.tasks["EndLeaf"][0] += 1
+        with pytest.raises(sq.ShenqiError, match="inconsistent DomainDecomp"):
+            B.validate()
+
+
+@pytest.mark.parametrize("nranks,level,over", [(2, 3, 4), (8, 3, 4), (8, 4, 8), (5, 3, 8)])
+def test_domain_from_histogram_with_the_reference_assignment(nranks, level, over):
+    """assign="reference": the same top tree, leaves handed to tasks by the reference's greedy rule; a valid domain whose
+    per-task load stays within one (heaviest) leaf of the mean, with cost weights as well."""
+    import shenqi_b200 as sq
+    box = 8.0
+    pos = random_clustered(100000, box, 7)
+    keys = o_keys(pos, box)
+    cnt = _hist(keys, level)
+    for cost in (None, cnt * (1.0 + (np.arange(len(cnt)) % 5))):
+        D = sq.domain_from_histogram(cnt, nranks, over, cost=cost, assign="reference")
+        D.validate()
+        owner = _check_domain(D, nranks, keys, level)
+        w = np.ones(len(keys)) if cost is None else (1.0 + ((keys >> np.uint64(63 - 3 * level)).astype(np.int64) % 5))
+        load = np.bincount(owner, weights=w, minlength=nranks)
+        leafload = np.bincount(D.topleaf_of(keys), weights=w, minlength=D.ntopleaves)
+        assert load.min() > 0 and np.abs(load - load.mean()).max() <= leafload.max() + 1e-9
