@@ -17,7 +17,7 @@
  *   sq_tree_walk             grav_short_tree (libgadget/gravity.h:89, gravshort-tree2.cpp:141)
  *   sq_set_walk_raw          the GravTreeParams argument of grav_short_tree_cuda (libgadget/gravshort2.hpp:21-55, 440-443)
  *   sq_pm_force              gravpm_force -> petapm_force (libgadget/gravity.h:86, petapm.cpp:472)
- *   sq_drift_device          drift_all_particles (libgadget/drift.h:9, drift.cpp:84)
+ *   sq_drift_device          drift_all_particles (libgadget/drift.h:9, drift.cpp:81)
  *   sq_kick_device           apply_hierarchical_grav_kick (libgadget/timestep.cpp:249)
  *   sq_active_sublist_device build_active_sublist (libgadget/timestep.cpp:111, 1373)
  *   sq_gravity_timebins_device / sq_timebin_pushdown_device
@@ -326,7 +326,7 @@ int sq_toptree_export_count(sq_ctx * ctx, int64_t * nexports, int64_t * nparticl
  * All pointers except random_shift and nsub are device pointers on the context's device; work is queued on the
  * context's stream.  `skip` (may be NULL) holds one byte per particle, non-zero = IsGarbage || Swallowed.
  *
- * sq_drift_device replaces drift_all_particles / real_drift_particle (libgadget/drift.cpp:16-81, 84-103) for
+ * sq_drift_device replaces drift_all_particles / real_drift_particle (libgadget/drift.cpp:16-78, 81-99) for
  * collisionless particles: Pos += Vel * ddrift + random_shift, wrapped into (0, BoxSize]; skipped particles only
  * follow the shift.  A non-finite result is fatal in the reference (endrun 5): SQ_ERR_NONFINITE here.
  * sq_kick_device replaces the loop of apply_hierarchical_grav_kick (libgadget/timestep.cpp:270-287, 962-968):

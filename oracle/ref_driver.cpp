@@ -10,7 +10,7 @@
  *   grav_short_tree                libgadget/gravshort-tree2.cpp:141
  *   GravLocalTreeWalk::visit       libgadget/gravshort2.hpp:227   (interaction counts)
  *   grav_short_pair                libgadget/gravshort-pair.c:22
- *   drift_all_particles            libgadget/drift.cpp:84
+ *   drift_all_particles            libgadget/drift.cpp:81
  * the way libgadget/tests/test_forcetree.cpp:294-331 and test_gravity.cpp:197-247 do
  * (single rank, trivial domain).  Only tests/, smoke() and bench.py's CPU-baseline leg load it.
  */
@@ -160,7 +160,7 @@ void ref_get_particles(double * pos, float * mass, uint64_t * ids, double * full
     }
 }
 
-/* drift_all_particles (drift.cpp:84-103) on the loaded particles with the given velocities; flags: bit0 IsGarbage, bit1 Swallowed */
+/* drift_all_particles (drift.cpp:81-99) on the loaded particles with the given velocities; flags: bit0 IsGarbage, bit1 Swallowed */
 void ref_drift_all(const double * vel, const unsigned char * flags, double ddrift, const double * random_shift)
 {
     #pragma omp parallel for

@@ -671,7 +671,7 @@ int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsign
     return m;
 }
 
-/* libgadget/timebinmgr.cpp:190-203 */
+/* libgadget/timebinmgr.cpp:189-202 */
 int64_t sqo_round_down_power_of_two(int64_t dti)
 {
     int64_t ti_min = (int64_t) 1 << 46;

@@ -116,7 +116,7 @@ int64_t sqo_active_sublist(const int32_t * active, int64_t nactive, const unsign
 /* libgadget/timestep.cpp:351-377 (gravity time-bin assignment of hierarchical_gravity_accelerations) with
  * grav_acceleration2 / get_timestep_gravity_dloga (:1012-1039), convert_timestep_to_ti (:157-174),
  * TimeBinMgr::dti_from_dloga / ti_from_loga_snap (libgadget/timebinmgr.h:123-156), round_down_power_of_two
- * (libgadget/timebinmgr.cpp:190-203), get_timestep_bin (:1236-1250).  Same scalars as sq_timebin_params. */
+ * (libgadget/timebinmgr.cpp:189-202), get_timestep_bin (:1236-1250).  Same scalars as sq_timebin_params. */
 typedef struct sqo_timebin_params {
     double atime, hubble, ErrTolIntAccuracy, MinSizeTimestep, softening;
     int64_t Ti_Current, dti_max;

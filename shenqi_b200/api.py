@@ -577,7 +577,7 @@ class Context:
 
     # ---- drift_all_particles / apply_hierarchical_grav_kick / build_active_sublist on device arrays
     def drift_device(self, pos_ptr, vel_ptr, n, ddrift, random_shift, BoxSize, skip_ptr=None):
-        """drift_all_particles (libgadget/drift.cpp:84-103): pos, vel = device double[n][3]; skip = device uint8[n] or None."""
+        """drift_all_particles (libgadget/drift.cpp:81-99): pos, vel = device double[n][3]; skip = device uint8[n] or None."""
         sh = (c_dbl * 3)(*[float(x) for x in random_shift]) if random_shift is not None else None
         self._check(self.L.sq_drift_device(self._ctx, ctypes.c_void_p(pos_ptr), ctypes.c_void_p(vel_ptr), ctypes.c_void_p(skip_ptr),
                                            c_i64(n), c_dbl(ddrift), sh, c_dbl(BoxSize)))

@@ -1,7 +1,7 @@
 // the steps either side of each tree call in hierarchical stepping, on device arrays, so that
 // particles stay resident between sub-steps (BASELINE config 5).  All three are HBM-bound streaming kernels.
 //
-//   sq_drift_device           real_drift_particle / drift_all_particles    libgadget/drift.cpp:16-81, 84-103
+//   sq_drift_device           real_drift_particle / drift_all_particles    libgadget/drift.cpp:16-78, 81-99
 //   sq_kick_device            apply_hierarchical_grav_kick + do_grav_short_range_kick
 //                                                                          libgadget/timestep.cpp:247-288, 962-968
 //   sq_active_sublist_device  SubActivePredicate + build_active_sublist    libgadget/timestep.cpp:1353-1397

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Regenerates tests/golden/step_ref.npz from the reference's OWN drift_all_particles (libgadget/drift.cpp:84-103,
+"""Regenerates tests/golden/step_ref.npz from the reference's OWN drift_all_particles (libgadget/drift.cpp:81-99,
 compiled unmodified into oracle/_ref/libshenqi_ref.so; run in the build container only).  Contents: a seeded
 4096-particle set with velocities large enough that some coordinates wrap once or several times in either
 direction, IsGarbage / Swallowed flags on a few particles, a random shift, and the reference's positions after the

@@ -278,7 +278,7 @@ def reference_gravity_test_metric(total, direct):
 
 # ----------------------------------------------------------------------------- reference wrappers
 def r_drift(pos, vel, flags, ddrift, shift, box):
-    """The reference's drift_all_particles (libgadget/drift.cpp:84) on (pos, vel); flags bit0 IsGarbage, bit1 Swallowed."""
+    """The reference's drift_all_particles (libgadget/drift.cpp:81) on (pos, vel); flags bit0 IsGarbage, bit1 Swallowed."""
     R = ref()
     pos = np.ascontiguousarray(pos, np.float64)
     r_load(pos, np.ones(len(pos), np.float32), box)
