@@ -111,6 +111,29 @@ def cpu_threads():
     return n
 
 
+def reference_pm_subprocess(pos, mass, box, nmesh, G, asmth=1.5, timeout=900):
+    """tools/ref_pm_once.py on (pos, mass): {"pm_ref_s": seconds of gravpm_force, "gravpm_ref": accelerations in input order}
+    or {"pm_ref_s": None, "pm_ref_error": why}."""
+    import subprocess, tempfile
+    scratch = os.path.join(ROOT, "oracle", "_ref", "scratch")
+    try:
+        os.makedirs(scratch, exist_ok=True)
+        with tempfile.TemporaryDirectory(dir=scratch) as d:
+            src, dst = os.path.join(d, "in.npz"), os.path.join(d, "out.npz")
+            np.savez(src, pos=pos, mass=mass, box=np.float64(box), nmesh=np.int64(nmesh), asmth=np.float64(asmth), G=np.float64(G))
+            env = dict(os.environ, OMP_NUM_THREADS=str(cpu_threads()))
+            for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+                env.pop(k, None)
+            r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ref_pm_once.py"), src, dst], env=env, timeout=timeout,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+            if r.returncode != 0 or not os.path.exists(dst):
+                return {"pm_ref_s": None, "pm_ref_error": "exit %d: %s" % (r.returncode, r.stderr.decode(errors="replace")[-300:])}
+            o = np.load(dst)
+            return {"pm_ref_s": float(o["seconds"]), "gravpm_ref": o["gravpm"]}
+    except Exception as e:                                   # noqa
+        return {"pm_ref_s": None, "pm_ref_error": repr(e)}
+
+
 def cpu_reference_step(pos, mass, par, old=None, want="auto", with_pm=True):
     """One step of the reference's own CPU code (oracle/_ref: slots_gc_sorted, force_tree_full, grav_short_tree, OpenMP, all
     host cores) or, if that was not built, of the C port (oracle/).  old = (FullTreeGravAccel, GravPM) inputs of the
@@ -177,17 +200,9 @@ def _cpu_reference_step(H, pos, mass, par, opar, meansep, use_ref, out, old, wit
         t0 = time.perf_counter(); H.o_pm_force(pos, mass, box, par["Nmesh"], 1.5, par["G"]); out["pm_s"] = time.perf_counter() - t0
         if use_ref and hasattr(H.ref(), "ref_petapm_fft"):
             # the reference's own gravpm_force (gravpm.cpp + petapm.cpp, unmodified; includes the tree it builds for its
-            # regions) on the particles still loaded; its FFT is the stand-in of oracle/ref_shim/heffte.h, not FFTW
-            try:
-                scratch = os.path.join(ROOT, "oracle", "_ref", "scratch")
-                os.makedirs(scratch, exist_ok=True)
-                H.ref().ref_set_power_dir(scratch.encode())
-                t0 = time.perf_counter(); H.ref().ref_gravpm_force(H.c_int(par["Nmesh"]), H.c_dbl(1.5), H.c_dbl(par["G"])); out["pm_ref_s"] = time.perf_counter() - t0
-                g = np.zeros((n, 3)); H.ref().ref_get_gravpm(H.ptr(g))
-                out["gravpm_ref"] = np.zeros((n, 3)); out["gravpm_ref"][inv] = g          # back to input order
-            except Exception as e:                                                        # a reported extra, never fatal
-                out["pm_ref_s"] = None
-                out["pm_ref_error"] = repr(e)
+            # regions; its FFT is the stand-in of oracle/ref_shim/heffte.h, not FFTW) - in a process of its own: an
+            # abort inside the reference must not take the benchmark down.  A reported extra, never fatal.
+            out.update(reference_pm_subprocess(pos, mass, box, par["Nmesh"], par["G"]))
     out["step_s"] = out["sort_s"] + out["tree_s"] + out["walk_s"]
     return out
 
